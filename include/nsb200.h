@@ -1,0 +1,182 @@
+/* nsb200.h -- C-ABI of libnsb200.so: hand-written sm_100a CUDA kernels for the per-step
+ * hot path of the P2-P1 incompressible Navier-Stokes solvers of
+ * LKM-code-base/NavierStokes-with-Fenics (finite-element assembly, Dirichlet rows, sparse
+ * Krylov solves, BDF history updates).
+ *
+ * The reference has no FFI of its own: the seam is the subset of the dolfin Python API its
+ * solver classes call.  Each entry point below cites the reference call site
+ * (file:line under /root/reference) whose native work it replaces.
+ *
+ * Conventions
+ *  - every function returns 0 on success, <0 on error; nsb_last_error() gives the message.
+ *    No C++ exception crosses this boundary.  The Python shim raises RuntimeError on != 0,
+ *    which keeps the reference's `except RuntimeError` continuation fallback working
+ *    (source/ns_problem.py:462-501).
+ *  - "dev" pointers are device addresses (e.g. torch.Tensor.data_ptr()); buffers are owned by
+ *    the caller, the library never frees them.  "host" pointers are ordinary host memory.
+ *  - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Calls are
+ *    asynchronous unless they return a scalar to the host.
+ *  - one nsb_ctx per GPU / rank; not thread-safe; no internal threads.
+ *  - all floating point is IEEE double; all indices int32 (value offsets are widened to
+ *    int64 inside the kernels).
+ *  - P2 "nodes" are scalar: vertex v -> v, edge e -> nverts + e.  The collapsed velocity
+ *    space V = [P2]^d is interleaved, dof = d*node + comp; Q = P1, dof = vertex.
+ *    Cell-local P2 order: vertices then edges in UFC order.
+ */
+#ifndef NSB200_H
+#define NSB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nsb_ctx nsb_ctx;
+typedef struct nsb_pattern_builder nsb_pattern_builder;
+
+#define NSB_VERSION 100
+
+/* assembly flags */
+#define NSB_VEC 1        /* assemble the vector (residual / rhs)            */
+#define NSB_MAT 2        /* assemble the matrix (Jacobian / lhs)            */
+#define NSB_PICARD 4     /* Jacobian without the Newton term (frozen convecting velocity) */
+#define NSB_BDF 8        /* mixed forms: include the BDF mass term          */
+#define NSB_SYMBC 16     /* mixed forms: SystemAssembler symmetric local BC elimination */
+
+/* pattern ids for nsb_set_pattern */
+#define NSB_PAT_P2P2 0   /* scalar P2 nodes x P2 nodes (velocity BSR-d / mass CSR)  */
+#define NSB_PAT_P1P1 1   /* vertices x vertices (pressure)                           */
+#define NSB_PAT_WW 2     /* mixed Taylor-Hood dofs x dofs (monolithic solvers)       */
+
+/* matrix kinds for nsb_matrix */
+#define NSB_CSR 0        /* scalar CSR applied to `bs` interleaved components: y[bs*i+c] = sum_j a_ij x[bs*j+c] */
+#define NSB_BSR 1        /* bs x bs dense blocks, row-major inside the block         */
+
+/* Dirichlet modes */
+#define NSB_BC_LINEAR 0  /* b[i] = g[i]          LinearVariationalSolver  bc.apply(A,b)   */
+#define NSB_BC_NEWTON 1  /* b[i] = x[i] - g[i]   NonlinearVariationalSolver bc.apply(b,x) */
+
+typedef struct nsb_matrix {
+    int32_t kind;            /* NSB_CSR | NSB_BSR                                        */
+    int32_t bs;              /* components (CSR) or block size (BSR)                      */
+    int32_t nrows;           /* scalar / block rows                                       */
+    int32_t nnz;             /* stored scalar (CSR) / block (BSR) entries = rowptr[nrows]  */
+    const int32_t* rowptr;   /* dev [nrows+1]                                             */
+    const int32_t* col;      /* dev [nnz] ascending per row                               */
+    const double* vals;      /* dev [nnz] (CSR) or [nnz*bs*bs] (BSR)                      */
+    const uint8_t* bc_mask;  /* dev [nrows*bs] or NULL: 1 = Dirichlet dof, the operator acts
+                                as the identity on that row (dolfin `ident`, diagonal 1.0) */
+} nsb_matrix;
+
+/* ---------------------------------------------------------------- life cycle ---------- */
+int nsb_version(void);
+int nsb_create(nsb_ctx** ctx, int device);
+int nsb_destroy(nsb_ctx* ctx);
+const char* nsb_last_error(const nsb_ctx* ctx);   /* ctx may be NULL: last ctx-less error */
+
+/* ---------------------------------------------------------------- host-side setup ------
+ * Sparsity pattern = union over cells of (row dofs x col dofs) of the whole element, columns
+ * ascending, no extra diagonal: dolfin SparsityPatternBuilder + PETSc AIJ as triggered by
+ * source/ns_solver_base.py:501-524 (function spaces) and every assemble().  Also emits the
+ * row -> (cell, local row, slot of every local column) incidence used by the atomic-free
+ * row-gather assembly kernels (the compressed cell-to-nnz map).  Pure CPU, setup only. */
+int nsb_pattern_build(int32_t nrows, int32_t ncells,
+                      int32_t nloc_row, const int32_t* cell_rows_host,
+                      int32_t nloc_col, const int32_t* cell_cols_host,
+                      nsb_pattern_builder** out);
+int nsb_pattern_sizes(const nsb_pattern_builder* pb, int64_t* nnz, int64_t* npairs, int32_t* max_row_len);
+int nsb_pattern_fill(const nsb_pattern_builder* pb, int32_t* rowptr, int32_t* col,
+                     int32_t* pair_ptr, int32_t* pair_cell, uint8_t* pair_iloc, uint8_t* pair_slots);
+int nsb_pattern_free(nsb_pattern_builder* pb);
+
+/* ---------------------------------------------------------------- device state --------- */
+/* mesh of source/grid_generator.py:111-208 (ordered simplices) + scalar P2 node map */
+int nsb_set_mesh(nsb_ctx* ctx, int32_t dim, int32_t nverts, const double* coords_dev,
+                 int32_t ncells, const int32_t* cell_verts_dev,
+                 int32_t nnodes, const int32_t* cell_nodes_dev);
+int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows,
+                    const int32_t* rowptr_dev, const int32_t* col_dev,
+                    const int32_t* pair_ptr_dev, const int32_t* pair_cell_dev,
+                    const uint8_t* pair_iloc_dev, const uint8_t* pair_slots_dev);
+/* mixed Taylor-Hood dof map [ncells x (d*NL2 + d+1)] (source/ns_solver_base.py:501-524) */
+int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs_dev);
+/* scalars: dlfn.Constant.assign of k, alpha_i (source/ns_ipcs_solver.py:210-227,
+ * source/ns_bdf_solver.py:108-126) and EquationCoefficientHandler values
+ * (source/auxiliary_classes.py:251-306).  coef = {k, a0, a1, a2, c_conv, c_p, c_visc, c_body} */
+int nsb_set_coefficients(nsb_ctx* ctx, const double* coef_host8);
+
+/* ---------------------------------------------------------------- assembly (K1-K8) ------ */
+/* IPCS tentative velocity F / J = derivative(F,u*)   source/ns_ipcs_solver.py:106-147 (:126-130, :136)
+ * b_out [d*nnodes]; A_out BSR-d values on NSB_PAT_P2P2. */
+int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const double* ustar, const double* un,
+                               const double* unm1, const double* pn, double* b_out, double* A_out,
+                               void* stream);
+/* IPCS pressure Poisson a / L   source/ns_ipcs_solver.py:149-171 (:160-164) */
+int nsb_assemble_poisson(nsb_ctx* ctx, int32_t flags, const double* pn, const double* ustar,
+                         double* b_out, double* A_out, void* stream);
+/* IPCS velocity correction a / L   source/ns_ipcs_solver.py:173-196 (:183-187).
+ * A_out: scalar P2 mass on NSB_PAT_P2P2 (the d x d block matrix of dolfin is mass (x) I_d). */
+int nsb_assemble_correction(nsb_ctx* ctx, int32_t flags, const double* ustar, const double* pnew,
+                            const double* pold, double* b_out, double* A_out, void* stream);
+/* P1 mass matrix and lumped weights int psi_v dx: dlfn.project / mean-pressure functionals
+ * source/ns_solver_base.py:1151,1168,1190-1203 */
+int nsb_assemble_p1_mass(nsb_ctx* ctx, int32_t flags, double* w_out, double* A_out, void* stream);
+/* monolithic residual / Jacobian on W   source/ns_bdf_solver.py:68-88,
+ * source/ns_solver_base.py:913-936; flags NSB_VEC|NSB_MAT|NSB_PICARD|NSB_BDF */
+int nsb_assemble_mixed(nsb_ctx* ctx, int32_t flags, const double* w0, const double* w1,
+                       const double* w2, double* b_out, double* A_out, void* stream);
+
+/* ---------------------------------------------------------------- Dirichlet rows (K9) ---- */
+/* DirichletBC.apply(A): zero the rows, diagonal 1.0, columns untouched (App. A.5);
+ * dofs are scalar dof indices (bs*node+comp for BSR). */
+int nsb_bc_apply_matrix(nsb_ctx* ctx, int32_t kind, int32_t bs, const int32_t* rowptr,
+                        const int32_t* col, double* vals, int32_t nbc, const int32_t* bc_dofs,
+                        void* stream);
+/* DirichletBC.apply(b) / apply(b,x) */
+int nsb_bc_apply_vector(nsb_ctx* ctx, int32_t mode, double* b, const double* x, int32_t nbc,
+                        const int32_t* bc_dofs, const double* bc_vals, void* stream);
+/* SystemAssembler symmetric local elimination (source/auxiliary_classes.py:141,160-164) is
+ * done inside nsb_assemble_mixed (flag NSB_SYMBC) from this table: mask[ndofs] (1 = Dirichlet
+ * dof) and g[ndofs] (boundary value, 0 elsewhere), both device arrays. */
+int nsb_set_mixed_bc(nsb_ctx* ctx, const uint8_t* bc_mask_dev, const double* bc_g_dev);
+
+/* ---------------------------------------------------------------- linear algebra (K10-13) */
+int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void* stream);
+/* inv_diag[i] = 1/A_ii (1 on masked rows): Jacobi preconditioner (K12) */
+int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_diag, void* stream);
+int64_t nsb_cg_workspace_doubles(int64_t n);
+int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart);
+/* Jacobi-preconditioned CG for the SPD pressure-Poisson and mass systems which the reference
+ * solves by LU (source/ns_ipcs_solver.py:171,195-196).  nullspace != 0: the operator has the
+ * constant null space (all-Neumann pressure): rhs and solution are projected to
+ * zero arithmetic mean.  Converged when ||r|| <= max(rtol*||b||, atol). */
+int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, const double* b, double* x,
+           double rtol, double atol, int32_t maxit, int32_t nullspace, double* work,
+           int32_t* iters_out, double* resid_out, void* stream);
+/* right-Jacobi-preconditioned restarted GMRES for the velocity / mixed systems
+ * (source/ns_ipcs_solver.py:138-147, source/ns_bdf_solver.py:91-100) */
+int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, const double* b, double* x,
+              double rtol, double atol, int32_t maxit, int32_t restart, double* work,
+              int32_t* iters_out, double* resid_out, void* stream);
+
+/* Function.assign / Vector ops (source/ns_ipcs_solver.py:41-43, source/ns_solver_base.py:1015-1016) */
+int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y, void* stream);
+int nsb_vec_axpy(nsb_ctx* ctx, int64_t n, double a, const double* x, double* y, void* stream); /* y += a x */
+int nsb_vec_scale(nsb_ctx* ctx, int64_t n, double a, double* x, void* stream);
+int nsb_vec_dot(nsb_ctx* ctx, int64_t n, const double* x, const double* y, double* out_host, void* stream);
+int nsb_vec_sum(nsb_ctx* ctx, int64_t n, const double* x, double* out_host, void* stream);
+/* FunctionAssigner (source/ns_solver_base.py:424-476): y[idx[i]] = x[i] / y[i] = x[idx[i]] */
+int nsb_vec_scatter(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream);
+int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream);
+/* BDF history shift of the IPCS fields, one launch (source/ns_ipcs_solver.py:35-43):
+ * u2 <- u1 <- u0 ; p_old <- p */
+int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, double* u2,
+                     int64_t nq, const double* p, double* p_old, void* stream);
+
+/* measured FP64 FMA rate (TFLOP/s) of this device: roofline denominator for element kernels */
+int nsb_fp64_peak(nsb_ctx* ctx, double* tflops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

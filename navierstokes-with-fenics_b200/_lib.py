@@ -1,0 +1,98 @@
+"""ctypes binding of libnsb200.so (include/nsb200.h).  There is no CPU fallback: a missing
+library or a missing GPU raises, loudly."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnsb200.so")
+
+# constants of include/nsb200.h
+VEC, MAT, PICARD, BDF, SYMBC = 1, 2, 4, 8, 16
+PAT_P2P2, PAT_P1P1, PAT_WW = 0, 1, 2
+CSR, BSR = 0, 1
+BC_LINEAR, BC_NEWTON = 0, 1
+
+c_i32p = C.POINTER(C.c_int32)
+c_u8p = C.POINTER(C.c_uint8)
+c_f64p = C.POINTER(C.c_double)
+c_i64p = C.POINTER(C.c_int64)
+vp = C.c_void_p
+
+
+class Matrix(C.Structure):
+    """struct nsb_matrix"""
+    _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
+                ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp)]
+
+
+# name -> (restype, argtypes); every symbol include/nsb200.h declares
+PROTOTYPES = {
+    "nsb_version": (C.c_int, []),
+    "nsb_create": (C.c_int, [C.POINTER(vp), C.c_int]),
+    "nsb_destroy": (C.c_int, [vp]),
+    "nsb_last_error": (C.c_char_p, [vp]),
+    "nsb_pattern_build": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32, vp, C.POINTER(vp)]),
+    "nsb_pattern_sizes": (C.c_int, [vp, c_i64p, c_i64p, c_i32p]),
+    "nsb_pattern_fill": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+    "nsb_pattern_free": (C.c_int, [vp]),
+    "nsb_set_mesh": (C.c_int, [vp, C.c_int32, C.c_int32, vp, C.c_int32, vp, C.c_int32, vp]),
+    "nsb_set_pattern": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),
+    "nsb_set_coefficients": (C.c_int, [vp, c_f64p]),
+    "nsb_assemble_ipcs_momentum": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp]),
+    "nsb_assemble_poisson": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp]),
+    "nsb_assemble_correction": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_assemble_p1_mass": (C.c_int, [vp, C.c_int32, vp, vp, vp]),
+    "nsb_assemble_mixed": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_bc_apply_matrix": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, C.c_int32, vp, vp]),
+    "nsb_bc_apply_vector": (C.c_int, [vp, C.c_int32, vp, vp, C.c_int32, vp, vp, vp]),
+    "nsb_set_mixed_bc": (C.c_int, [vp, vp, vp]),
+    "nsb_spmv": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp]),
+    "nsb_inv_diagonal": (C.c_int, [vp, C.POINTER(Matrix), vp, vp]),
+    "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
+    "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32]),
+    "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
+                         vp, c_i32p, c_f64p, vp]),
+    "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
+                            vp, c_i32p, c_f64p, vp]),
+    "nsb_vec_copy": (C.c_int, [vp, C.c_int64, vp, vp, vp]),
+    "nsb_vec_axpy": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp, vp]),
+    "nsb_vec_scale": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp]),
+    "nsb_vec_dot": (C.c_int, [vp, C.c_int64, vp, vp, c_f64p, vp]),
+    "nsb_vec_sum": (C.c_int, [vp, C.c_int64, vp, c_f64p, vp]),
+    "nsb_vec_scatter": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp]),
+    "nsb_vec_gather": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp]),
+    "nsb_ipcs_advance": (C.c_int, [vp, C.c_int64, vp, vp, vp, C.c_int64, vp, vp, vp]),
+    "nsb_fp64_peak": (C.c_int, [vp, c_f64p]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen libnsb200.so and attach the prototypes (raises if the library is not built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "libnsb200.so is not built (%s): run __graft_entry__.build(); there is no CPU fallback"
+                % LIB_PATH)
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(lib, name)     # AttributeError if the symbol is missing
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def last_error(ctx=None):
+    msg = load().nsb_last_error(ctx)
+    return msg.decode() if msg else ""
+
+
+def check(status, ctx=None):
+    """0 -> ok; otherwise RuntimeError (what dolfin raises on solver failure,
+    source/ns_problem.py:470 catches it)."""
+    if status != 0:
+        raise RuntimeError("nsb200: " + last_error(ctx))

@@ -1,0 +1,146 @@
+// common.cuh -- context, error plumbing and device helpers shared by the nsb200 kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include "../../include/nsb200.h"
+
+#define NSB_MAX_PARTIALS 4096
+
+struct nsb_pattern_dev {
+    int32_t nrows = 0;
+    const int32_t* rowptr = nullptr;
+    const int32_t* col = nullptr;
+    const int32_t* pair_ptr = nullptr;
+    const int32_t* pair_cell = nullptr;
+    const uint8_t* pair_iloc = nullptr;
+    const uint8_t* pair_slots = nullptr;
+};
+
+struct nsb_coef {
+    double k, a0, a1, a2, c_conv, c_p, c_visc, c_body;
+};
+
+struct nsb_ctx {
+    int device = 0;
+    int sm_count = 148;
+    std::string err;
+    // mesh
+    int32_t dim = 0, nverts = 0, ncells = 0, nnodes = 0;
+    const double* coords = nullptr;
+    const int32_t* cell_verts = nullptr;
+    const int32_t* cell_nodes = nullptr;
+    nsb_pattern_dev pat[3];
+    // mixed space
+    int32_t ndofs_w = 0;
+    const int32_t* cell_dofs_w = nullptr;
+    const uint8_t* w_bc_mask = nullptr;
+    const double* w_bc_g = nullptr;
+    nsb_coef coef = {1.0, 1.0, -1.0, 0.0, 1.0, 1.0, 1.0, 1.0};
+    // reduction scratch (device) + pinned host mirror
+    double* d_partials = nullptr;     // [NSB_MAX_PARTIALS * 8]
+    double* d_scalars = nullptr;      // [64] device-resident Krylov scalars
+    unsigned int* d_counter = nullptr;
+    double* h_scalars = nullptr;      // pinned [256]
+};
+
+extern thread_local std::string g_nsb_last_error;
+
+static inline int nsb_fail(nsb_ctx* ctx, const char* fmt, const char* a = "", const char* b = "") {
+    char buf[512];
+    snprintf(buf, sizeof buf, fmt, a, b);
+    if (ctx) ctx->err = buf;
+    g_nsb_last_error = buf;
+    return -1;
+}
+
+#define NSB_CUDA(ctx, call)                                                        \
+    do {                                                                           \
+        cudaError_t e_ = (call);                                                   \
+        if (e_ != cudaSuccess) return nsb_fail(ctx, "CUDA error %s at %s", cudaGetErrorString(e_), #call); \
+    } while (0)
+
+#define NSB_LAUNCH_CHECK(ctx, name)                                                \
+    do {                                                                           \
+        cudaError_t e_ = cudaGetLastError();                                       \
+        if (e_ != cudaSuccess) return nsb_fail(ctx, "launch of %s failed: %s", name, cudaGetErrorString(e_)); \
+    } while (0)
+
+#define NSB_REQUIRE(ctx, cond, msg)                                                \
+    do {                                                                           \
+        if (!(cond)) return nsb_fail(ctx, "%s (%s)", msg, #cond);                  \
+    } while (0)
+
+static inline int nsb_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+// ---- warp helpers ------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int LANES>
+__device__ __forceinline__ double group_sum(double v) {
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Deterministic block reduction of NV values; result valid in thread 0.
+template <int NV, int THREADS>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* [NV * THREADS/32] */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = warp_sum(v[i]);
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) smem[i * (THREADS / 32) + w] = v[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            double s = 0.0;
+            for (int j = 0; j < THREADS / 32; ++j) s += smem[i * (THREADS / 32) + j];
+            v[i] = s;
+        }
+    }
+}
+
+// Grid-wide deterministic reduction: every block writes its partials, the last block to
+// finish sums them in block order and stores into out[0..NV).  `counter` must be 0 on entry
+// and is reset to 0 on exit.
+template <int NV, int THREADS>
+__device__ __forceinline__ void grid_sum(double (&v)[NV], double* partials, unsigned int* counter,
+                                         double* out, double* smem) {
+    block_sum<NV, THREADS>(v, smem);
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) partials[(size_t)i * gridDim.x + blockIdx.x] = v[i];
+        __threadfence();
+        unsigned int t = atomicAdd(counter, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double s[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            s[i] = 0.0;
+            for (int j = threadIdx.x; j < (int)gridDim.x; j += THREADS)
+                s[i] += ((volatile double*)partials)[(size_t)i * gridDim.x + j];
+        }
+        __syncthreads();
+        block_sum<NV, THREADS>(s, smem);
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int i = 0; i < NV; ++i) out[i] = s[i];
+            *counter = 0u;
+        }
+    }
+}

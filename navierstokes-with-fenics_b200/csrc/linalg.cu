@@ -1,0 +1,200 @@
+// linalg.cu -- SpMV launcher, Jacobi diagonal (K12), vector kernels and the BDF history shift
+// (K13), reductions (K15).
+#include "spmv.cuh"
+
+// ---- SpMV dispatch ---------------------------------------------------------------------------
+template <int KIND, int BS, int LANES>
+static int launch_spmv_t(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
+                         const double* dot_with, double* scalar_out, cudaStream_t st) {
+    constexpr int RPB = NSB_SPMV_THREADS / LANES;
+    int64_t blocks = ((int64_t)A->nrows + RPB - 1) / RPB;
+    if (dot_with) {
+        const int64_t cap = (int64_t)ctx->sm_count * 8;
+        if (blocks > cap) blocks = cap;
+        k_spmv<KIND, BS, LANES, true><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
+            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, y, dot_with, ctx->d_partials,
+            ctx->d_counter, scalar_out);
+    } else {
+        k_spmv<KIND, BS, LANES, false><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
+            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, y, nullptr, nullptr, nullptr, nullptr);
+    }
+    NSB_LAUNCH_CHECK(ctx, "k_spmv");
+    return 0;
+}
+
+template <int KIND, int BS>
+static int launch_spmv_bs(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
+                          const double* dot_with, double* scalar_out, cudaStream_t st) {
+    double per_row = A->nrows > 0 ? (double)A->nnz / (double)A->nrows : 0.0;
+    if (KIND == NSB_BSR) per_row *= BS * BS;
+    if (per_row <= 10.0) return launch_spmv_t<KIND, BS, 4>(ctx, A, x, y, dot_with, scalar_out, st);
+    if (per_row <= 24.0) return launch_spmv_t<KIND, BS, 8>(ctx, A, x, y, dot_with, scalar_out, st);
+    if (per_row <= 64.0) return launch_spmv_t<KIND, BS, 16>(ctx, A, x, y, dot_with, scalar_out, st);
+    return launch_spmv_t<KIND, BS, 32>(ctx, A, x, y, dot_with, scalar_out, st);
+}
+
+int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
+                    const double* dot_with, double* scalar_out, cudaStream_t st) {
+    NSB_REQUIRE(ctx, A && A->rowptr && A->col && A->vals && A->nrows > 0, "bad matrix descriptor");
+    NSB_REQUIRE(ctx, x && y && x != y, "bad vectors (x must not alias y)");
+    if (A->kind == NSB_CSR) {
+        switch (A->bs) {
+            case 1: return launch_spmv_bs<NSB_CSR, 1>(ctx, A, x, y, dot_with, scalar_out, st);
+            case 2: return launch_spmv_bs<NSB_CSR, 2>(ctx, A, x, y, dot_with, scalar_out, st);
+            case 3: return launch_spmv_bs<NSB_CSR, 3>(ctx, A, x, y, dot_with, scalar_out, st);
+        }
+    } else if (A->kind == NSB_BSR) {
+        switch (A->bs) {
+            case 2: return launch_spmv_bs<NSB_BSR, 2>(ctx, A, x, y, dot_with, scalar_out, st);
+            case 3: return launch_spmv_bs<NSB_BSR, 3>(ctx, A, x, y, dot_with, scalar_out, st);
+        }
+    }
+    return nsb_fail(ctx, "unsupported matrix kind / block size%s%s");
+}
+
+extern "C" int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    return nsb_launch_spmv(ctx, A, x, y, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+// ---- Jacobi: inverse diagonal ------------------------------------------------------------------
+__global__ void k_inv_diag(int kind, int bs, int32_t nrows, const int32_t* __restrict__ rowptr,
+                           const int32_t* __restrict__ col, const double* __restrict__ vals,
+                           const uint8_t* __restrict__ mask, double* __restrict__ out) {
+    const int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= (int64_t)nrows * bs) return;
+    const int32_t row = (int32_t)(d / bs);
+    const int comp = (int)(d % bs);
+    double diag = 0.0;
+    int lo = rowptr[row], hi = rowptr[row + 1] - 1;
+    while (lo <= hi) {   // columns ascending: binary search for the diagonal
+        const int mid = (lo + hi) >> 1;
+        const int32_t c = col[mid];
+        if (c == row) {
+            diag = (kind == NSB_CSR) ? vals[mid] : vals[(int64_t)mid * bs * bs + comp * bs + comp];
+            break;
+        }
+        if (c < row) lo = mid + 1; else hi = mid - 1;
+    }
+    if (mask != nullptr && mask[d]) diag = 1.0;
+    out[d] = (diag != 0.0) ? 1.0 / diag : 1.0;
+}
+
+extern "C" int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_diag, void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, A && A->rowptr && A->col && A->vals && inv_diag, "bad arguments");
+    const int64_t n = (int64_t)A->nrows * A->bs;
+    k_inv_diag<<<nsb_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(A->kind, A->bs, A->nrows, A->rowptr,
+                                                                       A->col, A->vals, A->bc_mask, inv_diag);
+    NSB_LAUNCH_CHECK(ctx, "k_inv_diag");
+    return 0;
+}
+
+// ---- vector kernels ------------------------------------------------------------------------------
+__global__ void k_axpy(int64_t n, double a, const double* __restrict__ x, double* __restrict__ y) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] += a * x[i];
+}
+__global__ void k_scale(int64_t n, double a, double* __restrict__ x) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        x[i] *= a;
+}
+__global__ void k_scatter(int64_t n, const int32_t* __restrict__ idx, const double* __restrict__ x,
+                          double* __restrict__ y) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[idx[i]] = x[i];
+}
+__global__ void k_gather(int64_t n, const int32_t* __restrict__ idx, const double* __restrict__ x,
+                         double* __restrict__ y) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = x[idx[i]];
+}
+// u2 <- u1 <- u0 and p_old <- p in one pass (source/ns_ipcs_solver.py:35-43)
+__global__ void k_ipcs_advance(int64_t nv, const double* __restrict__ u0, double* __restrict__ u1,
+                               double* __restrict__ u2, int64_t nq, const double* __restrict__ p,
+                               double* __restrict__ pold) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+        const double a = u1[i];
+        u1[i] = u0[i];
+        u2[i] = a;
+    }
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nq; i += stride) pold[i] = p[i];
+}
+
+template <bool WITH_Y>
+__global__ void __launch_bounds__(256)
+k_dot(int64_t n, const double* __restrict__ x, const double* __restrict__ y, double* partials,
+      unsigned int* counter, double* out) {
+    double s[1] = {0.0};
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        s[0] += WITH_Y ? x[i] * y[i] : x[i];
+    __shared__ double red[8];
+    grid_sum<1, 256>(s, partials, counter, out, red);
+}
+
+static int grid_for(nsb_ctx* ctx, int64_t n, int threads) {
+    int64_t b = (n + threads - 1) / threads;
+    const int64_t cap = (int64_t)ctx->sm_count * 8;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+extern "C" int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y, void* stream) {
+    NSB_REQUIRE(ctx, ctx && x && y && n >= 0, "bad arguments");
+    NSB_CUDA(ctx, cudaMemcpyAsync(y, x, sizeof(double) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+}
+extern "C" int nsb_vec_axpy(nsb_ctx* ctx, int64_t n, double a, const double* x, double* y, void* stream) {
+    NSB_REQUIRE(ctx, ctx && x && y && n >= 0, "bad arguments");
+    k_axpy<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, a, x, y);
+    NSB_LAUNCH_CHECK(ctx, "k_axpy");
+    return 0;
+}
+extern "C" int nsb_vec_scale(nsb_ctx* ctx, int64_t n, double a, double* x, void* stream) {
+    NSB_REQUIRE(ctx, ctx && x && n >= 0, "bad arguments");
+    k_scale<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, a, x);
+    NSB_LAUNCH_CHECK(ctx, "k_scale");
+    return 0;
+}
+extern "C" int nsb_vec_scatter(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream) {
+    NSB_REQUIRE(ctx, ctx && idx && x && y && n >= 0, "bad arguments");
+    k_scatter<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, idx, x, y);
+    NSB_LAUNCH_CHECK(ctx, "k_scatter");
+    return 0;
+}
+extern "C" int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream) {
+    NSB_REQUIRE(ctx, ctx && idx && x && y && n >= 0, "bad arguments");
+    k_gather<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, idx, x, y);
+    NSB_LAUNCH_CHECK(ctx, "k_gather");
+    return 0;
+}
+extern "C" int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, double* u2,
+                                int64_t nq, const double* p, double* p_old, void* stream) {
+    NSB_REQUIRE(ctx, ctx && u0 && u1 && u2 && p && p_old, "bad arguments");
+    k_ipcs_advance<<<grid_for(ctx, nv, 256), 256, 0, (cudaStream_t)stream>>>(nv, u0, u1, u2, nq, p, p_old);
+    NSB_LAUNCH_CHECK(ctx, "k_ipcs_advance");
+    return 0;
+}
+
+static int fetch_scalar(nsb_ctx* ctx, double* out_host, cudaStream_t st) {
+    NSB_CUDA(ctx, cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(double), cudaMemcpyDeviceToHost, st));
+    NSB_CUDA(ctx, cudaStreamSynchronize(st));
+    *out_host = ctx->h_scalars[0];
+    return 0;
+}
+extern "C" int nsb_vec_dot(nsb_ctx* ctx, int64_t n, const double* x, const double* y, double* out_host, void* stream) {
+    NSB_REQUIRE(ctx, ctx && x && y && out_host && n >= 0, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    k_dot<true><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, y, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
+    NSB_LAUNCH_CHECK(ctx, "k_dot");
+    return fetch_scalar(ctx, out_host, st);
+}
+extern "C" int nsb_vec_sum(nsb_ctx* ctx, int64_t n, const double* x, double* out_host, void* stream) {
+    NSB_REQUIRE(ctx, ctx && x && out_host && n >= 0, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    k_dot<false><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, nullptr, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
+    NSB_LAUNCH_CHECK(ctx, "k_dot(sum)");
+    return fetch_scalar(ctx, out_host, st);
+}

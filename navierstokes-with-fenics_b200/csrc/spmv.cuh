@@ -1,0 +1,88 @@
+// spmv.cuh -- FP64 SpMV kernels (K10): Kronecker-CSR (scalar matrix applied to BS interleaved
+// components) and BSR-BS.  LANES cooperating lanes own one (block) row; value and column
+// streams are read coalesced along the row; x is gathered through L2 (x fits the 126 MB L2 for
+// every config of SURVEY.md 8).  Rows flagged in bc_mask act as identity rows (dolfin `ident`).
+// Optional fused epilogue: deterministic grid-wide dot(x-like vector, y)  (CG: p.Ap).
+#pragma once
+#include "common.cuh"
+
+#define NSB_SPMV_THREADS 256
+
+template <int BS, int LANES>
+__device__ __forceinline__ void csr_row(int32_t row, int lane, const int32_t* __restrict__ rowptr,
+                                        const int32_t* __restrict__ col, const double* __restrict__ vals,
+                                        const double* __restrict__ x, double (&acc)[BS]) {
+#pragma unroll
+    for (int b = 0; b < BS; ++b) acc[b] = 0.0;
+    const int32_t end = rowptr[row + 1];
+    for (int32_t s = rowptr[row] + lane; s < end; s += LANES) {
+        const double v = vals[s];
+        const int64_t c = (int64_t)col[s] * BS;
+#pragma unroll
+        for (int b = 0; b < BS; ++b) acc[b] += v * x[c + b];
+    }
+}
+
+template <int BS, int LANES>
+__device__ __forceinline__ void bsr_row(int32_t row, int lane, const int32_t* __restrict__ rowptr,
+                                        const int32_t* __restrict__ col, const double* __restrict__ vals,
+                                        const double* __restrict__ x, double (&acc)[BS]) {
+    constexpr int BB = BS * BS;
+#pragma unroll
+    for (int b = 0; b < BS; ++b) acc[b] = 0.0;
+    const int32_t r0 = rowptr[row];
+    const int n = (rowptr[row + 1] - r0) * BB;
+    const double* v = vals + (int64_t)r0 * BB;
+    for (int e = lane; e < n; e += LANES) {
+        const int blk = e / BB, rc = e - blk * BB;
+        const int r = rc / BS, c = rc - r * BS;
+        const double t = v[e] * x[(int64_t)col[r0 + blk] * BS + c];
+#pragma unroll
+        for (int b = 0; b < BS; ++b) acc[b] += (b == r) ? t : 0.0;
+    }
+}
+
+// y = A x ; if DOT: scalars_out[0] = sum_i d[i] * y[i]  (d = dot_with)
+template <int KIND, int BS, int LANES, bool DOT>
+__global__ void __launch_bounds__(NSB_SPMV_THREADS)
+k_spmv(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+       const double* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
+       double* __restrict__ y, const double* __restrict__ dot_with, double* partials,
+       unsigned int* counter, double* scalar_out) {
+    constexpr int ROWS_PER_BLOCK = NSB_SPMV_THREADS / LANES;
+    const int lane = threadIdx.x % LANES;
+    double dsum[1] = {0.0};
+    for (int64_t row0 = (int64_t)blockIdx.x * ROWS_PER_BLOCK; row0 < nrows;
+         row0 += (int64_t)gridDim.x * ROWS_PER_BLOCK) {
+        const int64_t row = row0 + threadIdx.x / LANES;
+        const bool valid = row < nrows;
+        double acc[BS];
+        if (valid) {
+            if (KIND == NSB_CSR) csr_row<BS, LANES>((int32_t)row, lane, rowptr, col, vals, x, acc);
+            else bsr_row<BS, LANES>((int32_t)row, lane, rowptr, col, vals, x, acc);
+        } else {
+#pragma unroll
+            for (int b = 0; b < BS; ++b) acc[b] = 0.0;
+        }
+#pragma unroll
+        for (int b = 0; b < BS; ++b) acc[b] = group_sum<LANES>(acc[b]);
+        if (valid && lane == 0) {
+#pragma unroll
+            for (int b = 0; b < BS; ++b) {
+                const int64_t d = row * BS + b;
+                double v = acc[b];
+                if (mask != nullptr && mask[d]) v = x[d];
+                y[d] = v;
+                if (DOT) dsum[0] += dot_with[d] * v;
+            }
+        }
+    }
+    if (DOT) {
+        __shared__ double red[NSB_SPMV_THREADS / 32];
+        grid_sum<1, NSB_SPMV_THREADS>(dsum, partials, counter, scalar_out, red);
+    }
+}
+
+// host-side launcher (defined in linalg.cu)
+int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
+                    const double* dot_with, double* scalar_out, cudaStream_t st);

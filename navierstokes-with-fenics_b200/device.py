@@ -1,0 +1,259 @@
+"""Device-side state of one mesh: PyTorch tensors as device buffers (plumbing only), the
+nsb_ctx of libnsb200.so, patterns and the thin typed wrappers around the C-ABI calls."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from .spaces import TaylorHoodSpaces
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class Pattern:
+    """CSR pattern + row->(cell, local row, slots) incidence, resident on the device."""
+
+    def __init__(self, dev, nrows, cell_rows, cell_cols):
+        lib = dev.lib
+        cell_rows = np.ascontiguousarray(cell_rows, dtype=np.int32)
+        cell_cols = np.ascontiguousarray(cell_cols, dtype=np.int32)
+        ncells, nlr = cell_rows.shape
+        nlc = cell_cols.shape[1]
+        h = C.c_void_p()
+        L.check(lib.nsb_pattern_build(nrows, ncells, nlr, cell_rows.ctypes.data, nlc, cell_cols.ctypes.data,
+                                      C.byref(h)))
+        try:
+            nnz, npairs, maxrow = C.c_int64(), C.c_int64(), C.c_int32()
+            L.check(lib.nsb_pattern_sizes(h, C.byref(nnz), C.byref(npairs), C.byref(maxrow)))
+            self.nrows, self.nnz, self.npairs, self.max_row = nrows, nnz.value, npairs.value, maxrow.value
+            self.nloc_col = nlc
+            rowptr = np.empty(nrows + 1, dtype=np.int32)
+            col = np.empty(self.nnz, dtype=np.int32)
+            pair_ptr = np.empty(nrows + 1, dtype=np.int32)
+            pair_cell = np.empty(self.npairs, dtype=np.int32)
+            pair_iloc = np.empty(self.npairs, dtype=np.uint8)
+            pair_slots = np.empty(self.npairs * nlc, dtype=np.uint8)
+            L.check(lib.nsb_pattern_fill(h, rowptr.ctypes.data, col.ctypes.data, pair_ptr.ctypes.data,
+                                         pair_cell.ctypes.data, pair_iloc.ctypes.data, pair_slots.ctypes.data))
+        finally:
+            lib.nsb_pattern_free(h)
+        self.rowptr_host, self.col_host = rowptr, col
+        up = dev.upload
+        self.rowptr, self.col = up(rowptr), up(col)
+        self.pair_ptr, self.pair_cell = up(pair_ptr), up(pair_cell)
+        self.pair_iloc, self.pair_slots = up(pair_iloc), up(pair_slots)
+
+
+class Device:
+    """One GPU, one mesh.  Raises if CUDA or libnsb200.so is unavailable (no CPU fallback)."""
+
+    def __init__(self, mesh, device_index=0, mixed=False):
+        if not torch.cuda.is_available():
+            raise RuntimeError("nsb200 needs a CUDA device: there is no CPU fallback")
+        self.lib = L.load()
+        self.torch_device = torch.device("cuda", device_index)
+        torch.cuda.set_device(self.torch_device)
+        self.ctx = C.c_void_p()
+        L.check(self.lib.nsb_create(C.byref(self.ctx), device_index))
+        self.mesh = mesh
+        self.spaces = sp = TaylorHoodSpaces(mesh)
+        self.dim = sp.dim
+        self.coords = self.upload(mesh.coords)
+        self.cell_verts = self.upload(mesh.cells)
+        self.cell_nodes = self.upload(sp.cell_nodes)
+        self.check(self.lib.nsb_set_mesh(self.ctx, sp.dim, mesh.num_vertices, _ptr(self.coords), mesh.num_cells,
+                                         _ptr(self.cell_verts), sp.n_nodes, _ptr(self.cell_nodes)))
+        self.patterns = {}
+        self.coef = None
+        self.launches = 0
+        if mixed:
+            self.pattern("WW")
+        else:
+            self.pattern("P2P2")
+            self.pattern("P1P1")
+
+    def __del__(self):
+        try:
+            if getattr(self, "ctx", None):
+                self.lib.nsb_destroy(self.ctx)
+                self.ctx = None
+        except Exception:
+            pass
+
+    # ---- plumbing ---------------------------------------------------------------------------
+    def check(self, status):
+        L.check(status, self.ctx)
+
+    def upload(self, array):
+        return torch.from_numpy(np.ascontiguousarray(array)).to(self.torch_device)
+
+    def zeros(self, n, dtype=torch.float64):
+        return torch.zeros(int(n), dtype=dtype, device=self.torch_device)
+
+    def empty(self, n, dtype=torch.float64):
+        return torch.empty(int(n), dtype=dtype, device=self.torch_device)
+
+    @property
+    def stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.torch_device).cuda_stream)
+
+    def pattern(self, name):
+        if name not in self.patterns:
+            sp = self.spaces
+            if name == "P2P2":
+                pat = Pattern(self, sp.n_nodes, sp.cell_nodes, sp.cell_nodes)
+                which = L.PAT_P2P2
+            elif name == "P1P1":
+                pat = Pattern(self, sp.n_vertices, self.mesh.cells, self.mesh.cells)
+                which = L.PAT_P1P1
+            elif name == "WW":
+                cd = sp.cell_dofs_W
+                pat = Pattern(self, sp.ndofs_W, cd, cd)
+                which = L.PAT_WW
+                self.cell_dofs_W = self.upload(cd)
+                self.check(self.lib.nsb_set_mixed_dofmap(self.ctx, sp.ndofs_W, _ptr(self.cell_dofs_W)))
+            else:
+                raise KeyError(name)
+            self.check(self.lib.nsb_set_pattern(self.ctx, which, pat.nrows, _ptr(pat.rowptr), _ptr(pat.col),
+                                                _ptr(pat.pair_ptr), _ptr(pat.pair_cell), _ptr(pat.pair_iloc),
+                                                _ptr(pat.pair_slots)))
+            self.patterns[name] = pat
+        return self.patterns[name]
+
+    def matrix(self, pattern, vals, kind, bs, bc_mask=None):
+        """nsb_matrix descriptor (keeps the tensors alive through attributes)."""
+        pat = self.patterns[pattern]
+        m = L.Matrix(kind, bs, pat.nrows, pat.nnz, pat.rowptr.data_ptr(), pat.col.data_ptr(), vals.data_ptr(),
+                     bc_mask.data_ptr() if bc_mask is not None else None)
+        m._keep = (pat, vals, bc_mask)
+        return m
+
+    # ---- coefficients -----------------------------------------------------------------------
+    def set_coefficients(self, k, alpha, c_conv=1.0, c_p=1.0, c_visc=1.0, c_body=1.0):
+        arr = (C.c_double * 8)(k, alpha[0], alpha[1], alpha[2], c_conv, c_p, c_visc, c_body)
+        self.check(self.lib.nsb_set_coefficients(self.ctx, arr))
+        self.coef = tuple(arr)
+
+    # ---- assembly ---------------------------------------------------------------------------
+    def assemble_ipcs_momentum(self, flags, ustar, un=None, unm1=None, pn=None, b=None, A=None):
+        self.launches += bin(flags & 3).count("1")
+        self.check(self.lib.nsb_assemble_ipcs_momentum(self.ctx, flags, _ptr(ustar), _ptr(un), _ptr(unm1),
+                                                       _ptr(pn), _ptr(b), _ptr(A), self.stream))
+
+    def assemble_poisson(self, flags, pn=None, ustar=None, b=None, A=None):
+        self.launches += bin(flags & 3).count("1")
+        self.check(self.lib.nsb_assemble_poisson(self.ctx, flags, _ptr(pn), _ptr(ustar), _ptr(b), _ptr(A),
+                                                 self.stream))
+
+    def assemble_correction(self, flags, ustar=None, pnew=None, pold=None, b=None, A=None):
+        self.launches += bin(flags & 3).count("1")
+        self.check(self.lib.nsb_assemble_correction(self.ctx, flags, _ptr(ustar), _ptr(pnew), _ptr(pold),
+                                                    _ptr(b), _ptr(A), self.stream))
+
+    def assemble_p1_mass(self, flags, w=None, A=None):
+        self.launches += bin(flags & 3).count("1")
+        self.check(self.lib.nsb_assemble_p1_mass(self.ctx, flags, _ptr(w), _ptr(A), self.stream))
+
+    def assemble_mixed(self, flags, w0, w1=None, w2=None, b=None, A=None):
+        self.launches += 1
+        self.check(self.lib.nsb_assemble_mixed(self.ctx, flags, _ptr(w0), _ptr(w1), _ptr(w2), _ptr(b), _ptr(A),
+                                               self.stream))
+
+    def set_mixed_bc(self, mask, g):
+        self._mixed_bc = (mask, g)
+        self.check(self.lib.nsb_set_mixed_bc(self.ctx, _ptr(mask), _ptr(g)))
+
+    # ---- Dirichlet rows ---------------------------------------------------------------------
+    def bc_apply_matrix(self, pattern, vals, kind, bs, bc_dofs):
+        if bc_dofs.numel() == 0:
+            return
+        pat = self.patterns[pattern]
+        self.launches += 1
+        self.check(self.lib.nsb_bc_apply_matrix(self.ctx, kind, bs, _ptr(pat.rowptr), _ptr(pat.col), _ptr(vals),
+                                                bc_dofs.numel(), _ptr(bc_dofs), self.stream))
+
+    def bc_apply_vector(self, mode, b, bc_dofs, bc_vals, x=None):
+        if bc_dofs.numel() == 0:
+            return
+        self.launches += 1
+        self.check(self.lib.nsb_bc_apply_vector(self.ctx, mode, _ptr(b), _ptr(x), bc_dofs.numel(), _ptr(bc_dofs),
+                                                _ptr(bc_vals), self.stream))
+
+    # ---- linear algebra ---------------------------------------------------------------------
+    def spmv(self, A, x, y):
+        self.launches += 1
+        self.check(self.lib.nsb_spmv(self.ctx, C.byref(A), _ptr(x), _ptr(y), self.stream))
+
+    def inv_diagonal(self, A, out):
+        self.launches += 1
+        self.check(self.lib.nsb_inv_diagonal(self.ctx, C.byref(A), _ptr(out), self.stream))
+
+    def cg(self, A, inv_diag, b, x, rtol=1e-12, atol=0.0, maxit=10000, nullspace=False, work=None):
+        n = A.nrows * A.bs
+        if work is None or work.numel() < 4 * n:
+            work = self.empty(self.lib.nsb_cg_workspace_doubles(n))
+        it, res = C.c_int32(), C.c_double()
+        st = self.lib.nsb_cg(self.ctx, C.byref(A), _ptr(inv_diag), _ptr(b), _ptr(x), rtol, atol, maxit,
+                             1 if nullspace else 0, _ptr(work), C.byref(it), C.byref(res), self.stream)
+        self.launches += 4 + 4 * it.value
+        self.check(st)
+        return it.value, res.value
+
+    def gmres(self, A, inv_diag, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None):
+        n = A.nrows * A.bs
+        need = self.lib.nsb_gmres_workspace_doubles(n, restart)
+        if work is None or work.numel() < need:
+            work = self.empty(need)
+        it, res = C.c_int32(), C.c_double()
+        st = self.lib.nsb_gmres(self.ctx, C.byref(A), _ptr(inv_diag), _ptr(b), _ptr(x), rtol, atol, maxit, restart,
+                                _ptr(work), C.byref(it), C.byref(res), self.stream)
+        self.launches += 4 + 8 * it.value
+        self.check(st)
+        return it.value, res.value
+
+    def copy(self, x, y):
+        self.check(self.lib.nsb_vec_copy(self.ctx, x.numel(), _ptr(x), _ptr(y), self.stream))
+
+    def axpy(self, a, x, y):
+        self.launches += 1
+        self.check(self.lib.nsb_vec_axpy(self.ctx, x.numel(), float(a), _ptr(x), _ptr(y), self.stream))
+
+    def scale(self, a, x):
+        self.launches += 1
+        self.check(self.lib.nsb_vec_scale(self.ctx, x.numel(), float(a), _ptr(x), self.stream))
+
+    def dot(self, x, y):
+        out = C.c_double()
+        self.launches += 1
+        self.check(self.lib.nsb_vec_dot(self.ctx, x.numel(), _ptr(x), _ptr(y), C.byref(out), self.stream))
+        return out.value
+
+    def norm(self, x):
+        return float(np.sqrt(self.dot(x, x)))
+
+    def sum(self, x):
+        out = C.c_double()
+        self.launches += 1
+        self.check(self.lib.nsb_vec_sum(self.ctx, x.numel(), _ptr(x), C.byref(out), self.stream))
+        return out.value
+
+    def scatter(self, idx, x, y):
+        self.launches += 1
+        self.check(self.lib.nsb_vec_scatter(self.ctx, idx.numel(), _ptr(idx), _ptr(x), _ptr(y), self.stream))
+
+    def gather(self, idx, x, y):
+        self.launches += 1
+        self.check(self.lib.nsb_vec_gather(self.ctx, idx.numel(), _ptr(idx), _ptr(x), _ptr(y), self.stream))
+
+    def ipcs_advance(self, u0, u1, u2, p, p_old):
+        self.launches += 1
+        self.check(self.lib.nsb_ipcs_advance(self.ctx, u0.numel(), _ptr(u0), _ptr(u1), _ptr(u2), p.numel(), _ptr(p),
+                                             _ptr(p_old), self.stream))
+
+    def fp64_peak(self):
+        out = C.c_double()
+        self.check(self.lib.nsb_fp64_peak(self.ctx, C.byref(out)))
+        return out.value

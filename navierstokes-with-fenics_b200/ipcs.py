@@ -1,0 +1,227 @@
+"""IPCSSolver: mirror of ``source/ns_ipcs_solver.py`` whose per-step work (assembly of the
+three sub-steps, Dirichlet rows, the linear solves, the history shift) runs in libnsb200.so.
+
+Same constructor arguments, ``set_boundary_conditions`` / ``set_equation_coefficients`` /
+``set_initial_conditions`` / ``solve`` / ``advance_time`` / ``solution`` as the reference class.
+Differences forced by replacing LU: Krylov tolerances ``linear_rtol`` and the
+zero-mean representative for the all-Neumann pressure problem (H4).
+"""
+import numpy as np
+import torch
+
+from . import _lib as L
+from .device import Device
+from .solver_base import SolverBase, Expression, NewtonNotConverged, newton_converged
+
+
+class IPCSSolver(SolverBase):
+    def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
+                 device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True):
+        super().__init__(mesh, boundary_markers, form_convective_term)
+        assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
+        assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
+        self._time_stepping = time_stepping
+        self._tol, self._maxiter = tol, max_iter
+        self._linear_rtol, self._restart = linear_rtol, gmres_restart
+        self._cache = cache_constant_matrices
+        self.dev = dev = Device(mesh, device_index)
+        sp = dev.spaces
+        nV, nQ = sp.ndofs_V, sp.ndofs_Q
+        # fields (source/ns_ipcs_solver.py:66-82)
+        self._velocities = [dev.zeros(nV) for _ in range(time_stepping.n_levels() + 1)]
+        while len(self._velocities) < 3:
+            self._velocities.append(dev.zeros(nV))
+        self._intermediate_velocity = dev.zeros(nV)
+        self._pressure, self._old_pressure = dev.zeros(nQ), dev.zeros(nQ)
+        # work space
+        p22, p11 = dev.patterns["P2P2"], dev.patterns["P1P1"]
+        d = sp.dim
+        self._A_mom = dev.empty(p22.nnz * d * d)
+        self._A_mass = dev.empty(p22.nnz)
+        self._A_lap = dev.empty(p11.nnz)
+        self._bV, self._dxV, self._dinvV = dev.empty(nV), dev.empty(nV), dev.empty(nV)
+        self._dinv_mass = dev.empty(nV)
+        self._bQ, self._dinvQ = dev.empty(nQ), dev.empty(nQ)
+        self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nV, gmres_restart),
+                                   dev.lib.nsb_cg_workspace_doubles(nV)))
+        self._have_constant = False
+        self._bc_ready = False
+        self.newton_iterations, self.krylov_iterations = [], []
+        self._alpha, self._next_step_size = None, None
+
+    # ---- BC tables on the device --------------------------------------------------------------
+    def _setup_boundary_conditions(self):
+        """source/ns_ipcs_solver.py:45-64: velocity BCs on V, pressure BCs on Q."""
+        dev, sp = self.dev, self.dev.spaces
+        vd, vv = sp.dirichlet_table(self._velocity_bcs, "V")
+        pd, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
+        assert len(vd) + len(pd) > 0
+        self._vbc_dofs, self._vbc_vals = dev.upload(vd), dev.upload(vv)
+        self._pbc_dofs, self._pbc_vals = dev.upload(pd), dev.upload(pv)
+        mV = np.zeros(sp.ndofs_V, dtype=np.uint8)
+        mV[vd] = 1
+        mQ = np.zeros(sp.ndofs_Q, dtype=np.uint8)
+        mQ[pd] = 1
+        self._maskV, self._maskQ = dev.upload(mV), dev.upload(mQ)
+        self._time_dependent_bcs = any(isinstance(v, Expression) for _, _, v in
+                                       self._velocity_bcs + self._pressure_bcs)
+        self._bc_ready = True
+        self._have_constant = False
+
+    def _update_bc_values(self):
+        """time-dependent Dirichlet data: re-evaluate on the host, upload the values (H11)."""
+        if not self._time_dependent_bcs:
+            return
+        sp = self.dev.spaces
+        _, vv = sp.dirichlet_table(self._velocity_bcs, "V")
+        self._vbc_vals.copy_(torch.from_numpy(vv))
+        if self._pbc_dofs.numel():
+            _, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
+            self._pbc_vals.copy_(torch.from_numpy(pv))
+
+    # ---- constant operators (pressure stiffness, velocity mass), quirk Q8 ----------------------
+    def _assemble_constant(self):
+        dev, d = self.dev, self.dev.dim
+        dev.assemble_poisson(L.MAT, A=self._A_lap)
+        dev.assemble_correction(L.MAT, A=self._A_mass)
+        self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pbc_dofs.numel() else None)
+        self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
+        self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None)
+        dev.inv_diagonal(self._lap, self._dinvQ)
+        dev.inv_diagonal(self._mass, self._dinv_mass)
+        self._have_constant = True
+
+    def _update_time_stepping_coefficients(self):
+        """source/ns_ipcs_solver.py:210-227"""
+        ts = self._time_stepping
+        alpha = list(ts.coefficients(1))
+        while len(alpha) < 3:
+            alpha.append(0.0)
+        self._alpha, self._next_step_size = tuple(alpha), ts.get_next_step_size()
+        co = self._equation_coefficients
+        self.dev.set_coefficients(self._next_step_size, self._alpha, co["convective_term"], co["pressure_term"],
+                                  co["viscous_term"])
+
+    def set_initial_conditions(self, initial_conditions):
+        """source/ns_solver_base.py:1123-1171 + source/ns_ipcs_solver.py:229-238: nodal data of
+        degree <= 2 (velocity) / 1 (pressure), for which dolfin's L2 projection is the identity."""
+        assert isinstance(initial_conditions, dict) and "velocity" in initial_conditions
+        sp, dev = self.dev.spaces, self.dev
+        v = initial_conditions["velocity"]
+        x = sp.node_coordinates()
+        if callable(v):
+            u0 = np.asarray(v(x), dtype=np.float64).reshape(len(x), sp.dim)
+        else:
+            assert len(v) == sp.dim
+            u0 = np.broadcast_to(np.asarray(v, dtype=np.float64), (len(x), sp.dim))
+        u0 = dev.upload(np.ascontiguousarray(u0).reshape(-1))
+        self._velocities[0].copy_(u0)
+        self._velocities[1].copy_(u0)
+        if "pressure" in initial_conditions:
+            p = initial_conditions["pressure"]
+            xv = sp.mesh.coords
+            p0 = np.asarray(p(xv), dtype=np.float64).reshape(-1) if callable(p) else np.full(len(xv), float(p))
+            p0 = dev.upload(p0)
+            self._pressure.copy_(p0)
+            self._old_pressure.copy_(p0)
+
+    # ---- one time step -------------------------------------------------------------------------
+    def solve(self):
+        """``InstationarySolverBase.solve`` (source/ns_solver_base.py:1174-1203)"""
+        if not self._bc_ready:
+            self._setup_boundary_conditions()
+        self._set_time(self._time_stepping.next_time)
+        self._update_bc_values()
+        self._update_time_stepping_coefficients()
+        if not (self._have_constant and self._cache):
+            self._assemble_constant()
+        self._solve_time_step()
+
+    def _residual(self):
+        dev = self.dev
+        dev.assemble_ipcs_momentum(L.VEC, self._intermediate_velocity, self._velocities[1], self._velocities[2],
+                                   self._old_pressure, b=self._bV)
+        dev.bc_apply_vector(L.BC_NEWTON, self._bV, self._vbc_dofs, self._vbc_vals, x=self._intermediate_velocity)
+        return dev.norm(self._bV)
+
+    def _solve_time_step(self):
+        """source/ns_ipcs_solver.py:198-208"""
+        dev, d = self.dev, self.dev.dim
+        ustar = self._intermediate_velocity
+        # (1) tentative velocity: dolfin NewtonSolver semantics (atol = tol, rtol = 10 tol)
+        atol, rtol = self._tol, 10.0 * self._tol
+        r0 = r = self._residual()
+        it, kry = 0, []
+        converged = newton_converged(r, r0, atol, rtol)
+        while not converged and it < self._maxiter:
+            dev.assemble_ipcs_momentum(L.MAT, ustar, A=self._A_mom)
+            dev.bc_apply_matrix("P2P2", self._A_mom, L.BSR, d, self._vbc_dofs)
+            dev.inv_diagonal(self._jac, self._dinvV)
+            self._dxV.zero_()
+            n_it, _ = dev.gmres(self._jac, self._dinvV, self._bV, self._dxV, rtol=self._linear_rtol,
+                                restart=self._restart, work=self._work)
+            kry.append(n_it)
+            dev.axpy(-1.0, self._dxV, ustar)
+            r = self._residual()
+            it += 1
+            converged = newton_converged(r, r0, atol, rtol)
+        self.newton_iterations.append(it)
+        self.newton_residual = r
+        if not converged:
+            raise NewtonNotConverged("Newton solver did not converge (%d iterations, residual %g)" % (it, r))
+        # (2) pressure Poisson
+        a0 = self._alpha[0]
+        dev.assemble_poisson(L.VEC, pn=self._old_pressure, ustar=ustar, b=self._bQ)
+        if self._pbc_dofs.numel():
+            dev.bc_apply_vector(L.BC_LINEAR, self._bQ, self._pbc_dofs, self._pbc_vals)
+            dev.bc_apply_vector(L.BC_LINEAR, self._pressure, self._pbc_dofs, self._pbc_vals)
+            n_p, _ = dev.cg(self._lap, self._dinvQ, self._bQ, self._pressure, rtol=self._linear_rtol, work=self._work)
+        else:
+            n_p, _ = dev.cg(self._lap, self._dinvQ, self._bQ, self._pressure, rtol=self._linear_rtol,
+                            nullspace=True, work=self._work)
+        # (3) velocity correction
+        dev.assemble_correction(L.VEC, ustar=ustar, pnew=self._pressure, pold=self._old_pressure, b=self._bV)
+        dev.bc_apply_vector(L.BC_LINEAR, self._bV, self._vbc_dofs, self._vbc_vals)
+        dev.copy(ustar, self._velocities[0])
+        dev.bc_apply_vector(L.BC_LINEAR, self._velocities[0], self._vbc_dofs, self._vbc_vals)
+        n_c, _ = dev.cg(self._mass, self._dinv_mass, self._bV, self._velocities[0], rtol=self._linear_rtol,
+                        work=self._work)
+        self.krylov_iterations.append(dict(momentum=kry, pressure=n_p, correction=n_c))
+        del a0
+
+    def advance_time(self):
+        """``_advance_solution`` source/ns_ipcs_solver.py:35-43"""
+        self.dev.ipcs_advance(self._velocities[0], self._velocities[1], self._velocities[2], self._pressure,
+                              self._old_pressure)
+
+    # ---- output ---------------------------------------------------------------------------------
+    @property
+    def velocity(self):
+        return self._velocities[0]
+
+    @property
+    def pressure(self):
+        return self._pressure
+
+    @property
+    def solution(self):
+        """mixed-space vector (source/ns_ipcs_solver.py:240-247), with the mean-pressure shift
+        of source/ns_solver_base.py:1190-1203 applied to the copy when requested."""
+        dev, sp = self.dev, self.dev.spaces
+        if not hasattr(self, "_w"):
+            self._w = dev.zeros(sp.ndofs_W)
+            self._v2w, self._q2w = dev.upload(sp.V_to_W()), dev.upload(sp.Q_to_W())
+        dev.scatter(self._v2w, self._velocities[0], self._w)
+        dev.scatter(self._q2w, self._pressure, self._w)
+        if hasattr(self, "_mean_pressure_value"):
+            shift = self.mean_pressure() - self._mean_pressure_value
+            self._w[sp.dim * sp.n_nodes:] -= shift
+        return self._w
+
+    def mean_pressure(self):
+        dev = self.dev
+        if not hasattr(self, "_p1_weights"):
+            self._p1_weights = dev.empty(dev.spaces.ndofs_Q)
+            dev.assemble_p1_mass(L.VEC, w=self._p1_weights)
+            self._volume = dev.sum(self._p1_weights)
+        return dev.dot(self._p1_weights, self._pressure) / self._volume

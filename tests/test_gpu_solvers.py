@@ -1,0 +1,235 @@
+"""GPU parity of the linear-algebra / Dirichlet kernels and of whole IPCS time steps against the
+CPU oracle (sparse direct LU, dolfin Newton/BC semantics).  Field tolerance 1e-8 relative
+(north star), matrix/vector entries 1e-12."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+from helpers import meshes, random_fields, rel_max_err, bsr_to_csr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", params=[0, 1], ids=["2d", "3d"])
+def case(request, built_library):
+    import oracle
+    from nsb200.device import Device
+    name, m, om = meshes()[request.param]
+    dev = Device(m)
+    dev.set_coefficients(1e-2, (1.5, -2.0, 0.5), 1.0, 1.0, 0.02)
+    return dict(dev=dev, om=om, d=m.dim, fields=random_fields(dev.spaces))
+
+
+def up(dev, a):
+    return dev.upload(np.ascontiguousarray(a))
+
+
+def test_spmv_bsr_csr_and_mask(case):
+    import nsb200._lib as L
+    dev, d = case["dev"], case["d"]
+    rng = np.random.default_rng(2025)
+    p22, p11 = dev.patterns["P2P2"], dev.patterns["P1P1"]
+    # BSR
+    vals = rng.uniform(-1, 1, p22.nnz * d * d)
+    x = rng.uniform(-1, 1, p22.nrows * d)
+    dv, dx, dy = up(dev, vals), up(dev, x), dev.empty(len(x))
+    dev.spmv(dev.matrix("P2P2", dv, L.BSR, d), dx, dy)
+    ref = bsr_to_csr(p22.rowptr_host, p22.col_host, vals, d) @ x
+    assert rel_max_err(dy.cpu().numpy(), ref) < 1e-13
+    # Kronecker CSR with identity rows on masked dofs
+    vals = rng.uniform(-1, 1, p22.nnz)
+    mask = (rng.uniform(size=len(x)) < 0.2).astype(np.uint8)
+    dv, dm = up(dev, vals), up(dev, mask)
+    dev.spmv(dev.matrix("P2P2", dv, L.CSR, d, dm), dx, dy)
+    n = p22.nrows
+    K = sp.kron(sp.csr_matrix((vals, p22.col_host, p22.rowptr_host), shape=(n, n)), sp.identity(d), format="csr")
+    ref = np.where(mask == 1, x, K @ x)
+    assert rel_max_err(dy.cpu().numpy(), ref) < 1e-13
+    # scalar CSR (short rows)
+    vals = rng.uniform(-1, 1, p11.nnz)
+    xq = rng.uniform(-1, 1, p11.nrows)
+    dv, dxq, dyq = up(dev, vals), up(dev, xq), dev.empty(len(xq))
+    dev.spmv(dev.matrix("P1P1", dv, L.CSR, 1), dxq, dyq)
+    ref = sp.csr_matrix((vals, p11.col_host, p11.rowptr_host), shape=(len(xq), len(xq))) @ xq
+    assert rel_max_err(dyq.cpu().numpy(), ref) < 1e-13
+
+
+def test_vector_kernels(case):
+    dev = case["dev"]
+    rng = np.random.default_rng(3)
+    n = 10007
+    x, y = rng.uniform(-1, 1, n), rng.uniform(-1, 1, n)
+    dx, dy = up(dev, x), up(dev, y)
+    assert abs(dev.dot(dx, dy) - x @ y) < 1e-12
+    assert abs(dev.sum(dx) - x.sum()) < 1e-12
+    dev.axpy(0.5, dx, dy)
+    assert np.allclose(dy.cpu().numpy(), y + 0.5 * x, rtol=0, atol=1e-15)
+    idx = rng.permutation(n).astype(np.int32)
+    dz = dev.zeros(n)
+    dev.scatter(up(dev, idx), dx, dz)
+    z = np.zeros(n)
+    z[idx] = x
+    assert np.array_equal(dz.cpu().numpy(), z)
+    dev.gather(up(dev, idx), dz, dy)
+    assert np.array_equal(dy.cpu().numpy(), x)
+    u0, u1, u2 = up(dev, x), up(dev, y), dev.zeros(n)
+    p, po = up(dev, x[:100]), dev.zeros(100)
+    dev.ipcs_advance(u0, u1, u2, p, po)
+    assert np.array_equal(u2.cpu().numpy(), y) and np.array_equal(u1.cpu().numpy(), x)
+    assert np.array_equal(po.cpu().numpy(), x[:100])
+
+
+def test_dirichlet_rows(case):
+    """K9 against the oracle's restatement of DirichletBC.apply."""
+    import nsb200._lib as L
+    import oracle
+    dev, d = case["dev"], case["d"]
+    rng = np.random.default_rng(5)
+    pat = dev.patterns["P2P2"]
+    vals = rng.uniform(-1, 1, pat.nnz * d * d)
+    dofs, g = dev.spaces.dirichlet_table([(1, None, (0.0,) * d), (4, 0, 1.0)], "V")
+    dv = up(dev, vals)
+    dev.bc_apply_matrix("P2P2", dv, L.BSR, d, up(dev, dofs))
+    ref = oracle.bc.apply_ident(bsr_to_csr(pat.rowptr_host, pat.col_host, vals, d), dofs)
+    got = bsr_to_csr(pat.rowptr_host, pat.col_host, dv.cpu().numpy(), d)
+    assert (got != ref).nnz == 0
+    b, x = rng.uniform(-1, 1, pat.nrows * d), rng.uniform(-1, 1, pat.nrows * d)
+    db = up(dev, b)
+    dev.bc_apply_vector(L.BC_NEWTON, db, up(dev, dofs), up(dev, g), x=up(dev, x))
+    assert np.array_equal(db.cpu().numpy(), oracle.bc.apply_rhs_newton(b, x, dofs, g))
+    db = up(dev, b)
+    dev.bc_apply_vector(L.BC_LINEAR, db, up(dev, dofs), up(dev, g))
+    assert np.array_equal(db.cpu().numpy(), oracle.bc.apply_rhs_linear(b, dofs, g))
+    # scalar CSR rows
+    p11 = dev.patterns["P1P1"]
+    vals = rng.uniform(-1, 1, p11.nnz)
+    pd, _ = dev.spaces.dirichlet_table([(2, "p", 0.0)], "Q")
+    dv = up(dev, vals)
+    dev.bc_apply_matrix("P1P1", dv, L.CSR, 1, up(dev, pd))
+    n = p11.nrows
+    ref = oracle.bc.apply_ident(sp.csr_matrix((vals, p11.col_host, p11.rowptr_host), shape=(n, n)), pd)
+    assert np.array_equal(dv.cpu().numpy(), ref.data)
+
+
+def test_cg_poisson_dirichlet_and_nullspace(case):
+    import nsb200._lib as L
+    dev = case["dev"]
+    pat = dev.patterns["P1P1"]
+    n = pat.nrows
+    A = dev.empty(pat.nnz)
+    dev.assemble_poisson(L.MAT, A=A)
+    Ah = sp.csr_matrix((A.cpu().numpy(), pat.col_host, pat.rowptr_host), shape=(n, n))
+    rng = np.random.default_rng(11)
+    # (a) Dirichlet rows through the mask
+    pd, pg = dev.spaces.dirichlet_table([(2, "p", 0.7)], "Q")
+    mask = np.zeros(n, dtype=np.uint8)
+    mask[pd] = 1
+    b = rng.uniform(-1, 1, n)
+    b[pd] = pg
+    mat = dev.matrix("P1P1", A, L.CSR, 1, up(dev, mask))
+    dinv = dev.empty(n)
+    dev.inv_diagonal(mat, dinv)
+    x0 = np.zeros(n)
+    x0[pd] = pg
+    x = up(dev, x0)
+    its, res = dev.cg(mat, dinv, up(dev, b), x, rtol=1e-13)
+    import oracle
+    ref = spla.spsolve(oracle.bc.apply_ident(Ah, pd).tocsc(), b)
+    assert rel_max_err(x.cpu().numpy(), ref) < 1e-9
+    # (b) singular all-Neumann problem, consistent after mean removal, zero-mean solution
+    mat = dev.matrix("P1P1", A, L.CSR, 1)
+    dev.inv_diagonal(mat, dinv)
+    b = Ah @ rng.uniform(-1, 1, n)
+    x = dev.zeros(n)
+    its, res = dev.cg(mat, dinv, up(dev, b), x, rtol=1e-13, nullspace=True)
+    ref = oracle.solvers.solve_singular_mean_zero(Ah, b - b.mean())
+    assert abs(x.cpu().numpy().mean()) < 1e-12
+    assert rel_max_err(x.cpu().numpy(), ref) < 1e-8
+
+
+def test_gmres_momentum_system(case):
+    import nsb200._lib as L
+    import oracle
+    dev, d = case["dev"], case["d"]
+    us = case["fields"][0]
+    pat = dev.patterns["P2P2"]
+    A = dev.empty(pat.nnz * d * d)
+    dev.assemble_ipcs_momentum(L.MAT, up(dev, us), A=A)
+    dofs, _ = dev.spaces.dirichlet_table([(1, None, (0.0,) * d), (3, None, (0.0,) * d)], "V")
+    dev.bc_apply_matrix("P2P2", A, L.BSR, d, up(dev, dofs))
+    mat = dev.matrix("P2P2", A, L.BSR, d)
+    n = pat.nrows * d
+    dinv = dev.empty(n)
+    dev.inv_diagonal(mat, dinv)
+    rng = np.random.default_rng(13)
+    b = rng.uniform(-1, 1, n)
+    x = dev.zeros(n)
+    for restart in (40, 7):          # also exercise restarts
+        x.zero_()
+        its, res = dev.gmres(mat, dinv, up(dev, b), x, rtol=1e-13, restart=restart, maxit=5000)
+        ref = spla.spsolve(bsr_to_csr(pat.rowptr_host, pat.col_host, A.cpu().numpy(), d).tocsc(), b)
+        assert rel_max_err(x.cpu().numpy(), ref) < 1e-9
+
+
+def _channel_bcs(d):
+    import nsb200
+    V, P = nsb200.VelocityBCType, nsb200.PressureBCType
+
+    def inflow(x, t):
+        u = np.zeros((len(x), d))
+        u[:, 0] = 6.0 * x[:, 1] * (1.0 - x[:, 1]) * (1.0 + 0.5 * np.sin(np.pi * t))
+        return u
+    return inflow, V, P
+
+
+@pytest.mark.parametrize("flow", ["channel", "cavity"])
+def test_ipcs_steps_match_oracle(case, flow):
+    """3 IPCS/BDF-2 steps (start-up BDF-1 included) against the LU-based oracle on the same mesh:
+    velocity and pressure to 1e-8 relative, identical Newton iteration counts."""
+    import nsb200
+    import oracle
+    d, om = case["d"], case["om"]
+    m = case["dev"].mesh
+    Re, dt, nsteps = 50.0, 0.01, 3
+    inflow, V, P = _channel_bcs(d)
+    expr = nsb200.Expression(inflow)
+    if flow == "channel":
+        bcs = [(V.function, 1, expr), (V.no_slip, 3, None), (V.no_slip, 4, None), (P.constant, 2, 0.0)]
+        o_vel = [(1, None, inflow), (3, None, (0.0,) * d), (4, None, (0.0,) * d)]
+        o_prs = [(2, 0.0)]
+        if d == 3:
+            bcs += [(V.no_slip, 5, None), (V.no_slip, 6, None)]
+            o_vel += [(5, None, (0.0,) * d), (6, None, (0.0,) * d)]
+    else:
+        lid = (1.0,) + (0.0,) * (d - 1)
+        walls = [1, 2, 3] + ([5, 6] if d == 3 else [])
+        bcs = [(V.no_slip, w, None) for w in walls] + [(V.constant, 4, lid)]
+        o_vel = [(w, None, (0.0,) * d) for w in walls] + [(4, None, lid)]
+        o_prs = []
+    ts = nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=dt)
+    solver = nsb200.IPCSSolver(m, m.bfacet_marker, "standard", ts, tol=1e-10, max_iter=50)
+    solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / Re))
+    solver.set_boundary_conditions(bcs)
+    orc = oracle.solvers.IPCSOracle(om, Re, o_vel, o_prs, tol=1e-10, max_iter=50)
+    ots = nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=dt)
+    for step in range(nsteps):
+        ts.update_coefficients()
+        solver.solve()
+        ots.update_coefficients()
+        a = list(ots.coefficients(1)) + [0.0]
+        orc.solve(tuple(a[:3]), ots.get_next_step_size(), ots.next_time)
+        u, p = solver.velocity.cpu().numpy(), solver.pressure.cpu().numpy()
+        assert rel_max_err(u, orc.velocities[0]) < 1e-8, "velocity, step %d" % step
+        if flow == "cavity":      # pressure up to a constant (H4): both carry the zero-mean representative
+            assert rel_max_err(p - p.mean(), orc.pressure - orc.pressure.mean()) < 1e-7
+        else:
+            assert rel_max_err(p, orc.pressure) < 1e-8, "pressure, step %d" % step
+        assert solver.newton_iterations[-1] == orc.newton_iterations[-1]
+        ts.advance_time()
+        solver.advance_time()
+        ots.advance_time()
+        orc.advance_time()
+    w = solver.solution.cpu().numpy()
+    sp_ = orc.sp
+    assert np.array_equal(w[sp_.V_to_W], solver.velocity.cpu().numpy())
