@@ -1,0 +1,301 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the nsb200 hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl nsb200|reference] [--n CELLS_PER_EDGE]
+
+Workload (BASELINE.json configs[4], SURVEY.md 8 "C5"): 3D lid-driven cavity, Re = 100, IPCS
+projection scheme with BDF-2, P2-P1 Taylor-Hood on the dolfin-style 73^3 x 6 tetrahedral unit
+cube (9 934 793 DOF), dt = 1e-2, lid (1,0,0) on y = 1, no-slip elsewhere, start from rest.  One
+"step" is one full IPCS time step: Newton on the tentative velocity (residual + Jacobian
+assembly, Dirichlet rows, Jacobi-GMRES), pressure Poisson (rhs assembly, Jacobi-CG), velocity
+correction (rhs assembly, Jacobi-CG on the mass matrix) and the BDF history shift.
+
+Prints ONE JSON line (rank 0).  `value` = time steps per second with every input resident in HBM;
+`e2e` = the same through the public solver API with the Dirichlet tables uploaded from pinned
+host memory and the mixed solution vector copied back to the host inside the timed region.
+`roofline` is for the kernel class with the largest share of the step, from CUDA-event pairs
+recorded by libnsb200 around every launch on the launching stream (nsb_timer_*).
+`cpu_baseline` / `--impl reference`: the CPU oracle (oracle/, plain C assembly + numpy Krylov,
+the "port" of the reference path -- FEniCS itself is unavailable on this box) on a bounded
+sample of the same workload, scaled to the metric's unit by the DOF ratio.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "time_steps_per_sec_ipcs_3d_cavity"
+UNIT = "steps/s"
+RE, DT = 100.0, 1.0e-2
+CPU_SAMPLE_N = 16          # 16^3 x 6 tets, 112 724 DOF: a few seconds of CPU work per step
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="nsb200", choices=["nsb200", "reference"])
+    ap.add_argument("--n", type=int, default=73, help="cells per edge of the unit cube (73 -> 9.93 M DOF)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def mixed_dofs(n):
+    """3 (2n+1)^3 + (n+1)^3"""
+    return 3 * (2 * n + 1) ** 3 + (n + 1) ** 3
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle on a bounded sample
+# ---------------------------------------------------------------------------------------------
+def cpu_oracle_steps(n, steps, warmup):
+    """Time `steps` IPCS steps of the CPU oracle (C assembly with all host threads, Jacobi
+    GMRES/CG in numpy) on the n^3 cavity.  Returns (seconds per step, threads)."""
+    import oracle
+    om = oracle.mesh.hyper_rectangle((0.0, 0.0, 0.0), (1.0, 1.0, 1.0), (n, n, n))
+    vel = [(w, None, (0.0, 0.0, 0.0)) for w in (1, 2, 3, 5, 6)] + [(4, None, (1.0, 0.0, 0.0))]
+    orc = oracle.solvers.IPCSOracle(om, RE, vel, [], assembler="c")
+    orc.linear_solver = "krylov"
+    t, times = 0.0, []
+    for s in range(warmup + steps):
+        alpha = (1.0, -1.0, 0.0) if s == 0 else (1.5, -2.0, 0.5)
+        t += DT
+        t0 = time.perf_counter()
+        orc.solve(alpha, DT, t)
+        orc.advance_time()
+        el = time.perf_counter() - t0
+        if s >= warmup:
+            times.append(el)
+    return sum(times) / len(times), orc.asm.threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sec, threads = cpu_oracle_steps(CPU_SAMPLE_N, args.steps, min(args.warmup, 1))
+    scale = mixed_dofs(CPU_SAMPLE_N) / mixed_dofs(args.n)
+    value = scale / sec
+    sample = ("IPCS step on the %d^3 x 6 cavity (%d DOF), C assembly on %d OpenMP threads + numpy Jacobi-GMRES/CG "
+              "(rtol 1e-12); steps/s scaled by the DOF ratio %.4g to the %d^3 workload (linear-cost assumption, "
+              "favours the CPU)" % (CPU_SAMPLE_N, mixed_dofs(CPU_SAMPLE_N), threads, scale, args.n))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 / value,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.n, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "FEniCS/PETSc (the reference's own CPU path) is not installable on this box; kind=port is the "
+                "CPU oracle restating it (oracle/c/nsoracle.c + oracle/krylov.py)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n, gpus):
+    return {"workload": "C5 3D lid-driven cavity IPCS/BDF-2, P2-P1 on %d^3x6 tets (%d DOF), Re=100, dt=1e-2"
+                        % (n, mixed_dofs(n)),
+            "cells_per_edge": n, "mixed_dofs": mixed_dofs(n),
+            "parallelism": "1 GPU" if gpus == 1 else "%d independent replicas (mesh-partitioned path: see DESIGN.md)" % gpus,
+            "l2_policy": "inputs larger than L2 (Jacobian 6.5 GB, Krylov basis 3.3 GB per GPU at n=73)",
+            "linear_solvers": "Jacobi-GMRES(40) rtol 1e-12 (velocity), Jacobi-CG rtol 1e-12 (pressure, mass)"}
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed region through NVML
+# ---------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.sm_max = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        while not self.stop_flag and self.nv is not None:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) \
+                    if hasattr(self.nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def result(self):
+        self.stop_flag = True
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def algorithmic_bytes(n):
+    """ALGORITHMIC bytes per launch of each kernel class at the n^3 cavity (stated
+    in DESIGN.md): FP64 values, int32 indices, every value / vector entry moved once."""
+    nverts = (n + 1) ** 3
+    ncells = 6 * n ** 3
+    nnodes = (2 * n + 1) ** 3
+    nnz22 = 230 * n ** 3 + 138 * n ** 2 + 24 * n + 1          # scalar P2 x P2 pattern (App. C)
+    nnz11 = 15 * n ** 3 + 21 * n ** 2 + 9 * n + 1
+    nV, nQ = 3 * nnodes, nverts
+    geo = 8 * 3 * nverts + 4 * 4 * ncells + 4 * 10 * ncells    # coords + cell->vertex + cell->node maps
+    return {
+        "spmv_bsr": 8 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,
+        "spmv_csr": None,                                       # two different matrices share the class
+        "asm_jacobian": 8 * 9 * nnz22 + geo + 8 * nV,
+        "asm_residual": 8 * nV + geo + 8 * (3 * nV + nQ),
+    }, dict(nV=nV, nQ=nQ, nnz22=nnz22, nnz11=nnz11)
+
+
+def run_nsb200(args):
+    import torch
+    import __graft_entry__
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl nsb200 needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if local == 0:
+        __graft_entry__.build()
+    if world > 1:
+        dist.barrier()
+    import nsb200
+    V = nsb200.VelocityBCType
+    n = args.n
+    mesh, markers = nsb200.hyper_cube(3, n)
+    ts = nsb200.BDFTimeStepping(0.0, 1.0e6, order=2, desired_start_time_step=DT)
+    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=local)
+    solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / RE))
+    solver.set_boundary_conditions([(V.no_slip, w, None) for w in (1, 2, 3, 5, 6)] + [(V.constant, 4, (1.0, 0.0, 0.0))])
+    dev = solver.dev
+
+    def step(e2e=False):
+        ts.update_coefficients()
+        solver.solve(upload_bcs=e2e)
+        h2d = solver.h2d_bytes
+        d2h = 0
+        if e2e:
+            _, d2h = solver.fetch_solution()
+        ts.advance_time()
+        solver.advance_time()
+        return h2d, d2h
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(K, e2e):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        h2d = d2h = 0
+        for _ in range(K):
+            a, b = step(e2e)
+            h2d, d2h = a, b
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), h2d, d2h
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = dev.launch_count()
+    dev.timer_enable(True)
+    ms, _, _ = timed(args.steps, False)
+    classes = dev.timer_report()
+    dev.timer_enable(False)
+    launches = dev.launch_count() - l0
+    clocks = sampler.result()
+    ms_e2e, h2d, d2h = timed(args.steps, True)
+    if rank != 0:
+        return
+    K = args.steps
+    value = world * K / (ms * 1e-3)
+    e2e_value = world * K / (ms_e2e * 1e-3)
+    alg, sizes = algorithmic_bytes(n)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except (OSError, ValueError):
+        peaks = {}
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks \
+        else (6650.0, "fallback (B200_PROFILING.md)")
+    total_ms = sum(v[0] for v in classes.values())
+    breakdown = {k: {"ms_per_step": v[0] / K, "launch_groups_per_step": v[1] / K,
+                     "share_of_kernel_time": v[0] / total_ms if total_ms else None} for k, v in classes.items()}
+    dom = max((k for k in classes if alg.get(k)), key=lambda k: classes[k][0])
+    dur_ms = classes[dom][0] / max(classes[dom][1], 1)
+    achieved = alg[dom] / (dur_ms * 1e-3) / 1e9
+    roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg[dom], "avg_launch_ms": dur_ms,
+                "launches_timed": classes[dom][1]}
+    for k in ("asm_jacobian", "asm_residual", "spmv_bsr"):
+        if classes[k][1]:
+            d_ms = classes[k][0] / classes[k][1]
+            breakdown[k]["GB/s"] = alg[k] / (d_ms * 1e-3) / 1e9
+            breakdown[k]["frac_of_hbm_peak"] = breakdown[k]["GB/s"] / hbm_peak
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(n, world), "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches, "roofline": roofline, "breakdown": breakdown,
+        "newton_iterations": solver.newton_iterations[-K:], "krylov_iterations": solver.krylov_iterations[-1],
+        "assembly_gdof_per_s": {k: sizes["nV"] / (classes[k][0] / classes[k][1] * 1e-3) / 1e9
+                                for k in ("asm_jacobian", "asm_residual") if classes[k][1]},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        sec, threads = cpu_oracle_steps(CPU_SAMPLE_N, 2, 1)
+        scale = mixed_dofs(CPU_SAMPLE_N) / mixed_dofs(n)
+        line["cpu_baseline"] = {
+            "value": scale / sec, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "2 IPCS steps of the CPU oracle (C assembly, %d OpenMP threads; numpy Jacobi-GMRES/CG rtol 1e-12) "
+                      "on the %d^3 x 6 cavity (%d DOF, %.3f s/step), scaled by the DOF ratio %.4g"
+                      % (threads, CPU_SAMPLE_N, mixed_dofs(CPU_SAMPLE_N), sec, scale)}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_nsb200(args)
+
+
+if __name__ == "__main__":
+    main()

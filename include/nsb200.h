@@ -56,6 +56,18 @@ typedef struct nsb_pattern_builder nsb_pattern_builder;
 #define NSB_BC_LINEAR 0  /* b[i] = g[i]          LinearVariationalSolver  bc.apply(A,b)   */
 #define NSB_BC_NEWTON 1  /* b[i] = x[i] - g[i]   NonlinearVariationalSolver bc.apply(b,x) */
 
+/* kernel classes of the built-in CUDA-event timers (nsb_timer_report) */
+#define NSB_T_ASM_JAC 0      /* momentum / mixed Jacobian assembly (K2, K8)          */
+#define NSB_T_ASM_RES 1      /* momentum / mixed residual assembly (K1, K7)          */
+#define NSB_T_ASM_CONST 2    /* constant operators: P1 stiffness, P1/P2 mass (K3,K5) */
+#define NSB_T_ASM_RHS 3      /* Poisson and correction right-hand sides (K4, K6)     */
+#define NSB_T_SPMV_BSR 4     /* BSR-d SpMV (K10)                                     */
+#define NSB_T_SPMV_CSR 5     /* CSR / Kronecker-CSR SpMV (K10)                       */
+#define NSB_T_KRYLOV 6       /* Krylov vector kernels: fused updates, dots, Arnoldi (K11) */
+#define NSB_T_BC 7           /* Dirichlet rows (K9)                                  */
+#define NSB_T_VEC 8          /* vector ops, history shift, gather/scatter (K13, K15) */
+#define NSB_T_NCLASS 9
+
 typedef struct nsb_matrix {
     int32_t kind;            /* NSB_CSR | NSB_BSR                                        */
     int32_t bs;              /* components (CSR) or block size (BSR)                      */
@@ -172,6 +184,16 @@ int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x,
  * u2 <- u1 <- u0 ; p_old <- p */
 int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, double* u2,
                      int64_t nq, const double* p, double* p_old, void* stream);
+
+/* ---------------------------------------------------------------- instrumentation ------- */
+/* Per-kernel-class CUDA-event timing on the launching stream (SURVEY.md 8b nsb_timer_*).
+ * enable != 0 starts recording an event pair around every launch group of every class;
+ * nsb_timer_report synchronises the device, writes accumulated milliseconds and the number of
+ * timed regions per class (arrays of NSB_T_NCLASS; either may be NULL) and resets both. */
+int nsb_timer_enable(nsb_ctx* ctx, int32_t enable);
+int nsb_timer_report(nsb_ctx* ctx, double* ms_out, int64_t* regions_out);
+/* kernels launched by this context since creation (every class) */
+int nsb_launch_count(nsb_ctx* ctx, int64_t* count_out);
 
 /* measured FP64 FMA rate (TFLOP/s) of this device: roofline denominator for element kernels */
 int nsb_fp64_peak(nsb_ctx* ctx, double* tflops_out);

@@ -11,6 +11,8 @@ VEC, MAT, PICARD, BDF, SYMBC = 1, 2, 4, 8, 16
 PAT_P2P2, PAT_P1P1, PAT_WW = 0, 1, 2
 CSR, BSR = 0, 1
 BC_LINEAR, BC_NEWTON = 0, 1
+TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
+                 "krylov_vec", "dirichlet", "vector")
 
 c_i32p = C.POINTER(C.c_int32)
 c_u8p = C.POINTER(C.c_uint8)
@@ -64,6 +66,9 @@ PROTOTYPES = {
     "nsb_vec_gather": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp]),
     "nsb_ipcs_advance": (C.c_int, [vp, C.c_int64, vp, vp, vp, C.c_int64, vp, vp, vp]),
     "nsb_fp64_peak": (C.c_int, [vp, c_f64p]),
+    "nsb_timer_enable": (C.c_int, [vp, C.c_int32]),
+    "nsb_timer_report": (C.c_int, [vp, c_f64p, c_i64p]),
+    "nsb_launch_count": (C.c_int, [vp, c_i64p]),
 }
 
 _lib = None

@@ -673,6 +673,7 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
     const nsb_coef cf = ctx->coef;
     if (flags & NSB_VEC) {
         NSB_REQUIRE(ctx, ustar && un && unm1 && pn && b_out, "null vector argument");
+        NSB_TIMED(ctx, NSB_T_ASM_RES, st);
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_residual<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
                                                      ctx->cell_nodes, ustar, un, unm1, pn, cf, b_out)),
@@ -684,6 +685,7 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
         NSB_REQUIRE(ctx, ustar && A_out, "null matrix argument");
         const int newton = (flags & NSB_PICARD) ? 0 : 1;
         const double mc = cf.a0 / cf.k;
+        NSB_TIMED(ctx, NSB_T_ASM_JAC, st);
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_jacobian<2><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
                                                      P.pair_slots, ctx->coords, ctx->cell_nodes, ustar, mc,
@@ -705,6 +707,7 @@ extern "C" int nsb_assemble_poisson(nsb_ctx* ctx, int32_t flags, const double* p
     const int T = 128, B = nsb_blocks(P.nrows, T);
     if (flags & NSB_MAT) {
         NSB_REQUIRE(ctx, A_out, "null matrix argument");
+        NSB_TIMED(ctx, NSB_T_ASM_CONST, st);
         NSB_DIM_DISPATCH(ctx,
             (k_p1_matrix<2><<<B, T, 0, st>>>(P.nrows, 0, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
                                              P.pair_slots, ctx->coords, ctx->cell_verts, A_out)),
@@ -715,6 +718,7 @@ extern "C" int nsb_assemble_poisson(nsb_ctx* ctx, int32_t flags, const double* p
     if (flags & NSB_VEC) {
         NSB_REQUIRE(ctx, pn && ustar && b_out, "null vector argument");
         const double aok = ctx->coef.a0 / ctx->coef.k;
+        NSB_TIMED(ctx, NSB_T_ASM_RHS, st);
         NSB_DIM_DISPATCH(ctx,
             (k_poisson_rhs<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
                                                ctx->cell_nodes, pn, ustar, aok, b_out)),
@@ -735,6 +739,7 @@ extern "C" int nsb_assemble_correction(nsb_ctx* ctx, int32_t flags, const double
     const int T = 128, B = nsb_blocks(P.nrows, T);
     if (flags & NSB_MAT) {
         NSB_REQUIRE(ctx, A_out, "null matrix argument");
+        NSB_TIMED(ctx, NSB_T_ASM_CONST, st);
         NSB_DIM_DISPATCH(ctx,
             (k_p2_mass<2><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc, P.pair_slots,
                                            ctx->coords, ctx->cell_nodes, A_out)),
@@ -745,6 +750,7 @@ extern "C" int nsb_assemble_correction(nsb_ctx* ctx, int32_t flags, const double
     if (flags & NSB_VEC) {
         NSB_REQUIRE(ctx, ustar && pnew && pold && b_out, "null vector argument");
         const double koa = ctx->coef.k / ctx->coef.a0;
+        NSB_TIMED(ctx, NSB_T_ASM_RHS, st);
         NSB_DIM_DISPATCH(ctx,
             (k_correction_rhs<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
                                                   ctx->cell_nodes, ustar, pnew, pold, koa, b_out)),
@@ -763,6 +769,7 @@ extern "C" int nsb_assemble_p1_mass(nsb_ctx* ctx, int32_t flags, double* w_out, 
     const int T = 128, B = nsb_blocks(P.nrows, T);
     if (flags & NSB_MAT) {
         NSB_REQUIRE(ctx, A_out, "null matrix argument");
+        NSB_TIMED(ctx, NSB_T_ASM_CONST, st);
         NSB_DIM_DISPATCH(ctx,
             (k_p1_matrix<2><<<B, T, 0, st>>>(P.nrows, 1, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
                                              P.pair_slots, ctx->coords, ctx->cell_verts, A_out)),
@@ -772,6 +779,7 @@ extern "C" int nsb_assemble_p1_mass(nsb_ctx* ctx, int32_t flags, double* w_out, 
     }
     if (flags & NSB_VEC) {
         NSB_REQUIRE(ctx, w_out, "null vector argument");
+        NSB_TIMED(ctx, NSB_T_ASM_CONST, st);
         NSB_DIM_DISPATCH(ctx,
             (k_p1_weights<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
                                               ctx->cell_verts, w_out)),
@@ -795,6 +803,7 @@ extern "C" int nsb_assemble_mixed(nsb_ctx* ctx, int32_t flags, const double* w0,
     NSB_REQUIRE(ctx, !symbc || (ctx->w_bc_mask && ctx->w_bc_g), "symmetric BC elimination needs nsb_set_mixed_bc");
     cudaStream_t st = (cudaStream_t)stream;
     const int T = 128, B = nsb_blocks(P.nrows, T);
+    nsb_timed_region mixed_region(ctx, do_mat ? NSB_T_ASM_JAC : NSB_T_ASM_RES, st);
     NSB_DIM_DISPATCH(ctx,
         (k_mixed_rows<2><<<B, T, 0, st>>>(P.nrows, do_vec, do_mat, newton, bdf, symbc, P.rowptr, P.pair_ptr,
                                           P.pair_cell, P.pair_iloc, P.pair_slots, ctx->coords, ctx->cell_verts,

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
+#include <vector>
 #include "../../include/nsb200.h"
 
 #define NSB_MAX_PARTIALS 4096
@@ -21,6 +22,14 @@ struct nsb_pattern_dev {
 
 struct nsb_coef {
     double k, a0, a1, a2, c_conv, c_p, c_visc, c_body;
+};
+
+// kernel classes of the built-in CUDA-event timers (nsb_timer_*), see include/nsb200.h
+struct nsb_timer_class {
+    std::vector<cudaEvent_t> ev;   // start/stop pairs, recycled after every report
+    size_t used = 0;               // events in use (2 per timed region)
+    double ms = 0.0;               // accumulated device time since the last reset
+    int64_t regions = 0;           // timed regions since the last reset
 };
 
 struct nsb_ctx {
@@ -44,7 +53,39 @@ struct nsb_ctx {
     double* d_scalars = nullptr;      // [64] device-resident Krylov scalars
     unsigned int* d_counter = nullptr;
     double* h_scalars = nullptr;      // pinned [256]
+    // instrumentation
+    int64_t launch_count = 0;         // kernels launched by this context (all classes)
+    bool timing = false;
+    nsb_timer_class timers[NSB_T_NCLASS];
 };
+
+int nsb_timer_flush(nsb_ctx* ctx);   // context.cu: fold finished event pairs into timers[].ms
+
+// RAII region: records a start/stop event pair on `st` around the launches of one kernel class
+struct nsb_timed_region {
+    nsb_ctx* ctx; int cls; cudaStream_t st; bool on;
+    nsb_timed_region(nsb_ctx* c, int k, cudaStream_t s) : ctx(c), cls(k), st(s), on(c && c->timing) {
+        if (!on) return;
+        nsb_timer_class& t = ctx->timers[cls];
+        if (t.used + 2 > t.ev.size()) {
+            if (t.ev.size() >= (1u << 16)) nsb_timer_flush(ctx);
+            if (t.used + 2 > t.ev.size()) {
+                cudaEvent_t a, b;
+                cudaEventCreate(&a); cudaEventCreate(&b);
+                t.ev.push_back(a); t.ev.push_back(b);
+            }
+        }
+        cudaEventRecord(t.ev[t.used], st);
+    }
+    ~nsb_timed_region() {
+        if (!on) return;
+        nsb_timer_class& t = ctx->timers[cls];
+        cudaEventRecord(t.ev[t.used + 1], st);
+        t.used += 2;
+        t.regions += 1;
+    }
+};
+#define NSB_TIMED(ctx, cls, st) nsb_timed_region nsb_region_##cls(ctx, cls, st)
 
 extern thread_local std::string g_nsb_last_error;
 
@@ -66,7 +107,11 @@ static inline int nsb_fail(nsb_ctx* ctx, const char* fmt, const char* a = "", co
     do {                                                                           \
         cudaError_t e_ = cudaGetLastError();                                       \
         if (e_ != cudaSuccess) return nsb_fail(ctx, "launch of %s failed: %s", name, cudaGetErrorString(e_)); \
+        (ctx)->launch_count += 1;                                                  \
     } while (0)
+
+// extra launches covered by one NSB_LAUNCH_CHECK
+#define NSB_COUNT(ctx, n) ((ctx)->launch_count += (n))
 
 #define NSB_REQUIRE(ctx, cond, msg)                                                \
     do {                                                                           \

@@ -123,6 +123,7 @@ extern "C" int nsb_bc_apply_matrix(nsb_ctx* ctx, int32_t kind, int32_t bs, const
     if (nbc == 0) return 0;
     NSB_REQUIRE(ctx, rowptr && col && vals && bc_dofs && nbc > 0 && bs >= 1, "bad arguments");
     const int T = 256, B = nsb_blocks((int64_t)nbc * 8, T);
+    NSB_TIMED(ctx, NSB_T_BC, (cudaStream_t)stream);
     if (kind == NSB_CSR) {
         NSB_REQUIRE(ctx, bs == 1, "CSR Dirichlet rows need an explicit (bs = 1) matrix; use bc_mask for Kronecker CSR");
         k_bc_rows_csr<<<B, T, 0, (cudaStream_t)stream>>>(nbc, bc_dofs, rowptr, col, vals);
@@ -147,6 +148,7 @@ extern "C" int nsb_bc_apply_vector(nsb_ctx* ctx, int32_t mode, double* b, const 
     if (nbc == 0) return 0;
     NSB_REQUIRE(ctx, b && bc_dofs && bc_vals && nbc > 0, "bad arguments");
     NSB_REQUIRE(ctx, mode == NSB_BC_LINEAR || (mode == NSB_BC_NEWTON && x), "Newton mode needs x");
+    NSB_TIMED(ctx, NSB_T_BC, (cudaStream_t)stream);
     k_bc_vector<<<nsb_blocks(nbc, 256), 256, 0, (cudaStream_t)stream>>>(nbc, mode, bc_dofs, bc_vals, x, b);
     NSB_LAUNCH_CHECK(ctx, "k_bc_vector");
     return 0;
@@ -187,5 +189,45 @@ extern "C" int nsb_fp64_peak(nsb_ctx* ctx, double* tflops_out) {
     cudaEventDestroy(e1);
     const double flops = 2.0 * 8.0 * (double)iters * (double)T * (double)B;
     *tflops_out = flops / (best * 1e-3) / 1e12;
+    return 0;
+}
+
+// ---- instrumentation: per-class CUDA-event timers and the launch counter -----------------------
+int nsb_timer_flush(nsb_ctx* ctx) {
+    for (int c = 0; c < NSB_T_NCLASS; ++c) {
+        nsb_timer_class& t = ctx->timers[c];
+        for (size_t i = 0; i + 1 < t.used; i += 2) {
+            if (cudaEventSynchronize(t.ev[i + 1]) != cudaSuccess) return -1;
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, t.ev[i], t.ev[i + 1]) != cudaSuccess) return -1;
+            t.ms += ms;
+        }
+        t.used = 0;
+    }
+    return 0;
+}
+
+extern "C" int nsb_timer_enable(nsb_ctx* ctx, int32_t enable) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    if (nsb_timer_flush(ctx)) return nsb_fail(ctx, "timer flush failed%s%s");
+    ctx->timing = enable != 0;
+    return 0;
+}
+
+extern "C" int nsb_timer_report(nsb_ctx* ctx, double* ms_out, int64_t* regions_out) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    if (nsb_timer_flush(ctx)) return nsb_fail(ctx, "timer flush failed%s%s");
+    for (int c = 0; c < NSB_T_NCLASS; ++c) {
+        if (ms_out) ms_out[c] = ctx->timers[c].ms;
+        if (regions_out) regions_out[c] = ctx->timers[c].regions;
+        ctx->timers[c].ms = 0.0;
+        ctx->timers[c].regions = 0;
+    }
+    return 0;
+}
+
+extern "C" int nsb_launch_count(nsb_ctx* ctx, int64_t* count_out) {
+    NSB_REQUIRE(ctx, ctx != nullptr && count_out != nullptr, "null argument");
+    *count_out = ctx->launch_count;
     return 0;
 }

@@ -117,15 +117,22 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, con
     const int G = krylov_grid(ctx, n);
     double shift = 0.0;
     if (nullspace) {
-        k_reduce<false><<<G, 256, 0, st>>>(n, b, nullptr, ctx->d_partials, ctx->d_counter, ds + S_OUT);
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_reduce<false><<<G, 256, 0, st>>>(n, b, nullptr, ctx->d_partials, ctx->d_counter, ds + S_OUT);
+        }
         NSB_LAUNCH_CHECK(ctx, "k_reduce");
         if (fetch(ctx, S_OUT, 1, st)) return -1;
         shift = ctx->h_scalars[S_OUT] / (double)n;
     }
     if (nsb_launch_spmv(ctx, A, x, q, nullptr, nullptr, st)) return -1;
-    k_cg_init<<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
-    k_cg_init_finish<<<1, 1, 0, st>>>(ds);
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cg_init<<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
+        k_cg_init_finish<<<1, 1, 0, st>>>(ds);
+    }
     NSB_LAUNCH_CHECK(ctx, "k_cg_init");
+    NSB_COUNT(ctx, 1);
     if (fetch(ctx, S_RZ0, 5, st)) return -1;
     const double bnorm = sqrt(ctx->h_scalars[S_BB]);
     double rnorm = sqrt(ctx->h_scalars[S_RR]);
@@ -134,10 +141,14 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, con
     int cur = S_RZ0, nxt = S_RZ1;
     while (rnorm > tol && it < maxit) {
         if (nsb_launch_spmv(ctx, A, p, q, p, ds + S_PQ, st)) return -1;
-        k_cg_update1<<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
-        k_cg_update1_finish<<<1, 1, 0, st>>>(ds, nxt);
-        k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, nxt, ds);
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_cg_update1<<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
+            k_cg_update1_finish<<<1, 1, 0, st>>>(ds, nxt);
+            k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, nxt, ds);
+        }
         NSB_LAUNCH_CHECK(ctx, "k_cg_update");
+        NSB_COUNT(ctx, 2);
         if (fetch(ctx, S_RR, 1, st)) return -1;
         rnorm = sqrt(ctx->h_scalars[S_RR]);
         if (!(rnorm == rnorm)) return nsb_fail(ctx, "CG breakdown: residual is NaN%s%s");
@@ -149,6 +160,7 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, con
         if (fetch(ctx, S_OUT, 1, st)) return -1;
         k_shift<<<G, 256, 0, st>>>(n, ctx->h_scalars[S_OUT] / (double)n, x);
         NSB_LAUNCH_CHECK(ctx, "k_shift");
+        NSB_COUNT(ctx, 1);
     }
     if (iters_out) *iters_out = it;
     if (resid_out) *resid_out = rnorm;
@@ -251,7 +263,10 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, 
     std::vector<double> H((size_t)(m + 1) * m, 0.0), cs(m), sn(m), g(m + 1), y(m);
 
     // ||b||
-    k_reduce<true><<<G, 256, 0, st>>>(n, b, b, ctx->d_partials, ctx->d_counter, ds + S_OUT);
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_reduce<true><<<G, 256, 0, st>>>(n, b, b, ctx->d_partials, ctx->d_counter, ds + S_OUT);
+    }
     NSB_LAUNCH_CHECK(ctx, "k_reduce");
     if (fetch(ctx, S_OUT, 1, st)) return -1;
     const double bnorm = sqrt(hs[S_OUT]);
@@ -261,29 +276,40 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, 
     while (true) {
         // true residual r = b - A x -> w
         if (nsb_launch_spmv(ctx, A, x, t, nullptr, nullptr, st)) return -1;
-        k_residual<<<G, 256, 0, st>>>(n, b, t, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_residual<<<G, 256, 0, st>>>(n, b, t, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+        }
         NSB_LAUNCH_CHECK(ctx, "k_residual");
         if (fetch(ctx, S_NRM, 1, st)) return -1;
         rnorm = sqrt(hs[S_NRM]);
         if (!(rnorm == rnorm)) return nsb_fail(ctx, "GMRES breakdown: residual is NaN%s%s");
         if (rnorm <= tol || it >= maxit) break;
-        k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, dinv, V, t);
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, dinv, V, t);
+        }
+        NSB_COUNT(ctx, 1);
         g.assign(m + 1, 0.0);
         g[0] = rnorm;
         int j = 0;
         for (; j < m && it < maxit; ++j) {
             if (nsb_launch_spmv(ctx, A, t, w, nullptr, nullptr, st)) return -1;
             const int nk = j + 1;
+            nsb_timed_region* arnoldi = new nsb_timed_region(ctx, NSB_T_KRYLOV, st);
             for (int pass = 0; pass < 2; ++pass) {   // CGS-2
                 double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
                 for (int k0 = 0; k0 < nk; k0 += 8) {
                     const int c = nk - k0 < 8 ? nk - k0 : 8;
                     k_multi_dot<8><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
+                    NSB_COUNT(ctx, 1);
                 }
                 k_multi_axpy<<<G, 256, 0, st>>>(n, nk, V, hdev, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
             }
             k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, dinv, V + (int64_t)(j + 1) * n, t);
+            delete arnoldi;
             NSB_LAUNCH_CHECK(ctx, "gmres arnoldi");
+            NSB_COUNT(ctx, 2);
             // one host round trip per iteration: h1, h2, ||w||^2
             NSB_CUDA(ctx, cudaMemcpyAsync(hs + S_NRM, ds + S_NRM, sizeof(double) * (S_H2 + nk + 8 - S_NRM),
                                           cudaMemcpyDeviceToHost, st));
@@ -316,7 +342,10 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, 
         }
         for (int k = 0; k < nk; ++k) hs[S_Y + k] = y[k];
         NSB_CUDA(ctx, cudaMemcpyAsync(ds + S_Y, hs + S_Y, sizeof(double) * nk, cudaMemcpyHostToDevice, st));
-        k_gmres_update<<<G, 256, 0, st>>>(n, nk, V, ds + S_Y, dinv, x);
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_gmres_update<<<G, 256, 0, st>>>(n, nk, V, ds + S_Y, dinv, x);
+        }
         NSB_LAUNCH_CHECK(ctx, "k_gmres_update");
         NSB_CUDA(ctx, cudaStreamSynchronize(st));   // hs[S_Y..] is reused next cycle
     }

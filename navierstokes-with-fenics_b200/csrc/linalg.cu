@@ -8,6 +8,7 @@ static int launch_spmv_t(nsb_ctx* ctx, const nsb_matrix* A, const double* x, dou
                          const double* dot_with, double* scalar_out, cudaStream_t st) {
     constexpr int RPB = NSB_SPMV_THREADS / LANES;
     int64_t blocks = ((int64_t)A->nrows + RPB - 1) / RPB;
+    nsb_timed_region region(ctx, KIND == NSB_BSR ? NSB_T_SPMV_BSR : NSB_T_SPMV_CSR, st);
     if (dot_with) {
         const int64_t cap = (int64_t)ctx->sm_count * 8;
         if (blocks > cap) blocks = cap;
@@ -84,6 +85,7 @@ extern "C" int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_d
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, A && A->rowptr && A->col && A->vals && inv_diag, "bad arguments");
     const int64_t n = (int64_t)A->nrows * A->bs;
+    nsb_timed_region region(ctx, NSB_T_KRYLOV, (cudaStream_t)stream);
     k_inv_diag<<<nsb_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(A->kind, A->bs, A->nrows, A->rowptr,
                                                                        A->col, A->vals, A->bc_mask, inv_diag);
     NSB_LAUNCH_CHECK(ctx, "k_inv_diag");
@@ -148,24 +150,28 @@ extern "C" int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y,
 }
 extern "C" int nsb_vec_axpy(nsb_ctx* ctx, int64_t n, double a, const double* x, double* y, void* stream) {
     NSB_REQUIRE(ctx, ctx && x && y && n >= 0, "bad arguments");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
     k_axpy<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, a, x, y);
     NSB_LAUNCH_CHECK(ctx, "k_axpy");
     return 0;
 }
 extern "C" int nsb_vec_scale(nsb_ctx* ctx, int64_t n, double a, double* x, void* stream) {
     NSB_REQUIRE(ctx, ctx && x && n >= 0, "bad arguments");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
     k_scale<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, a, x);
     NSB_LAUNCH_CHECK(ctx, "k_scale");
     return 0;
 }
 extern "C" int nsb_vec_scatter(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream) {
     NSB_REQUIRE(ctx, ctx && idx && x && y && n >= 0, "bad arguments");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
     k_scatter<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, idx, x, y);
     NSB_LAUNCH_CHECK(ctx, "k_scatter");
     return 0;
 }
 extern "C" int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream) {
     NSB_REQUIRE(ctx, ctx && idx && x && y && n >= 0, "bad arguments");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
     k_gather<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, idx, x, y);
     NSB_LAUNCH_CHECK(ctx, "k_gather");
     return 0;
@@ -173,6 +179,7 @@ extern "C" int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const
 extern "C" int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, double* u2,
                                 int64_t nq, const double* p, double* p_old, void* stream) {
     NSB_REQUIRE(ctx, ctx && u0 && u1 && u2 && p && p_old, "bad arguments");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
     k_ipcs_advance<<<grid_for(ctx, nv, 256), 256, 0, (cudaStream_t)stream>>>(nv, u0, u1, u2, nq, p, p_old);
     NSB_LAUNCH_CHECK(ctx, "k_ipcs_advance");
     return 0;
@@ -187,14 +194,20 @@ static int fetch_scalar(nsb_ctx* ctx, double* out_host, cudaStream_t st) {
 extern "C" int nsb_vec_dot(nsb_ctx* ctx, int64_t n, const double* x, const double* y, double* out_host, void* stream) {
     NSB_REQUIRE(ctx, ctx && x && y && out_host && n >= 0, "bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
-    k_dot<true><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, y, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
+    {
+        NSB_TIMED(ctx, NSB_T_VEC, st);
+        k_dot<true><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, y, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
+    }
     NSB_LAUNCH_CHECK(ctx, "k_dot");
     return fetch_scalar(ctx, out_host, st);
 }
 extern "C" int nsb_vec_sum(nsb_ctx* ctx, int64_t n, const double* x, double* out_host, void* stream) {
     NSB_REQUIRE(ctx, ctx && x && out_host && n >= 0, "bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
-    k_dot<false><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, nullptr, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
+    {
+        NSB_TIMED(ctx, NSB_T_VEC, st);
+        k_dot<false><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, nullptr, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
+    }
     NSB_LAUNCH_CHECK(ctx, "k_dot(sum)");
     return fetch_scalar(ctx, out_host, st);
 }

@@ -253,6 +253,23 @@ class Device:
         self.check(self.lib.nsb_ipcs_advance(self.ctx, u0.numel(), _ptr(u0), _ptr(u1), _ptr(u2), p.numel(), _ptr(p),
                                              _ptr(p_old), self.stream))
 
+    # ---- instrumentation --------------------------------------------------------------------
+    def timer_enable(self, on=True):
+        self.check(self.lib.nsb_timer_enable(self.ctx, 1 if on else 0))
+
+    def timer_report(self):
+        """{class: (milliseconds, timed regions)} since the last report (synchronises)."""
+        n = len(L.TIMER_CLASSES)
+        ms, cnt = (C.c_double * n)(), (C.c_int64 * n)()
+        self.check(self.lib.nsb_timer_report(self.ctx, ms, cnt))
+        return {name: (ms[i], cnt[i]) for i, name in enumerate(L.TIMER_CLASSES)}
+
+    def launch_count(self):
+        """kernels launched by libnsb200 for this context (counted inside the library)."""
+        out = C.c_int64()
+        self.check(self.lib.nsb_launch_count(self.ctx, C.byref(out)))
+        return out.value
+
     def fp64_peak(self):
         out = C.c_double()
         self.check(self.lib.nsb_fp64_peak(self.ctx, C.byref(out)))

@@ -68,16 +68,43 @@ class IPCSSolver(SolverBase):
         self._bc_ready = True
         self._have_constant = False
 
-    def _update_bc_values(self):
-        """time-dependent Dirichlet data: re-evaluate on the host, upload the values (H11)."""
-        if not self._time_dependent_bcs:
-            return
+    def _update_bc_values(self, force=False):
+        """Dirichlet data: time-dependent values are re-evaluated on the host (the Python
+        ``Expression`` callbacks of the reference, H11) and uploaded from pinned host memory.
+        ``force`` uploads the tables even when they are constant (dolfin re-evaluates every
+        DirichletBC on each apply; bench.py's end-to-end leg counts these bytes)."""
+        if not (self._time_dependent_bcs or force):
+            return 0
         sp = self.dev.spaces
-        _, vv = sp.dirichlet_table(self._velocity_bcs, "V")
-        self._vbc_vals.copy_(torch.from_numpy(vv))
+        if not hasattr(self, "_vbc_host"):
+            self._vbc_host = torch.empty(self._vbc_vals.numel(), dtype=torch.float64).pin_memory()
+            self._pbc_host = torch.empty(self._pbc_vals.numel(), dtype=torch.float64).pin_memory()
+            self._vbc_host.copy_(self._vbc_vals)
+            self._pbc_host.copy_(self._pbc_vals)
+        if self._time_dependent_bcs:
+            _, vv = sp.dirichlet_table(self._velocity_bcs, "V")
+            self._vbc_host.copy_(torch.from_numpy(vv))
+            if self._pbc_dofs.numel():
+                _, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
+                self._pbc_host.copy_(torch.from_numpy(pv))
+        self._vbc_vals.copy_(self._vbc_host, non_blocking=True)
+        nbytes = self._vbc_host.numel() * 8
         if self._pbc_dofs.numel():
-            _, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
-            self._pbc_vals.copy_(torch.from_numpy(pv))
+            self._pbc_vals.copy_(self._pbc_host, non_blocking=True)
+            nbytes += self._pbc_host.numel() * 8
+        return nbytes
+
+    def fetch_solution(self, out=None):
+        """Device -> pinned host copy of the mixed solution vector (what the reference hands to
+        its XDMF writer, source/ns_problem.py:733-735).  Returns (host tensor, bytes)."""
+        w = self.solution
+        if out is None:
+            if not hasattr(self, "_w_host"):
+                self._w_host = torch.empty(w.numel(), dtype=torch.float64).pin_memory()
+            out = self._w_host
+        out.copy_(w, non_blocking=True)
+        torch.cuda.current_stream(self.dev.torch_device).synchronize()
+        return out, w.numel() * 8
 
     # ---- constant operators (pressure stiffness, velocity mass), quirk Q8 ----------------------
     def _assemble_constant(self):
@@ -126,12 +153,12 @@ class IPCSSolver(SolverBase):
             self._old_pressure.copy_(p0)
 
     # ---- one time step -------------------------------------------------------------------------
-    def solve(self):
+    def solve(self, upload_bcs=False):
         """``InstationarySolverBase.solve`` (source/ns_solver_base.py:1174-1203)"""
         if not self._bc_ready:
             self._setup_boundary_conditions()
         self._set_time(self._time_stepping.next_time)
-        self._update_bc_values()
+        self.h2d_bytes = self._update_bc_values(force=upload_bcs)
         self._update_time_stepping_coefficients()
         if not (self._have_constant and self._cache):
             self._assemble_constant()

@@ -73,12 +73,17 @@ def dirichlet_values(spaces, bcs):
 def apply_ident(A, dofs):
     """``bc.apply(A)``: zero the BC rows (pattern kept), diagonal 1.0, columns untouched."""
     A = A.tocsr(copy=True)
-    for i in dofs:
-        s, e = A.indptr[i], A.indptr[i + 1]
-        A.data[s:e] = 0.0
-        j = s + np.searchsorted(A.indices[s:e], i)
-        assert A.indices[j] == i
-        A.data[j] = 1.0
+    dofs = np.asarray(dofs, dtype=np.int64)
+    if len(dofs) == 0:
+        return A
+    is_bc = np.zeros(A.shape[0], dtype=bool)
+    is_bc[dofs] = True
+    rows = np.repeat(np.arange(A.shape[0]), np.diff(A.indptr))
+    in_bc_row = is_bc[rows]
+    diag = in_bc_row & (A.indices == rows)
+    assert diag.sum() == len(np.unique(dofs)), "a Dirichlet row has no diagonal entry in the pattern"
+    A.data[in_bc_row] = 0.0
+    A.data[diag] = 1.0
     return A
 
 

@@ -84,10 +84,14 @@ def project_Q(asm, f):
 
 
 class _Base:
-    def __init__(self, mesh, Re=None, coefficients=None):
+    def __init__(self, mesh, Re=None, coefficients=None, assembler="numpy", threads=None):
         self.mesh = mesh
         self.sp = Spaces(mesh)
-        self.asm = Assembler(self.sp)
+        if assembler == "c":      # plain-C restatement (oracle/c/nsoracle.c), same interface
+            from .native import CAssembler
+            self.asm = CAssembler(self.sp, threads=threads)
+        else:
+            self.asm = Assembler(self.sp)
         # EquationCoefficientHandler (source/auxiliary_classes.py:251-306): conv=1, p=1, visc=1/Re
         co = dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / Re if Re else 1.0)
         if coefficients:
@@ -99,8 +103,9 @@ class _Base:
 class IPCSOracle(_Base):
     """State: velocities[0..2] (V), intermediate_velocity (V), pressure, old_pressure (Q)."""
 
-    def __init__(self, mesh, Re, velocity_bcs, pressure_bcs=(), tol=1e-10, max_iter=50, time_fn=None):
-        super().__init__(mesh, Re)
+    def __init__(self, mesh, Re, velocity_bcs, pressure_bcs=(), tol=1e-10, max_iter=50, time_fn=None,
+                 assembler="numpy", threads=None):
+        super().__init__(mesh, Re, assembler=assembler, threads=threads)
         s = self.sp
         self.velocities = [np.zeros(s.ndofs_V) for _ in range(3)]
         self.intermediate_velocity = np.zeros(s.ndofs_V)
@@ -110,6 +115,8 @@ class IPCSOracle(_Base):
         self.pressure_bcs = list(pressure_bcs)        # [(marker, value)]
         self.tol, self.max_iter = tol, max_iter
         self.alpha, self.k = (1.0, -1.0, 0.0), None
+        self.linear_solver = "lu"          # "lu" (reference-faithful) | "krylov" (algorithm-matched)
+        self.krylov_iterations = []
 
     def _bcs_at(self, t):
         def bind(v):
@@ -143,21 +150,47 @@ class IPCSOracle(_Base):
         def J(x):
             return obc.apply_ident(asm.ipcs_momentum_jacobian(x, a0, k, self.c_conv, self.c_visc), vd)
 
+        krylov = self.linear_solver == "krylov"
+        kit = dict(momentum=[], pressure=0, correction=0)
+        if krylov:
+            from . import krylov as okr
+
+            def lin(A, b):
+                x, n_it = okr.gmres(A, b, rtol=1e-12)
+                kit["momentum"].append(n_it)
+                return x
+        else:
+            lin = lu_solve
         its, hist = newton(F, J, self.intermediate_velocity, atol=self.tol, rtol=10 * self.tol,
-                           maxit=self.max_iter)
+                           maxit=self.max_iter, solve=lin)
         self.newton_iterations.append(its)
         self.newton_history = hist
         # (2) pressure Poisson
         A = asm.poisson_matrix()
         b = asm.poisson_rhs(pn, self.intermediate_velocity, a0, k)
-        if len(pd):
+        if krylov:
+            if len(pd):
+                x0 = self.pressure.copy()
+                x0[pd] = pv
+                self.pressure[:], kit["pressure"] = okr.pcg(obc.apply_ident(A, pd), obc.apply_rhs_linear(b, pd, pv),
+                                                            x0=x0, rtol=1e-12)
+            else:
+                self.pressure[:], kit["pressure"] = okr.pcg(A, b, x0=self.pressure, rtol=1e-12, nullspace=True)
+        elif len(pd):
             self.pressure[:] = lu_solve(obc.apply_ident(A, pd), obc.apply_rhs_linear(b, pd, pv))
         else:
             self.pressure[:] = solve_singular_mean_zero(A, b - b.mean())
         # (3) velocity correction
         M = asm.velocity_mass_matrix()
         b = asm.correction_rhs(self.intermediate_velocity, self.pressure, self.old_pressure, a0, k)
-        self.velocities[0][:] = lu_solve(obc.apply_ident(M, vd), obc.apply_rhs_linear(b, vd, vv))
+        if krylov:
+            x0 = self.intermediate_velocity.copy()
+            x0[vd] = vv
+            self.velocities[0][:], kit["correction"] = okr.pcg(obc.apply_ident(M, vd),
+                                                               obc.apply_rhs_linear(b, vd, vv), x0=x0, rtol=1e-12)
+        else:
+            self.velocities[0][:] = lu_solve(obc.apply_ident(M, vd), obc.apply_rhs_linear(b, vd, vv))
+        self.krylov_iterations.append(kit)
 
     def advance_time(self):
         """``_advance_solution`` source/ns_ipcs_solver.py:35-43."""
@@ -169,8 +202,9 @@ class IPCSOracle(_Base):
 class BDFOracle(_Base):
     """Monolithic BDF-2 Newton on W; solutions[0..2]."""
 
-    def __init__(self, mesh, Re, velocity_bcs, pressure_bcs=(), tol=1e-10, max_iter=50):
-        super().__init__(mesh, Re)
+    def __init__(self, mesh, Re, velocity_bcs, pressure_bcs=(), tol=1e-10, max_iter=50, assembler="numpy",
+                 threads=None):
+        super().__init__(mesh, Re, assembler=assembler, threads=threads)
         self.solutions = [np.zeros(self.sp.ndofs_W) for _ in range(3)]
         self.velocity_bcs, self.pressure_bcs = list(velocity_bcs), list(pressure_bcs)
         self.tol, self.max_iter = tol, max_iter
