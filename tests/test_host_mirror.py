@@ -1,0 +1,60 @@
+"""Host-side mirror of the reference interface (meshes, spaces, Dirichlet tables, BC tuple
+format) against the independently written oracle equivalents.  Bit-exact (integer / index work)."""
+import numpy as np
+import pytest
+
+import nsb200
+import oracle
+
+CASES = [((0.0, 0.0), (2.0, 1.0), (5, 3)), ((0.0, 0.0, 0.0), (1.0, 2.0, 0.5), (2, 3, 2))]
+
+
+@pytest.mark.parametrize("box", CASES, ids=["2d", "3d"])
+def test_mesh_spaces_and_bc_tables(box):
+    m, markers = nsb200.hyper_rectangle(*box)
+    om = oracle.mesh.hyper_rectangle(*box)
+    assert np.array_equal(m.coords, om.coords) and np.array_equal(m.cells, om.cells)
+    assert np.array_equal(m.edges, om.edges) and np.array_equal(m.cell_edges, om.cell_edges)
+    assert markers is m.bfacet_marker and m.boundary_ids() == om.boundary_marker_ids()
+    key = lambda f, mk: sorted(zip(map(tuple, f.tolist()), mk.tolist()))   # noqa: E731
+    assert key(m.bfacets, m.bfacet_marker) == key(om.bfacets, om.bfacet_marker)
+    sp, osp = nsb200.TaylorHoodSpaces(m), oracle.dofmap.Spaces(om)
+    assert np.array_equal(sp.cell_nodes, osp.cell_nodes) and np.array_equal(sp.cell_dofs_W, osp.cell_dofs_W)
+    assert np.array_equal(sp.cell_dofs_V, osp.cell_dofs_V)
+    assert np.array_equal(sp.V_to_W(), osp.V_to_W) and np.array_equal(sp.Q_to_W(), osp.Q_to_W)
+    assert np.array_equal(sp.node_coordinates(), osp.node_coords())
+    d = m.dim
+
+    def inflow(x):
+        u = np.zeros((len(x), d))
+        u[:, 0] = 6.0 * x[:, 1] * (1.0 - x[:, 1])
+        return u
+    bcs = [(1, None, inflow), (3, None, (0.0,) * d), (4, 0, 1.0), (4, 1, lambda x: x[:, 0] ** 2), (2, "p", 0.5)]
+    for space in ("V", "Q", "W"):
+        dofs, vals = sp.dirichlet_table(bcs, space)
+        obcs = [(space, mk, c, v) for mk, c, v in bcs if (c == "p") == (space == "Q") or space == "W"]
+        odofs, ovals = oracle.bc.dirichlet_values(osp, obcs)
+        assert np.array_equal(dofs, odofs) and np.array_equal(vals, ovals), space
+
+
+def test_bc_tuple_translation_matches_reference_format():
+    """same tuples as the reference demos/tests (demo/cavity_flow.py:26-29,
+    tests/test_ipcs_solver.py:27-37): validated against the markers, last wins."""
+    V, P = nsb200.VelocityBCType, nsb200.PressureBCType
+    m, markers = nsb200.hyper_cube(2, 4)
+    base = nsb200.solver_base.SolverBase(m, markers, "standard")
+    base.set_boundary_conditions([(V.no_slip, 1, None), (V.no_slip, 2, None), (V.no_slip, 3, None),
+                                  (V.constant, 4, (1.0, 0.0)), (P.constant, 2, 0.0),
+                                  (V.constant_component, 3, 1, 0.0), (V.no_normal_flux, 1, None)])
+    assert base._velocity_bcs[3] == (4, None, (1.0, 0.0)) and base._pressure_bcs == [(2, "p", 0.0)]
+    assert base._velocity_bcs[-1] == (1, 0, 0.0)          # planar normal of x = 0 is axis 0
+    with pytest.raises(AssertionError):
+        base.set_boundary_conditions([(V.no_slip, 9, None)])       # unknown boundary id
+    with pytest.raises(NotImplementedError):
+        nsb200.solver_base.SolverBase(m, markers, "rotational")
+    base.set_equation_coefficients(dict(convective_term=1.0, viscous_term=0.01))
+    with pytest.raises(AssertionError):
+        base.set_equation_coefficients(dict(viscous_term=-1.0))
+    assert nsb200.solver_base.newton_converged(1e-11, 1.0, 1e-10, 1e-9)
+    assert nsb200.solver_base.newton_converged(1e-3, 1e7, 1e-10, 1e-9)
+    assert not nsb200.solver_base.newton_converged(1e-3, 1.0, 1e-10, 1e-9)
