@@ -78,6 +78,10 @@ typedef struct nsb_matrix {
     const double* vals;      /* dev [nnz] (CSR) or [nnz*bs*bs] (BSR)                      */
     const uint8_t* bc_mask;  /* dev [nrows*bs] or NULL: 1 = Dirichlet dof, the operator acts
                                 as the identity on that row (dolfin `ident`, diagonal 1.0) */
+    const uint32_t* tiles;   /* dev [ntiles*64] or NULL: TMA row tiles of this pattern
+                                (nsb_tiles_build); enables the bulk-copy SpMV kernels       */
+    int32_t ntiles;
+    int32_t reserved;
 } nsb_matrix;
 
 /* ---------------------------------------------------------------- life cycle ---------- */
@@ -100,6 +104,11 @@ int nsb_pattern_sizes(const nsb_pattern_builder* pb, int64_t* nnz, int64_t* npai
 int nsb_pattern_fill(const nsb_pattern_builder* pb, int32_t* rowptr, int32_t* col,
                      int32_t* pair_ptr, int32_t* pair_cell, uint8_t* pair_iloc, uint8_t* pair_slots);
 int nsb_pattern_free(nsb_pattern_builder* pb);
+/* Row tiles for the TMA (cp.async.bulk) SpMV kernels: rows grouped so that the value and column
+ * streams of a tile are one contiguous 16-byte aligned chunk of <= max_entries entries.  Pure CPU.
+ * records == NULL: only count.  Record layout (64 uint32 per tile) in csrc/setup_host.cu. */
+int nsb_tiles_build(int32_t nrows, const int32_t* rowptr_host, int32_t max_entries, int32_t* ntiles_out,
+                    uint32_t* records_host);
 
 /* ---------------------------------------------------------------- device state --------- */
 /* mesh of source/grid_generator.py:111-208 (ordered simplices) + scalar P2 node map */

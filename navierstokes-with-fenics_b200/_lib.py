@@ -11,6 +11,8 @@ VEC, MAT, PICARD, BDF, SYMBC = 1, 2, 4, 8, 16
 PAT_P2P2, PAT_P1P1, PAT_WW = 0, 1, 2
 CSR, BSR = 0, 1
 BC_LINEAR, BC_NEWTON = 0, 1
+# entries per TMA tile of the bulk-copy SpMV kernels, keyed by (matrix kind, bs) (csrc/spmv_tma.cuh)
+TILE_ENTRIES = {(BSR, 3): 384, (BSR, 2): 768}
 TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
                  "krylov_vec", "dirichlet", "vector")
 
@@ -24,7 +26,8 @@ vp = C.c_void_p
 class Matrix(C.Structure):
     """struct nsb_matrix"""
     _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
-                ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp)]
+                ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp), ("tiles", vp),
+                ("ntiles", C.c_int32), ("reserved", C.c_int32)]
 
 
 # name -> (restype, argtypes); every symbol include/nsb200.h declares
@@ -37,6 +40,7 @@ PROTOTYPES = {
     "nsb_pattern_sizes": (C.c_int, [vp, c_i64p, c_i64p, c_i32p]),
     "nsb_pattern_fill": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "nsb_pattern_free": (C.c_int, [vp]),
+    "nsb_tiles_build": (C.c_int, [C.c_int32, vp, C.c_int32, c_i32p, vp]),
     "nsb_set_mesh": (C.c_int, [vp, C.c_int32, C.c_int32, vp, C.c_int32, vp, C.c_int32, vp]),
     "nsb_set_pattern": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),

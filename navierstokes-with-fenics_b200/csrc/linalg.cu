@@ -1,6 +1,7 @@
 // linalg.cu -- SpMV launcher, Jacobi diagonal (K12), vector kernels and the BDF history shift
 // (K13), reductions (K15).
 #include "spmv.cuh"
+#include "spmv_tma.cuh"
 
 // ---- SpMV dispatch ---------------------------------------------------------------------------
 template <int KIND, int BS, int LANES>
@@ -45,6 +46,13 @@ int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* 
             case 3: return launch_spmv_bs<NSB_CSR, 3>(ctx, A, x, y, dot_with, scalar_out, st);
         }
     } else if (A->kind == NSB_BSR) {
+        const bool tma_ok = A->tiles && A->ntiles > 0 && !dot_with &&
+                            ((((uintptr_t)A->vals) | ((uintptr_t)A->col) | ((uintptr_t)A->tiles)) & 15) == 0;
+        if (tma_ok) {
+            nsb_timed_region region(ctx, NSB_T_SPMV_BSR, st);
+            if (A->bs == 3) return launch_spmv_bsr_tma<3>(ctx, A, x, y, st);
+            if (A->bs == 2) return launch_spmv_bsr_tma<2>(ctx, A, x, y, st);
+        }
         switch (A->bs) {
             case 2: return launch_spmv_bs<NSB_BSR, 2>(ctx, A, x, y, dot_with, scalar_out, st);
             case 3: return launch_spmv_bs<NSB_BSR, 3>(ctx, A, x, y, dot_with, scalar_out, st);

@@ -129,3 +129,46 @@ extern "C" int nsb_pattern_free(nsb_pattern_builder* pb) {
     delete pb;
     return 0;
 }
+
+// ---- TMA row tiles ------------------------------------------------------------------------------
+// Partition of the rows of a CSR/BSR pattern into tiles whose value and column streams are one
+// contiguous, 16-byte aligned chunk each, so that a CTA can fetch a whole tile with three bulk
+// copies (spmv_tma.cuh).  Record = 64 uint32 (256 B):
+//   [0] first row  [1] rows  [2] first entry (= rowptr[first row])  [3] entries
+//   then uint16 off[rows + 1]: entry offset of every row inside the tile (off[rows] = entries).
+// The kernels fetch the 4-entry aligned hull of [first entry, first entry + entries) (16-byte
+// alignment of the column stream: 4 x 4 B; of the value stream: 4 x 8 B x bs^2), so tiles need
+// no alignment themselves.  Returns -1 when a single row exceeds max_entries (the caller then
+// keeps the generic kernel).
+#define NSB_TILE_WORDS 64
+#define NSB_TILE_MAX_ROWS 119
+
+extern "C" int nsb_tiles_build(int32_t nrows, const int32_t* rowptr, int32_t max_entries, int32_t* ntiles_out,
+                               uint32_t* records) {
+    if (!rowptr || nrows <= 0 || max_entries < 4 || max_entries > 65535 || !ntiles_out)
+        return nsb_fail(nullptr, "nsb_tiles_build: bad arguments%s%s");
+    int32_t nt = 0;
+    int32_t r0 = 0;
+    while (r0 < nrows) {
+        int32_t best = -1;
+        for (int32_t r1 = r0 + 1; r1 <= nrows && r1 - r0 <= NSB_TILE_MAX_ROWS; ++r1) {
+            if (rowptr[r1] - rowptr[r0] > max_entries) break;
+            best = r1;
+        }
+        if (best < 0) return nsb_fail(nullptr, "nsb_tiles_build: a row is longer than the tile%s%s");
+        if (records) {
+            uint32_t* rec = records + (size_t)nt * NSB_TILE_WORDS;
+            memset(rec, 0, sizeof(uint32_t) * NSB_TILE_WORDS);
+            rec[0] = (uint32_t)r0;
+            rec[1] = (uint32_t)(best - r0);
+            rec[2] = (uint32_t)rowptr[r0];
+            rec[3] = (uint32_t)(rowptr[best] - rowptr[r0]);
+            uint16_t* off = reinterpret_cast<uint16_t*>(rec + 4);
+            for (int32_t r = r0; r <= best; ++r) off[r - r0] = (uint16_t)(rowptr[r] - rowptr[r0]);
+        }
+        ++nt;
+        r0 = best;
+    }
+    *ntiles_out = nt;
+    return 0;
+}

@@ -1,0 +1,114 @@
+// spmv_tma.cuh -- BSR-BS SpMV with the matrix streamed through shared memory by the sm_100a
+// bulk-copy engine (K10, TMA 1-D form).
+//
+// One CTA per row tile (setup_host.cu::nsb_tiles_build).  Thread 0 arms an mbarrier with the
+// tile's byte count and issues three cp.async.bulk copies: the 256-byte tile record (row
+// offsets), the contiguous value chunk (entries * BS*BS * 8 B) and the contiguous column chunk
+// (entries * 4 B).  No registers stage the matrix, so the bytes in flight per SM are
+// resident CTAs x tile bytes (7 x 29 KB for BS = 3) -- far above the ~35 KB/SM Little's-law
+// requirement of HBM3e -- independent of how short the rows are.  After the barrier flips,
+// each warp owns rows w, w+NW, ... of the tile: a lane owns whole BS x BS blocks (LDS.64 at a
+// 72-byte stride is bank-conflict free for BS = 3), gathers x through L1/L2, and a shuffle tree
+// finishes the row.  Rows flagged in bc_mask act as identity rows (dolfin `ident`).
+#pragma once
+#include "common.cuh"
+#include "tma.cuh"
+
+#define NSB_TILE_WORDS 64
+
+template <int BS>
+struct SpmvTmaCfg {
+    static constexpr int BB = BS * BS;
+    static constexpr int TILE = (BS == 3) ? 384 : 768;     // entries per tile (== _lib.TILE_ENTRIES)
+    static constexpr int THREADS = 256;
+    static constexpr int CAP = TILE + 8;                   // + the 4-entry alignment hull on both sides
+    static constexpr size_t VAL_BYTES = (size_t)CAP * BB * 8;
+    static constexpr size_t COL_BYTES = (size_t)CAP * 4;
+    static constexpr size_t SMEM = VAL_BYTES + COL_BYTES + NSB_TILE_WORDS * 4 + 16;
+};
+
+template <int BS>
+__global__ void __launch_bounds__(SpmvTmaCfg<BS>::THREADS)
+k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* __restrict__ col,
+               const double* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
+               double* __restrict__ y) {
+    using Cfg = SpmvTmaCfg<BS>;
+    constexpr int BB = Cfg::BB, NW = Cfg::THREADS / 32;
+    extern __shared__ __align__(128) unsigned char smem[];
+    double* sv = reinterpret_cast<double*>(smem);
+    int32_t* sc = reinterpret_cast<int32_t*>(smem + Cfg::VAL_BYTES);
+    uint32_t* rec = reinterpret_cast<uint32_t*>(smem + Cfg::VAL_BYTES + Cfg::COL_BYTES);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(rec + NSB_TILE_WORDS);
+    const uint32_t* trec = tiles + (size_t)blockIdx.x * NSB_TILE_WORDS;
+    const uint32_t row0 = __ldg(trec), nrows = __ldg(trec + 1), ent0 = __ldg(trec + 2), nent = __ldg(trec + 3);
+    // bulk-copied hull [a0, a1): 4-entry (16-byte) aligned, clipped to the array; entry k of the tile
+    // lands at shared index shift + k; a tail [a1, ent0 + nent) exists only at the very end of the matrix
+    const uint32_t a0 = ent0 & ~3u, shift = ent0 - a0;
+    uint32_t a1 = (ent0 + nent + 3u) & ~3u;
+    if (a1 > nnz) a1 = nnz & ~3u;
+    const uint32_t nal = a1 > a0 ? a1 - a0 : 0u;
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(bar, NSB_TILE_WORDS * 4 + nal * (BB * 8 + 4));
+        tma_load_1d(rec, trec, NSB_TILE_WORDS * 4, bar);
+        if (nal) {
+            tma_load_1d(sv, vals + (size_t)a0 * BB, nal * BB * 8, bar);
+            tma_load_1d(sc, col + a0, nal * 4, bar);
+        }
+    }
+    if (a0 + nal < ent0 + nent) {               // <= 3 trailing entries of the matrix: plain loads
+        const uint32_t n1 = ent0 + nent - a0;   // entries wanted, counted from a0
+        for (uint32_t e = nal * BB + threadIdx.x; e < n1 * BB; e += Cfg::THREADS) sv[e] = vals[(size_t)a0 * BB + e];
+        for (uint32_t e = nal + threadIdx.x; e < n1; e += Cfg::THREADS) sc[e] = col[a0 + e];
+        __syncthreads();
+    }
+    mbar_wait(bar, 0);
+    const uint16_t* off = reinterpret_cast<const uint16_t*>(rec + 4);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (uint32_t lr = w; lr < nrows; lr += NW) {
+        const uint32_t o0 = shift + off[lr], o1 = shift + off[lr + 1];
+        double acc[BS];
+#pragma unroll
+        for (int b = 0; b < BS; ++b) acc[b] = 0.0;
+        for (uint32_t k = o0 + lane; k < o1; k += 32) {
+            const double* xb = x + (int64_t)sc[k] * BS;
+            double xv[BS];
+#pragma unroll
+            for (int c = 0; c < BS; ++c) xv[c] = __ldg(xb + c);
+            const double* v = sv + (size_t)k * BB;
+#pragma unroll
+            for (int r = 0; r < BS; ++r)
+#pragma unroll
+                for (int c = 0; c < BS; ++c) acc[r] += v[r * BS + c] * xv[c];
+        }
+#pragma unroll
+        for (int b = 0; b < BS; ++b) acc[b] = warp_sum(acc[b]);
+        if (lane < BS) {
+            const int64_t d = (int64_t)(row0 + lr) * BS + lane;
+            double v = acc[0];
+#pragma unroll
+            for (int b = 1; b < BS; ++b) v = (lane == b) ? acc[b] : v;
+            if (mask != nullptr && mask[d]) v = x[d];
+            y[d] = v;
+        }
+    }
+}
+
+template <int BS>
+static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, cudaStream_t st) {
+    using Cfg = SpmvTmaCfg<BS>;
+    static bool configured = false;
+    if (!configured) {
+        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        configured = true;
+    }
+    k_spmv_bsr_tma<BS><<<A->ntiles, Cfg::THREADS, Cfg::SMEM, st>>>(A->tiles, (uint32_t)A->nnz, A->col, A->vals,
+                                                                 A->bc_mask, x, y);
+    NSB_LAUNCH_CHECK(ctx, "k_spmv_bsr_tma");
+    return 0;
+}

@@ -41,10 +41,27 @@ class Pattern:
         finally:
             lib.nsb_pattern_free(h)
         self.rowptr_host, self.col_host = rowptr, col
+        self._dev, self._tiles = dev, {}
         up = dev.upload
         self.rowptr, self.col = up(rowptr), up(col)
         self.pair_ptr, self.pair_cell = up(pair_ptr), up(pair_cell)
         self.pair_iloc, self.pair_slots = up(pair_iloc), up(pair_slots)
+
+
+    def tiles(self, max_entries):
+        """TMA row tiles (nsb_tiles_build) for tiles of <= max_entries entries, cached;
+        (device tensor, ntiles) or (None, 0) when the pattern has no aligned partition."""
+        if max_entries not in self._tiles:
+            lib = self._dev.lib
+            nt = C.c_int32()
+            if lib.nsb_tiles_build(self.nrows, self.rowptr_host.ctypes.data, max_entries, C.byref(nt), None) != 0:
+                self._tiles[max_entries] = (None, 0)
+            else:
+                rec = np.empty(nt.value * 64, dtype=np.uint32)
+                L.check(lib.nsb_tiles_build(self.nrows, self.rowptr_host.ctypes.data, max_entries, C.byref(nt),
+                                            rec.ctypes.data))
+                self._tiles[max_entries] = (self._dev.upload(rec), nt.value)
+        return self._tiles[max_entries]
 
 
 class Device:
@@ -126,9 +143,11 @@ class Device:
     def matrix(self, pattern, vals, kind, bs, bc_mask=None):
         """nsb_matrix descriptor (keeps the tensors alive through attributes)."""
         pat = self.patterns[pattern]
+        tiles, ntiles = pat.tiles(L.TILE_ENTRIES[(kind, bs)]) if (kind, bs) in L.TILE_ENTRIES else (None, 0)
         m = L.Matrix(kind, bs, pat.nrows, pat.nnz, pat.rowptr.data_ptr(), pat.col.data_ptr(), vals.data_ptr(),
-                     bc_mask.data_ptr() if bc_mask is not None else None)
-        m._keep = (pat, vals, bc_mask)
+                     bc_mask.data_ptr() if bc_mask is not None else None,
+                     tiles.data_ptr() if tiles is not None else None, ntiles, 0)
+        m._keep = (pat, vals, bc_mask, tiles)
         return m
 
     # ---- coefficients -----------------------------------------------------------------------
