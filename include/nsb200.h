@@ -84,6 +84,18 @@ typedef struct nsb_matrix {
     int32_t reserved;
 } nsb_matrix;
 
+/* preconditioners of nsb_cg / nsb_gmres (K12) */
+#define NSB_PC_NONE 0
+#define NSB_PC_JACOBI 1      /* z = D^-1 v                                                    */
+#define NSB_PC_CHEBYSHEV 2   /* z = p(D^-1 A) D^-1 v, p = Chebyshev polynomial of `degree` terms
+                                (degree-1 SpMVs) for the interval [lambda_min, lambda_max] of D^-1 A */
+typedef struct nsb_precond {
+    int32_t kind;
+    int32_t degree;
+    const double* inv_diag;  /* dev [nrows*bs], nsb_inv_diagonal */
+    double lambda_min, lambda_max;
+} nsb_precond;
+
 /* ---------------------------------------------------------------- life cycle ---------- */
 int nsb_version(void);
 int nsb_create(nsb_ctx** ctx, int device);
@@ -167,18 +179,22 @@ int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void
 int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_diag, void* stream);
 int64_t nsb_cg_workspace_doubles(int64_t n);
 int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart);
-/* Jacobi-preconditioned CG for the SPD pressure-Poisson and mass systems which the reference
- * solves by LU (source/ns_ipcs_solver.py:171,195-196).  nullspace != 0: the operator has the
- * constant null space (all-Neumann pressure): rhs and solution are projected to
- * zero arithmetic mean.  Converged when ||r|| <= max(rtol*||b||, atol). */
-int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, const double* b, double* x,
+/* Preconditioned CG for the SPD pressure-Poisson and mass systems which the reference solves by
+ * LU (source/ns_ipcs_solver.py:171,195-196).  nullspace != 0: the operator has the constant
+ * null space (all-Neumann pressure): rhs and solution are projected to zero
+ * arithmetic mean.  Converged when ||r|| <= max(rtol*||b||, atol).  work: nsb_cg_workspace_doubles. */
+int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
            double rtol, double atol, int32_t maxit, int32_t nullspace, double* work,
            int32_t* iters_out, double* resid_out, void* stream);
-/* right-Jacobi-preconditioned restarted GMRES for the velocity / mixed systems
+/* right-preconditioned restarted GMRES (CGS-2 Arnoldi) for the velocity / mixed Newton systems
  * (source/ns_ipcs_solver.py:138-147, source/ns_bdf_solver.py:91-100) */
-int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, const double* b, double* x,
+int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
               double rtol, double atol, int32_t maxit, int32_t restart, double* work,
               int32_t* iters_out, double* resid_out, void* stream);
+/* largest eigenvalue (modulus) of D^-1 A by `iters` power iterations: upper end of the Chebyshev
+ * interval.  work: 2 * nrows*bs doubles. */
+int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, double* work,
+                   double* lambda_out_host, void* stream);
 
 /* Function.assign / Vector ops (source/ns_ipcs_solver.py:41-43, source/ns_solver_base.py:1015-1016) */
 int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y, void* stream);

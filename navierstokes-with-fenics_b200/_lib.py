@@ -30,6 +30,14 @@ class Matrix(C.Structure):
                 ("ntiles", C.c_int32), ("reserved", C.c_int32)]
 
 
+class Precond(C.Structure):
+    """struct nsb_precond"""
+    _fields_ = [("kind", C.c_int32), ("degree", C.c_int32), ("inv_diag", vp), ("lambda_min", C.c_double),
+                ("lambda_max", C.c_double)]
+
+
+PC_NONE, PC_JACOBI, PC_CHEBYSHEV = 0, 1, 2
+
 # name -> (restype, argtypes); every symbol include/nsb200.h declares
 PROTOTYPES = {
     "nsb_version": (C.c_int, []),
@@ -57,9 +65,10 @@ PROTOTYPES = {
     "nsb_inv_diagonal": (C.c_int, [vp, C.POINTER(Matrix), vp, vp]),
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32]),
-    "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
+    "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, vp, c_f64p, vp]),
+    "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                          vp, c_i32p, c_f64p, vp]),
-    "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
+    "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                             vp, c_i32p, c_f64p, vp]),
     "nsb_vec_copy": (C.c_int, [vp, C.c_int64, vp, vp, vp]),
     "nsb_vec_axpy": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp, vp]),

@@ -1,7 +1,10 @@
-// krylov.cu -- Krylov solvers (K11) replacing the sparse direct LU of the reference
-// (SURVEY.md G3): Jacobi-preconditioned CG for the SPD pressure-Poisson / mass systems
-// (source/ns_ipcs_solver.py:166-171,189-196) and right-Jacobi-preconditioned restarted GMRES
-// with CGS-2 Arnoldi for the velocity / mixed Newton systems (source/ns_ipcs_solver.py:138-147).
+// krylov.cu -- Krylov solvers (K11, K12) replacing the sparse direct LU of the reference
+// (SURVEY.md G3): preconditioned CG for the SPD pressure-Poisson / mass systems
+// (source/ns_ipcs_solver.py:166-171,189-196) and right-preconditioned restarted GMRES with
+// CGS-2 Arnoldi for the velocity / mixed Newton systems (source/ns_ipcs_solver.py:138-147).
+// Preconditioners: Jacobi, or a Chebyshev polynomial in D^-1 A on [lambda_min, lambda_max]
+// (K12; lambda_max from nsb_lambda_max power iteration).  The polynomial trades Arnoldi steps
+// (whose Gram-Schmidt cost grows with the basis) for SpMVs, which run near the HBM roofline.
 // Step lengths stay on the device (kernels read alpha/beta from device scalars); inner products
 // are warp-shuffle + deterministic last-block reductions; vector updates are fused with the
 // reductions that follow them and p.Ap is fused into the SpMV epilogue.
@@ -10,7 +13,7 @@
 #include "spmv.cuh"
 
 // device scalar slots
-enum { S_OUT = 0, S_RZ0 = 1, S_RZ1 = 2, S_PQ = 3, S_RR = 4, S_BB = 5, S_NRM = 8, S_H1 = 32, S_H2 = 96, S_Y = 160 };
+enum { S_OUT = 0, S_RZ0 = 1, S_RZ1 = 2, S_PQ = 3, S_RR = 4, S_BB = 5, S_NRM = 8, S_TMP = 11, S_H1 = 32, S_H2 = 96, S_Y = 160 };
 
 static int krylov_grid(nsb_ctx* ctx, int64_t n) {
     int64_t b = (n + 255) / 256;
@@ -19,70 +22,108 @@ static int krylov_grid(nsb_ctx* ctx, int64_t n) {
     return (int)(b < 1 ? 1 : b);
 }
 
+#define GRID_STRIDE(i, n) \
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < (n); i += (int64_t)gridDim.x * blockDim.x)
+
+// ---------------------------------------------------------------------------------------------
+// preconditioner kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_jacobi(int64_t n, const double* __restrict__ dinv, const double* __restrict__ v, double* __restrict__ z) {
+    GRID_STRIDE(i, n) z[i] = dinv[i] * v[i];
+}
+
+// Chebyshev start (z0 = 0): r = D^-1 v ; d = r / theta ; z = d
+__global__ void __launch_bounds__(256)
+k_cheb_first(int64_t n, const double* __restrict__ dinv, const double* __restrict__ v, double inv_theta,
+             double* __restrict__ r, double* __restrict__ d, double* __restrict__ z) {
+    GRID_STRIDE(i, n) {
+        const double c = dinv[i] * v[i];
+        const double di = c * inv_theta;
+        r[i] = c; d[i] = di; z[i] = di;
+    }
+}
+
+// Chebyshev step: r -= D^-1 q (q = A d) ; d = a d + b r ; z += d
+__global__ void __launch_bounds__(256)
+k_cheb_step(int64_t n, const double* __restrict__ dinv, const double* __restrict__ q, double a, double b,
+            double* __restrict__ r, double* __restrict__ d, double* __restrict__ z) {
+    GRID_STRIDE(i, n) {
+        const double ri = r[i] - dinv[i] * q[i];
+        const double di = a * d[i] + b * ri;
+        r[i] = ri; d[i] = di; z[i] += di;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // CG kernels
 // ---------------------------------------------------------------------------------------------
-// r = b - shift - q ; z = dinv r ; p = z ; sums: r.z, r.r, (b-shift).(b-shift)
+// r = b - shift - q ; [JAC: z = dinv r ; p = z] ; sums: r.z (JAC), r.r, (b-shift).(b-shift)
+template <bool JAC>
 __global__ void __launch_bounds__(256)
 k_cg_init(int64_t n, const double* __restrict__ b, const double* __restrict__ q, const double* __restrict__ dinv,
           double shift, double* __restrict__ r, double* __restrict__ z, double* __restrict__ p,
           double* partials, unsigned int* counter, double* scal) {
     double s[3] = {0.0, 0.0, 0.0};
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    GRID_STRIDE(i, n) {
         const double bi = b[i] - shift;
         const double ri = bi - q[i];
-        const double zi = dinv[i] * ri;
-        r[i] = ri; z[i] = zi; p[i] = zi;
-        s[0] += ri * zi; s[1] += ri * ri; s[2] += bi * bi;
+        r[i] = ri;
+        if (JAC) {
+            const double zi = dinv[i] * ri;
+            z[i] = zi; p[i] = zi;
+            s[0] += ri * zi;
+        }
+        s[1] += ri * ri; s[2] += bi * bi;
     }
     __shared__ double red[3 * 8];
-    double out3[3];
-    (void)out3;
-    grid_sum<3, 256>(s, partials, counter, scal + S_PQ + 8, red);   // staged below
+    grid_sum<3, 256>(s, partials, counter, scal + S_TMP, red);
 }
 
-// the 3 sums of k_cg_init land in scal[S_PQ+8 .. +10]; move them to their slots
-__global__ void k_cg_init_finish(double* scal) {
-    scal[S_RZ0] = scal[S_PQ + 8];
-    scal[S_RR] = scal[S_PQ + 9];
-    scal[S_BB] = scal[S_PQ + 10];
+__global__ void k_cg_init_finish(double* scal, int jac) {
+    if (jac) scal[S_RZ0] = scal[S_TMP];
+    scal[S_RR] = scal[S_TMP + 1];
+    scal[S_BB] = scal[S_TMP + 2];
 }
 
-// alpha = rz/pq ; x += alpha p ; r -= alpha q ; z = dinv r ; sums r.z -> rz_new, r.r
+// alpha = rz/pq ; x += alpha p ; r -= alpha q ; [JAC: z = dinv r ; sum r.z] ; sum r.r
+template <bool JAC>
 __global__ void __launch_bounds__(256)
 k_cg_update1(int64_t n, const double* __restrict__ p, const double* __restrict__ q,
              const double* __restrict__ dinv, double* __restrict__ x, double* __restrict__ r,
              double* __restrict__ z, int slot_rz, double* partials, unsigned int* counter, double* scal) {
     const double alpha = scal[slot_rz] / scal[S_PQ];
     double s[2] = {0.0, 0.0};
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    GRID_STRIDE(i, n) {
         x[i] += alpha * p[i];
         const double ri = r[i] - alpha * q[i];
-        const double zi = dinv[i] * ri;
-        r[i] = ri; z[i] = zi;
-        s[0] += ri * zi; s[1] += ri * ri;
+        r[i] = ri;
+        if (JAC) {
+            const double zi = dinv[i] * ri;
+            z[i] = zi;
+            s[0] += ri * zi;
+        }
+        s[1] += ri * ri;
     }
     __shared__ double red[2 * 8];
-    grid_sum<2, 256>(s, partials, counter, scal + S_PQ + 8, red);
+    grid_sum<2, 256>(s, partials, counter, scal + S_TMP, red);
 }
 
-__global__ void k_cg_update1_finish(double* scal, int slot_rz_new) {
-    scal[slot_rz_new] = scal[S_PQ + 8];
-    scal[S_RR] = scal[S_PQ + 9];
+__global__ void k_cg_update1_finish(double* scal, int slot_rz_new, int jac) {
+    if (jac) scal[slot_rz_new] = scal[S_TMP];
+    scal[S_RR] = scal[S_TMP + 1];
 }
 
-// beta = rz_new / rz ; p = z + beta p
+// beta = rz_new / rz ; p = z + beta p     (first = 1: p = z)
 __global__ void __launch_bounds__(256)
 k_cg_update2(int64_t n, const double* __restrict__ z, double* __restrict__ p, int slot_rz, int slot_rz_new,
-             const double* __restrict__ scal) {
-    const double beta = scal[slot_rz_new] / scal[slot_rz];
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        p[i] = z[i] + beta * p[i];
+             int first, const double* __restrict__ scal) {
+    const double beta = first ? 0.0 : scal[slot_rz_new] / scal[slot_rz];
+    GRID_STRIDE(i, n) p[i] = z[i] + beta * p[i];
 }
 
 __global__ void k_shift(int64_t n, double s, double* __restrict__ x) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        x[i] -= s;
+    GRID_STRIDE(i, n) x[i] -= s;
 }
 
 template <bool WITH_Y>
@@ -90,8 +131,7 @@ __global__ void __launch_bounds__(256)
 k_reduce(int64_t n, const double* __restrict__ x, const double* __restrict__ y, double* partials,
          unsigned int* counter, double* out) {
     double s[1] = {0.0};
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        s[0] += WITH_Y ? x[i] * y[i] : x[i];
+    GRID_STRIDE(i, n) s[0] += WITH_Y ? x[i] * y[i] : x[i];
     __shared__ double red[8];
     grid_sum<1, 256>(s, partials, counter, out, red);
 }
@@ -103,18 +143,120 @@ static int fetch(nsb_ctx* ctx, int slot, int count, cudaStream_t st) {
     return 0;
 }
 
-extern "C" int64_t nsb_cg_workspace_doubles(int64_t n) { return 4 * n; }
+// ---------------------------------------------------------------------------------------------
+// preconditioner application  z = M^-1 v   (scratch: 3 n doubles for Chebyshev)
+// ---------------------------------------------------------------------------------------------
+static int apply_pc(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* v, double* z,
+                    double* scratch, int64_t n, cudaStream_t st) {
+    const int G = krylov_grid(ctx, n);
+    if (M->kind == NSB_PC_NONE) {
+        NSB_CUDA(ctx, cudaMemcpyAsync(z, v, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
+        return 0;
+    }
+    if (M->kind == NSB_PC_JACOBI) {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_jacobi<<<G, 256, 0, st>>>(n, M->inv_diag, v, z);
+        NSB_LAUNCH_CHECK(ctx, "k_jacobi");
+        return 0;
+    }
+    // Chebyshev iteration on D^-1 A z = D^-1 v from z = 0 (Saad, Iterative Methods, Alg. 12.1)
+    double *r = scratch, *d = scratch + n, *q = scratch + 2 * n;
+    const double theta = 0.5 * (M->lambda_max + M->lambda_min), delta = 0.5 * (M->lambda_max - M->lambda_min);
+    const double sigma1 = theta / delta;
+    double rho_old = 1.0 / sigma1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cheb_first<<<G, 256, 0, st>>>(n, M->inv_diag, v, 1.0 / theta, r, d, z);
+        NSB_LAUNCH_CHECK(ctx, "k_cheb_first");
+    }
+    for (int k = 1; k < M->degree; ++k) {
+        if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st)) return -1;
+        const double rho = 1.0 / (2.0 * sigma1 - rho_old);
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cheb_step<<<G, 256, 0, st>>>(n, M->inv_diag, q, rho * rho_old, 2.0 * rho / delta, r, d, z);
+        NSB_LAUNCH_CHECK(ctx, "k_cheb_step");
+        rho_old = rho;
+    }
+    return 0;
+}
 
-extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, const double* b, double* x,
+static int check_pc(nsb_ctx* ctx, const nsb_precond* M) {
+    NSB_REQUIRE(ctx, M != nullptr, "null preconditioner");
+    NSB_REQUIRE(ctx, M->kind == NSB_PC_NONE || M->kind == NSB_PC_JACOBI || M->kind == NSB_PC_CHEBYSHEV,
+                "unknown preconditioner kind");
+    NSB_REQUIRE(ctx, M->kind == NSB_PC_NONE || M->inv_diag != nullptr, "preconditioner needs the inverse diagonal");
+    if (M->kind == NSB_PC_CHEBYSHEV)
+        NSB_REQUIRE(ctx, M->degree >= 1 && M->degree <= 64 && M->lambda_min > 0.0 && M->lambda_max > M->lambda_min,
+                    "Chebyshev needs 1 <= degree <= 64 and 0 < lambda_min < lambda_max");
+    return 0;
+}
+
+// ---- largest eigenvalue of D^-1 A by power iteration (upper end of the Chebyshev interval) ----
+__global__ void k_pi_init(int64_t n, double* __restrict__ v) {
+    GRID_STRIDE(i, n) {
+        uint32_t h = (uint32_t)i * 2654435761u;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        v[i] = 0.5 + (double)(h & 0xffffu) / 65536.0;
+    }
+}
+// v = (D^-1 q) * (1/sqrt(prev)) ; sum v^2
+__global__ void __launch_bounds__(256)
+k_pi_step(int64_t n, const double* __restrict__ dinv, const double* __restrict__ q, const double* prev2,
+          double* __restrict__ v, double* partials, unsigned int* counter, double* out) {
+    const double sc = prev2 ? 1.0 / sqrt(*prev2) : 1.0;
+    double s[1] = {0.0};
+    GRID_STRIDE(i, n) {
+        const double vi = dinv[i] * q[i] * sc;
+        v[i] = vi;
+        s[0] += vi * vi;
+    }
+    __shared__ double red[8];
+    grid_sum<1, 256>(s, partials, counter, out, red);
+}
+
+extern "C" int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters,
+                              double* work, double* lambda_out, void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, A && inv_diag && work && lambda_out && iters >= 1, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = (int64_t)A->nrows * A->bs;
+    const int G = krylov_grid(ctx, n);
+    double *v = work, *q = work + n;
+    double* ds = ctx->d_scalars;
+    k_pi_init<<<G, 256, 0, st>>>(n, v);
+    NSB_LAUNCH_CHECK(ctx, "k_pi_init");
+    // slots S_H1 / S_H1+1 alternate: ||v_k||^2 with v_k = D^-1 A v_{k-1} / ||v_{k-1}||
+    for (int k = 0; k <= iters; ++k) {
+        if (nsb_launch_spmv(ctx, A, v, q, nullptr, nullptr, st)) return -1;
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_pi_step<<<G, 256, 0, st>>>(n, inv_diag, q, k == 0 ? nullptr : ds + S_H1 + ((k - 1) & 1), v, ctx->d_partials,
+                                     ctx->d_counter, ds + S_H1 + (k & 1));
+        NSB_LAUNCH_CHECK(ctx, "k_pi_step");
+    }
+    // ||v_iters||^2 = || D^-1 A v_{iters-1} ||^2 / ||v_{iters-1}||^2   (the k = 0 step is unnormalised)
+    if (fetch(ctx, S_H1, 2, st)) return -1;
+    *lambda_out = sqrt(ctx->h_scalars[S_H1 + (iters & 1)]);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// CG
+// ---------------------------------------------------------------------------------------------
+extern "C" int64_t nsb_cg_workspace_doubles(int64_t n) { return 7 * n; }
+
+extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
                       double rtol, double atol, int32_t maxit, int32_t nullspace, double* work,
                       int32_t* iters_out, double* resid_out, void* stream) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
-    NSB_REQUIRE(ctx, A && dinv && b && x && work, "null argument");
+    NSB_REQUIRE(ctx, A && b && x && work, "null argument");
+    if (check_pc(ctx, M)) return -1;
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t n = (int64_t)A->nrows * A->bs;
-    double *r = work, *z = work + n, *p = work + 2 * n, *q = work + 3 * n;
+    double *r = work, *z = work + n, *p = work + 2 * n, *q = work + 3 * n, *scratch = work + 4 * n;
     double* ds = ctx->d_scalars;
     const int G = krylov_grid(ctx, n);
+    const bool jac = M->kind == NSB_PC_JACOBI;
+    const double* dinv = M->inv_diag;
     double shift = 0.0;
     if (nullspace) {
         {
@@ -126,29 +268,49 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, con
         shift = ctx->h_scalars[S_OUT] / (double)n;
     }
     if (nsb_launch_spmv(ctx, A, x, q, nullptr, nullptr, st)) return -1;
+    int cur = S_RZ0, nxt = S_RZ1;
     {
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-        k_cg_init<<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
-        k_cg_init_finish<<<1, 1, 0, st>>>(ds);
+        if (jac) k_cg_init<true><<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
+        else k_cg_init<false><<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
+        k_cg_init_finish<<<1, 1, 0, st>>>(ds, jac ? 1 : 0);
     }
     NSB_LAUNCH_CHECK(ctx, "k_cg_init");
     NSB_COUNT(ctx, 1);
+    if (!jac) {
+        if (apply_pc(ctx, A, M, r, z, scratch, n, st)) return -1;
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_reduce<true><<<G, 256, 0, st>>>(n, r, z, ctx->d_partials, ctx->d_counter, ds + cur);
+        k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, cur, 1, ds);
+        NSB_LAUNCH_CHECK(ctx, "k_cg_init(pc)");
+        NSB_COUNT(ctx, 1);
+    }
     if (fetch(ctx, S_RZ0, 5, st)) return -1;
     const double bnorm = sqrt(ctx->h_scalars[S_BB]);
     double rnorm = sqrt(ctx->h_scalars[S_RR]);
     const double tol = fmax(rtol * bnorm, atol);
     int it = 0;
-    int cur = S_RZ0, nxt = S_RZ1;
     while (rnorm > tol && it < maxit) {
         if (nsb_launch_spmv(ctx, A, p, q, p, ds + S_PQ, st)) return -1;
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-            k_cg_update1<<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
-            k_cg_update1_finish<<<1, 1, 0, st>>>(ds, nxt);
-            k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, nxt, ds);
+            if (jac) k_cg_update1<true><<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
+            else k_cg_update1<false><<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
+            k_cg_update1_finish<<<1, 1, 0, st>>>(ds, nxt, jac ? 1 : 0);
         }
-        NSB_LAUNCH_CHECK(ctx, "k_cg_update");
-        NSB_COUNT(ctx, 2);
+        NSB_LAUNCH_CHECK(ctx, "k_cg_update1");
+        NSB_COUNT(ctx, 1);
+        if (!jac) {
+            if (apply_pc(ctx, A, M, r, z, scratch, n, st)) return -1;
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_reduce<true><<<G, 256, 0, st>>>(n, r, z, ctx->d_partials, ctx->d_counter, ds + nxt);
+            NSB_LAUNCH_CHECK(ctx, "k_reduce(rz)");
+        }
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, nxt, 0, ds);
+        }
+        NSB_LAUNCH_CHECK(ctx, "k_cg_update2");
         if (fetch(ctx, S_RR, 1, st)) return -1;
         rnorm = sqrt(ctx->h_scalars[S_RR]);
         if (!(rnorm == rnorm)) return nsb_fail(ctx, "CG breakdown: residual is NaN%s%s");
@@ -176,7 +338,7 @@ __global__ void __launch_bounds__(256)
 k_residual(int64_t n, const double* __restrict__ b, const double* __restrict__ q, double* __restrict__ r,
            double* partials, unsigned int* counter, double* out) {
     double s[1] = {0.0};
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    GRID_STRIDE(i, n) {
         const double ri = b[i] - q[i];
         r[i] = ri;
         s[0] += ri * ri;
@@ -185,19 +347,14 @@ k_residual(int64_t n, const double* __restrict__ b, const double* __restrict__ q
     grid_sum<1, 256>(s, partials, counter, out, red);
 }
 
-// v = w / sqrt(scal[slot]) ; t = dinv * v   (next Arnoldi input, right preconditioning)
+// v = w / sqrt(*nrm2)
 __global__ void __launch_bounds__(256)
-k_normalize(int64_t n, const double* __restrict__ w, const double* __restrict__ nrm2, const double* __restrict__ dinv,
-            double* __restrict__ v, double* __restrict__ t) {
+k_normalize(int64_t n, const double* __restrict__ w, const double* __restrict__ nrm2, double* __restrict__ v) {
     const double inv = 1.0 / sqrt(*nrm2);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        const double vi = w[i] * inv;
-        v[i] = vi;
-        t[i] = dinv[i] * vi;
-    }
+    GRID_STRIDE(i, n) v[i] = w[i] * inv;
 }
 
-// h[k] = V_k . w for k in [k0, k0+NV)
+// h[k] = V_k . w for k in [k0, k0+nk), NV accumulators per thread: one pass over w per NV vectors
 template <int NV>
 __global__ void __launch_bounds__(256)
 k_multi_dot(int64_t n, int k0, int nk, const double* __restrict__ V, const double* __restrict__ w,
@@ -205,7 +362,7 @@ k_multi_dot(int64_t n, int k0, int nk, const double* __restrict__ V, const doubl
     double s[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) s[k] = 0.0;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    GRID_STRIDE(i, n) {
         const double wi = w[i];
 #pragma unroll
         for (int k = 0; k < NV; ++k)
@@ -220,7 +377,7 @@ __global__ void __launch_bounds__(256)
 k_multi_axpy(int64_t n, int nk, const double* __restrict__ V, const double* __restrict__ h,
              double* __restrict__ w, double* partials, unsigned int* counter, double* out) {
     double s[1] = {0.0};
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    GRID_STRIDE(i, n) {
         double wi = w[i];
         for (int k = 0; k < nk; ++k) wi -= h[k] * V[(int64_t)k * n + i];
         w[i] = wi;
@@ -230,39 +387,44 @@ k_multi_axpy(int64_t n, int nk, const double* __restrict__ V, const double* __re
     grid_sum<1, 256>(s, partials, counter, out, red);
 }
 
-// x += dinv * sum_k y[k] V_k
+// u = sum_k y[k] V_k
 __global__ void __launch_bounds__(256)
-k_gmres_update(int64_t n, int nk, const double* __restrict__ V, const double* __restrict__ y,
-               const double* __restrict__ dinv, double* __restrict__ x) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+k_combine(int64_t n, int nk, const double* __restrict__ V, const double* __restrict__ y, double* __restrict__ u) {
+    GRID_STRIDE(i, n) {
         double s = 0.0;
         for (int k = 0; k < nk; ++k) s += y[k] * V[(int64_t)k * n + i];
-        x[i] += dinv[i] * s;
+        u[i] = s;
     }
+}
+
+__global__ void __launch_bounds__(256)
+k_add(int64_t n, const double* __restrict__ t, double* __restrict__ x) {
+    GRID_STRIDE(i, n) x[i] += t[i];
 }
 
 #define NSB_GMRES_MAX_RESTART 60
 
-extern "C" int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart) { return (int64_t)(restart + 3) * n; }
+extern "C" int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart) { return (int64_t)(restart + 6) * n; }
 
-extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, const double* b, double* x,
+extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
                          double rtol, double atol, int32_t maxit, int32_t restart, double* work,
                          int32_t* iters_out, double* resid_out, void* stream) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
-    NSB_REQUIRE(ctx, A && dinv && b && x && work, "null argument");
+    NSB_REQUIRE(ctx, A && b && x && work, "null argument");
     NSB_REQUIRE(ctx, restart >= 1 && restart <= NSB_GMRES_MAX_RESTART, "restart must be in [1, 60]");
+    if (check_pc(ctx, M)) return -1;
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t n = (int64_t)A->nrows * A->bs;
     const int m = restart;
     double* V = work;                       // (m+1) x n
     double* w = work + (int64_t)(m + 1) * n;
     double* t = w + n;
+    double* scratch = t + n;                // 3 n (Chebyshev)
     double* ds = ctx->d_scalars;
     double* hs = ctx->h_scalars;
     const int G = krylov_grid(ctx, n);
     std::vector<double> H((size_t)(m + 1) * m, 0.0), cs(m), sn(m), g(m + 1), y(m);
 
-    // ||b||
     {
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_reduce<true><<<G, 256, 0, st>>>(n, b, b, ctx->d_partials, ctx->d_counter, ds + S_OUT);
@@ -287,27 +449,32 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, 
         if (rnorm <= tol || it >= maxit) break;
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-            k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, dinv, V, t);
+            k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, V);
         }
-        NSB_COUNT(ctx, 1);
+        NSB_LAUNCH_CHECK(ctx, "k_normalize");
         g.assign(m + 1, 0.0);
         g[0] = rnorm;
         int j = 0;
         for (; j < m && it < maxit; ++j) {
+            // w = A M^-1 v_j
+            if (apply_pc(ctx, A, M, V + (int64_t)j * n, t, scratch, n, st)) return -1;
             if (nsb_launch_spmv(ctx, A, t, w, nullptr, nullptr, st)) return -1;
             const int nk = j + 1;
-            nsb_timed_region* arnoldi = new nsb_timed_region(ctx, NSB_T_KRYLOV, st);
-            for (int pass = 0; pass < 2; ++pass) {   // CGS-2
-                double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
-                for (int k0 = 0; k0 < nk; k0 += 8) {
-                    const int c = nk - k0 < 8 ? nk - k0 : 8;
-                    k_multi_dot<8><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
-                    NSB_COUNT(ctx, 1);
+            {
+                NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+                for (int pass = 0; pass < 2; ++pass) {   // CGS-2
+                    double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
+                    for (int k0 = 0; k0 < nk; k0 += 16) {
+                        const int c = nk - k0 < 16 ? nk - k0 : 16;
+                        if (c <= 4) k_multi_dot<4><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
+                        else if (c <= 8) k_multi_dot<8><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
+                        else k_multi_dot<16><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
+                        NSB_COUNT(ctx, 1);
+                    }
+                    k_multi_axpy<<<G, 256, 0, st>>>(n, nk, V, hdev, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
                 }
-                k_multi_axpy<<<G, 256, 0, st>>>(n, nk, V, hdev, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+                k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, V + (int64_t)(j + 1) * n);
             }
-            k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, dinv, V + (int64_t)(j + 1) * n, t);
-            delete arnoldi;
             NSB_LAUNCH_CHECK(ctx, "gmres arnoldi");
             NSB_COUNT(ctx, 2);
             // one host round trip per iteration: h1, h2, ||w||^2
@@ -333,7 +500,7 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, 
             if (!(rnorm == rnorm)) return nsb_fail(ctx, "GMRES breakdown: NaN in the Arnoldi process%s%s");
             if (rnorm <= tol) { ++j; break; }
         }
-        // back substitution, x += Dinv V y
+        // back substitution, x += M^-1 (V y)
         const int nk = j;
         for (int i = nk - 1; i >= 0; --i) {
             double s = g[i];
@@ -344,9 +511,15 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const double* dinv, 
         NSB_CUDA(ctx, cudaMemcpyAsync(ds + S_Y, hs + S_Y, sizeof(double) * nk, cudaMemcpyHostToDevice, st));
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-            k_gmres_update<<<G, 256, 0, st>>>(n, nk, V, ds + S_Y, dinv, x);
+            k_combine<<<G, 256, 0, st>>>(n, nk, V, ds + S_Y, w);
         }
-        NSB_LAUNCH_CHECK(ctx, "k_gmres_update");
+        NSB_LAUNCH_CHECK(ctx, "k_combine");
+        if (apply_pc(ctx, A, M, w, t, scratch, n, st)) return -1;
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_add<<<G, 256, 0, st>>>(n, t, x);
+        }
+        NSB_LAUNCH_CHECK(ctx, "k_add");
         NSB_CUDA(ctx, cudaStreamSynchronize(st));   // hs[S_Y..] is reused next cycle
     }
     if (iters_out) *iters_out = it;

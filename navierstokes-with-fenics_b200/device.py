@@ -85,7 +85,7 @@ class Device:
                                          _ptr(self.cell_verts), sp.n_nodes, _ptr(self.cell_nodes)))
         self.patterns = {}
         self.coef = None
-        self.launches = 0
+        self._launch_hint = 0
         if mixed:
             self.pattern("WW")
         else:
@@ -158,26 +158,21 @@ class Device:
 
     # ---- assembly ---------------------------------------------------------------------------
     def assemble_ipcs_momentum(self, flags, ustar, un=None, unm1=None, pn=None, b=None, A=None):
-        self.launches += bin(flags & 3).count("1")
         self.check(self.lib.nsb_assemble_ipcs_momentum(self.ctx, flags, _ptr(ustar), _ptr(un), _ptr(unm1),
                                                        _ptr(pn), _ptr(b), _ptr(A), self.stream))
 
     def assemble_poisson(self, flags, pn=None, ustar=None, b=None, A=None):
-        self.launches += bin(flags & 3).count("1")
         self.check(self.lib.nsb_assemble_poisson(self.ctx, flags, _ptr(pn), _ptr(ustar), _ptr(b), _ptr(A),
                                                  self.stream))
 
     def assemble_correction(self, flags, ustar=None, pnew=None, pold=None, b=None, A=None):
-        self.launches += bin(flags & 3).count("1")
         self.check(self.lib.nsb_assemble_correction(self.ctx, flags, _ptr(ustar), _ptr(pnew), _ptr(pold),
                                                     _ptr(b), _ptr(A), self.stream))
 
     def assemble_p1_mass(self, flags, w=None, A=None):
-        self.launches += bin(flags & 3).count("1")
         self.check(self.lib.nsb_assemble_p1_mass(self.ctx, flags, _ptr(w), _ptr(A), self.stream))
 
     def assemble_mixed(self, flags, w0, w1=None, w2=None, b=None, A=None):
-        self.launches += 1
         self.check(self.lib.nsb_assemble_mixed(self.ctx, flags, _ptr(w0), _ptr(w1), _ptr(w2), _ptr(b), _ptr(A),
                                                self.stream))
 
@@ -190,46 +185,61 @@ class Device:
         if bc_dofs.numel() == 0:
             return
         pat = self.patterns[pattern]
-        self.launches += 1
         self.check(self.lib.nsb_bc_apply_matrix(self.ctx, kind, bs, _ptr(pat.rowptr), _ptr(pat.col), _ptr(vals),
                                                 bc_dofs.numel(), _ptr(bc_dofs), self.stream))
 
     def bc_apply_vector(self, mode, b, bc_dofs, bc_vals, x=None):
         if bc_dofs.numel() == 0:
             return
-        self.launches += 1
         self.check(self.lib.nsb_bc_apply_vector(self.ctx, mode, _ptr(b), _ptr(x), bc_dofs.numel(), _ptr(bc_dofs),
                                                 _ptr(bc_vals), self.stream))
 
     # ---- linear algebra ---------------------------------------------------------------------
     def spmv(self, A, x, y):
-        self.launches += 1
         self.check(self.lib.nsb_spmv(self.ctx, C.byref(A), _ptr(x), _ptr(y), self.stream))
 
     def inv_diagonal(self, A, out):
-        self.launches += 1
         self.check(self.lib.nsb_inv_diagonal(self.ctx, C.byref(A), _ptr(out), self.stream))
 
-    def cg(self, A, inv_diag, b, x, rtol=1e-12, atol=0.0, maxit=10000, nullspace=False, work=None):
+    def precond(self, inv_diag, kind=L.PC_JACOBI, degree=1, lambda_min=0.0, lambda_max=0.0):
+        """nsb_precond descriptor; a plain tensor passed to cg/gmres means Jacobi."""
+        m = L.Precond(kind, degree, inv_diag.data_ptr() if inv_diag is not None else None, lambda_min, lambda_max)
+        m._keep = inv_diag
+        return m
+
+    def _pc(self, M):
+        return M if isinstance(M, L.Precond) else self.precond(M)
+
+    def lambda_max(self, A, inv_diag, iters=12, work=None):
         n = A.nrows * A.bs
-        if work is None or work.numel() < 4 * n:
-            work = self.empty(self.lib.nsb_cg_workspace_doubles(n))
+        if work is None or work.numel() < 2 * n:
+            work = self.empty(2 * n)
+        out = C.c_double()
+        self.check(self.lib.nsb_lambda_max(self.ctx, C.byref(A), _ptr(inv_diag), iters, _ptr(work), C.byref(out),
+                                           self.stream))
+        return out.value
+
+    def cg(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=10000, nullspace=False, work=None):
+        n = A.nrows * A.bs
+        need = self.lib.nsb_cg_workspace_doubles(n)
+        if work is None or work.numel() < need:
+            work = self.empty(need)
         it, res = C.c_int32(), C.c_double()
-        st = self.lib.nsb_cg(self.ctx, C.byref(A), _ptr(inv_diag), _ptr(b), _ptr(x), rtol, atol, maxit,
+        M = self._pc(M)
+        st = self.lib.nsb_cg(self.ctx, C.byref(A), C.byref(M), _ptr(b), _ptr(x), rtol, atol, maxit,
                              1 if nullspace else 0, _ptr(work), C.byref(it), C.byref(res), self.stream)
-        self.launches += 4 + 4 * it.value
         self.check(st)
         return it.value, res.value
 
-    def gmres(self, A, inv_diag, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None):
+    def gmres(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None):
         n = A.nrows * A.bs
         need = self.lib.nsb_gmres_workspace_doubles(n, restart)
         if work is None or work.numel() < need:
             work = self.empty(need)
         it, res = C.c_int32(), C.c_double()
-        st = self.lib.nsb_gmres(self.ctx, C.byref(A), _ptr(inv_diag), _ptr(b), _ptr(x), rtol, atol, maxit, restart,
+        M = self._pc(M)
+        st = self.lib.nsb_gmres(self.ctx, C.byref(A), C.byref(M), _ptr(b), _ptr(x), rtol, atol, maxit, restart,
                                 _ptr(work), C.byref(it), C.byref(res), self.stream)
-        self.launches += 4 + 8 * it.value
         self.check(st)
         return it.value, res.value
 
@@ -237,16 +247,13 @@ class Device:
         self.check(self.lib.nsb_vec_copy(self.ctx, x.numel(), _ptr(x), _ptr(y), self.stream))
 
     def axpy(self, a, x, y):
-        self.launches += 1
         self.check(self.lib.nsb_vec_axpy(self.ctx, x.numel(), float(a), _ptr(x), _ptr(y), self.stream))
 
     def scale(self, a, x):
-        self.launches += 1
         self.check(self.lib.nsb_vec_scale(self.ctx, x.numel(), float(a), _ptr(x), self.stream))
 
     def dot(self, x, y):
         out = C.c_double()
-        self.launches += 1
         self.check(self.lib.nsb_vec_dot(self.ctx, x.numel(), _ptr(x), _ptr(y), C.byref(out), self.stream))
         return out.value
 
@@ -255,22 +262,22 @@ class Device:
 
     def sum(self, x):
         out = C.c_double()
-        self.launches += 1
         self.check(self.lib.nsb_vec_sum(self.ctx, x.numel(), _ptr(x), C.byref(out), self.stream))
         return out.value
 
     def scatter(self, idx, x, y):
-        self.launches += 1
         self.check(self.lib.nsb_vec_scatter(self.ctx, idx.numel(), _ptr(idx), _ptr(x), _ptr(y), self.stream))
 
     def gather(self, idx, x, y):
-        self.launches += 1
         self.check(self.lib.nsb_vec_gather(self.ctx, idx.numel(), _ptr(idx), _ptr(x), _ptr(y), self.stream))
 
     def ipcs_advance(self, u0, u1, u2, p, p_old):
-        self.launches += 1
         self.check(self.lib.nsb_ipcs_advance(self.ctx, u0.numel(), _ptr(u0), _ptr(u1), _ptr(u2), p.numel(), _ptr(p),
                                              _ptr(p_old), self.stream))
+
+    @property
+    def launches(self):
+        return self.launch_count()
 
     # ---- instrumentation --------------------------------------------------------------------
     def timer_enable(self, on=True):
