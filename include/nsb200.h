@@ -131,6 +131,14 @@ int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows,
                     const int32_t* rowptr_dev, const int32_t* col_dev,
                     const int32_t* pair_ptr_dev, const int32_t* pair_cell_dev,
                     const uint8_t* pair_iloc_dev, const uint8_t* pair_slots_dev);
+/* Row groups for the warp-cooperative assembly kernels (csrc/assemble_jac.cu): consecutive rows
+ * with <= max_pairs (row, cell) incidence pairs.  nsb_row_groups_build is host-only (group_row_host
+ * == NULL: count); nsb_set_row_groups registers the device copies plus pair_row[npairs] (row of
+ * every pair) and the longest row of the pattern.  Without them the generic kernels are used. */
+int nsb_row_groups_build(int32_t nrows, const int32_t* pair_ptr_host, int32_t max_pairs, int32_t* ngroups_out,
+                         int32_t* group_row_host);
+int nsb_set_row_groups(nsb_ctx* ctx, int32_t which, int32_t ngroups, const int32_t* group_row_dev,
+                       const int32_t* pair_row_dev, int32_t max_row_len);
 /* mixed Taylor-Hood dof map [ncells x (d*NL2 + d+1)] (source/ns_solver_base.py:501-524) */
 int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs_dev);
 /* scalars: dlfn.Constant.assign of k, alpha_i (source/ns_ipcs_solver.py:210-227,

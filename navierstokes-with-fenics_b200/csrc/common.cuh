@@ -18,6 +18,10 @@ struct nsb_pattern_dev {
     const int32_t* pair_cell = nullptr;
     const uint8_t* pair_iloc = nullptr;
     const uint8_t* pair_slots = nullptr;
+    // row groups of the warp-cooperative assembly kernels (nsb_set_row_groups)
+    int32_t ngroups = 0, max_row_len = 0;
+    const int32_t* group_row = nullptr;   // [ngroups+1] first row of every group
+    const int32_t* pair_row = nullptr;    // [npairs] row of every (row, cell) pair
 };
 
 struct nsb_coef {
@@ -59,7 +63,10 @@ struct nsb_ctx {
     nsb_timer_class timers[NSB_T_NCLASS];
 };
 
-int nsb_timer_flush(nsb_ctx* ctx);   // context.cu: fold finished event pairs into timers[].ms
+int nsb_timer_flush(nsb_ctx* ctx);
+// assemble_jac.cu: 0 = launched, 1 = not applicable (caller falls back), -1 = error
+int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass_coef, int newton, double* A_out,
+                                  cudaStream_t st);   // context.cu: fold finished event pairs into timers[].ms
 
 // RAII region: records a start/stop event pair on `st` around the launches of one kernel class
 struct nsb_timed_region {

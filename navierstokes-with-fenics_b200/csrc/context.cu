@@ -68,6 +68,17 @@ extern "C" int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows, const
     return 0;
 }
 
+extern "C" int nsb_set_row_groups(nsb_ctx* ctx, int32_t which, int32_t ngroups, const int32_t* group_row,
+                                  const int32_t* pair_row, int32_t max_row_len) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, which >= 0 && which < 3, "unknown pattern id");
+    NSB_REQUIRE(ctx, ngroups > 0 && group_row && pair_row && max_row_len > 0, "bad row-group arrays");
+    nsb_pattern_dev& P = ctx->pat[which];
+    NSB_REQUIRE(ctx, P.nrows > 0, "set the pattern before its row groups");
+    P.ngroups = ngroups; P.group_row = group_row; P.pair_row = pair_row; P.max_row_len = max_row_len;
+    return 0;
+}
+
 extern "C" int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, ndofs > 0 && cell_dofs, "bad mixed dofmap");

@@ -172,3 +172,23 @@ extern "C" int nsb_tiles_build(int32_t nrows, const int32_t* rowptr, int32_t max
     *ntiles_out = nt;
     return 0;
 }
+
+// ---- row groups of the warp-cooperative assembly kernels ------------------------------------------
+// Consecutive rows with at most max_pairs (row, cell) incidence pairs per group (a single row
+// with more pairs forms its own group).  group_row[ngroups + 1]; group_row == NULL only counts.
+extern "C" int nsb_row_groups_build(int32_t nrows, const int32_t* pair_ptr, int32_t max_pairs, int32_t* ngroups_out,
+                                    int32_t* group_row) {
+    if (!pair_ptr || nrows <= 0 || max_pairs < 1 || !ngroups_out)
+        return nsb_fail(nullptr, "nsb_row_groups_build: bad arguments%s%s");
+    int32_t ng = 0, r0 = 0;
+    while (r0 < nrows) {
+        int32_t r1 = r0 + 1;
+        while (r1 < nrows && pair_ptr[r1 + 1] - pair_ptr[r0] <= max_pairs) ++r1;
+        if (group_row) group_row[ng] = r0;
+        ++ng;
+        r0 = r1;
+    }
+    if (group_row) group_row[ng] = nrows;
+    *ngroups_out = ng;
+    return 0;
+}

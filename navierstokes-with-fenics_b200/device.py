@@ -42,6 +42,14 @@ class Pattern:
             lib.nsb_pattern_free(h)
         self.rowptr_host, self.col_host = rowptr, col
         self._dev, self._tiles = dev, {}
+        # row groups (<= 32 incidence pairs) + row of every pair: warp-cooperative assembly kernels
+        ng = C.c_int32()
+        L.check(lib.nsb_row_groups_build(nrows, pair_ptr.ctypes.data, 32, C.byref(ng), None))
+        group_row = np.empty(ng.value + 1, dtype=np.int32)
+        L.check(lib.nsb_row_groups_build(nrows, pair_ptr.ctypes.data, 32, C.byref(ng), group_row.ctypes.data))
+        pair_row = np.repeat(np.arange(nrows, dtype=np.int32), np.diff(pair_ptr))
+        self.ngroups = ng.value
+        self.group_row, self.pair_row = dev.upload(group_row), dev.upload(pair_row)
         up = dev.upload
         self.rowptr, self.col = up(rowptr), up(col)
         self.pair_ptr, self.pair_cell = up(pair_ptr), up(pair_cell)
@@ -137,6 +145,8 @@ class Device:
             self.check(self.lib.nsb_set_pattern(self.ctx, which, pat.nrows, _ptr(pat.rowptr), _ptr(pat.col),
                                                 _ptr(pat.pair_ptr), _ptr(pat.pair_cell), _ptr(pat.pair_iloc),
                                                 _ptr(pat.pair_slots)))
+            self.check(self.lib.nsb_set_row_groups(self.ctx, which, pat.ngroups, _ptr(pat.group_row),
+                                                   _ptr(pat.pair_row), pat.max_row))
             self.patterns[name] = pat
         return self.patterns[name]
 
