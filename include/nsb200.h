@@ -139,6 +139,10 @@ int nsb_row_groups_build(int32_t nrows, const int32_t* pair_ptr_host, int32_t ma
                          int32_t* group_row_host);
 int nsb_set_row_groups(nsb_ctx* ctx, int32_t which, int32_t ngroups, const int32_t* group_row_dev,
                        const int32_t* pair_row_dev, int32_t max_row_len);
+/* Caller-owned device workspace for the two-phase (element vectors per cell -> gather per row)
+ * vector assembly kernels; needs ncells * NL2 * d doubles.  Without it the one-thread-per-row
+ * kernels are used.  NULL / 0 unregisters. */
+int nsb_set_scratch(nsb_ctx* ctx, double* scratch_dev, int64_t ndoubles);
 /* mixed Taylor-Hood dof map [ncells x (d*NL2 + d+1)] (source/ns_solver_base.py:501-524) */
 int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs_dev);
 /* scalars: dlfn.Constant.assign of k, alpha_i (source/ns_ipcs_solver.py:210-227,

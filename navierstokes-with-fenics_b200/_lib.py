@@ -53,6 +53,7 @@ PROTOTYPES = {
     "nsb_set_pattern": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "nsb_row_groups_build": (C.c_int, [C.c_int32, vp, C.c_int32, c_i32p, vp]),
     "nsb_set_row_groups": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, C.c_int32]),
+    "nsb_set_scratch": (C.c_int, [vp, vp, C.c_int64]),
     "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),
     "nsb_set_coefficients": (C.c_int, [vp, c_f64p]),
     "nsb_assemble_ipcs_momentum": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp]),

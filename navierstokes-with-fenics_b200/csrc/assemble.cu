@@ -610,12 +610,16 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
     if (flags & NSB_VEC) {
         NSB_REQUIRE(ctx, ustar && un && unm1 && pn && b_out, "null vector argument");
         NSB_TIMED(ctx, NSB_T_ASM_RES, st);
+        const int tp = nsb_launch_residual_cells(ctx, ustar, un, unm1, pn, b_out, st);
+        if (tp < 0) return -1;
+        if (tp == 1) {
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_residual<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
                                                      ctx->cell_nodes, ustar, un, unm1, pn, cf, b_out)),
             (k_momentum_residual<3><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
                                                      ctx->cell_nodes, ustar, un, unm1, pn, cf, b_out)));
         NSB_LAUNCH_CHECK(ctx, "k_momentum_residual");
+        }
     }
     if (flags & NSB_MAT) {
         NSB_REQUIRE(ctx, ustar && A_out, "null matrix argument");

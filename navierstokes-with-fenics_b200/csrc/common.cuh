@@ -57,6 +57,9 @@ struct nsb_ctx {
     double* d_scalars = nullptr;      // [64] device-resident Krylov scalars
     unsigned int* d_counter = nullptr;
     double* h_scalars = nullptr;      // pinned [256]
+    // caller-owned workspace of the two-phase (cell -> row) assembly kernels (nsb_set_scratch)
+    double* scratch = nullptr;
+    int64_t scratch_doubles = 0;
     // instrumentation
     int64_t launch_count = 0;         // kernels launched by this context (all classes)
     bool timing = false;
@@ -65,6 +68,8 @@ struct nsb_ctx {
 
 int nsb_timer_flush(nsb_ctx* ctx);
 // assemble_jac.cu: 0 = launched, 1 = not applicable (caller falls back), -1 = error
+int nsb_launch_residual_cells(nsb_ctx* ctx, const double* ustar, const double* un, const double* unm1,
+                              const double* pn, double* b_out, cudaStream_t st);   // assemble_res.cu
 int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass_coef, int newton, double* A_out,
                                   cudaStream_t st);   // context.cu: fold finished event pairs into timers[].ms
 

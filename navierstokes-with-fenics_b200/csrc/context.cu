@@ -79,6 +79,13 @@ extern "C" int nsb_set_row_groups(nsb_ctx* ctx, int32_t which, int32_t ngroups, 
     return 0;
 }
 
+extern "C" int nsb_set_scratch(nsb_ctx* ctx, double* scratch, int64_t ndoubles) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, (scratch == nullptr) == (ndoubles == 0) && ndoubles >= 0, "bad scratch");
+    ctx->scratch = scratch; ctx->scratch_doubles = ndoubles;
+    return 0;
+}
+
 extern "C" int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, ndofs > 0 && cell_dofs, "bad mixed dofmap");

@@ -91,6 +91,8 @@ class Device:
         self.cell_nodes = self.upload(sp.cell_nodes)
         self.check(self.lib.nsb_set_mesh(self.ctx, sp.dim, mesh.num_vertices, _ptr(self.coords), mesh.num_cells,
                                          _ptr(self.cell_verts), sp.n_nodes, _ptr(self.cell_nodes)))
+        self.scratch = self.empty(mesh.num_cells * sp.nloc2 * sp.dim)
+        self.check(self.lib.nsb_set_scratch(self.ctx, _ptr(self.scratch), self.scratch.numel()))
         self.patterns = {}
         self.coef = None
         self._launch_hint = 0
