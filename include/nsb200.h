@@ -131,14 +131,20 @@ int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows,
                     const int32_t* rowptr_dev, const int32_t* col_dev,
                     const int32_t* pair_ptr_dev, const int32_t* pair_cell_dev,
                     const uint8_t* pair_iloc_dev, const uint8_t* pair_slots_dev);
-/* Row groups for the warp-cooperative assembly kernels (csrc/assemble_jac.cu): consecutive rows
- * with <= max_pairs (row, cell) incidence pairs.  nsb_row_groups_build is host-only (group_row_host
- * == NULL: count); nsb_set_row_groups registers the device copies plus pair_row[npairs] (row of
- * every pair) and the longest row of the pattern.  Without them the generic kernels are used. */
-int nsb_row_groups_build(int32_t nrows, const int32_t* pair_ptr_host, int32_t max_pairs, int32_t* ngroups_out,
-                         int32_t* group_row_host);
-int nsb_set_row_groups(nsb_ctx* ctx, int32_t which, int32_t ngroups, const int32_t* group_row_dev,
-                       const int32_t* pair_row_dev, int32_t max_row_len);
+/* Conflict-free scatter schedule of the warp-cooperative matrix assembly (csrc/assemble_jac.cu):
+ * rows grouped (<= 32 incidence pairs, <= max_blocks entries), and per chunk of 32 pairs a proper
+ * edge colouring of the (pair, entry) graph so that all lanes of a warp add into distinct entries
+ * in every round.  nsb_sched_build is host-only; call it with group_row_host == NULL to obtain
+ * counts3 = {groups, chunks, rounds}, then with buffers group_row[groups+1], chunk_first[groups+1],
+ * round_ptr[chunks+1], sched[32*rounds].  nsb_set_schedule registers the device copies
+ * (group_max_entries = the max_blocks used).  Without a schedule the generic kernels are used. */
+int nsb_sched_build(int32_t nrows, const int32_t* rowptr_host, const int32_t* pair_ptr_host,
+                    const uint8_t* pair_slots_host, int32_t nloc, int32_t max_blocks, int64_t* counts3,
+                    int32_t* group_row_host, int32_t* chunk_first_host, int32_t* round_ptr_host,
+                    uint16_t* sched_host);
+int nsb_set_schedule(nsb_ctx* ctx, int32_t which, int32_t ngroups, int32_t group_max_entries,
+                     const int32_t* group_row_dev, const int32_t* chunk_first_dev, const int32_t* round_ptr_dev,
+                     const uint16_t* sched_dev);
 /* Caller-owned device workspace for the two-phase (element vectors per cell -> gather per row)
  * vector assembly kernels; needs ncells * NL2 * d doubles.  Without it the one-thread-per-row
  * kernels are used.  NULL / 0 unregisters. */

@@ -13,6 +13,7 @@ CSR, BSR = 0, 1
 BC_LINEAR, BC_NEWTON = 0, 1
 # entries per TMA tile of the bulk-copy SpMV kernels, keyed by (matrix kind, bs) (csrc/spmv_tma.cuh)
 TILE_ENTRIES = {(BSR, 3): 384, (BSR, 2): 768}
+SCHED_MAX_BLOCKS = 160     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
 TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
                  "krylov_vec", "dirichlet", "vector")
 
@@ -51,8 +52,8 @@ PROTOTYPES = {
     "nsb_tiles_build": (C.c_int, [C.c_int32, vp, C.c_int32, c_i32p, vp]),
     "nsb_set_mesh": (C.c_int, [vp, C.c_int32, C.c_int32, vp, C.c_int32, vp, C.c_int32, vp]),
     "nsb_set_pattern": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
-    "nsb_row_groups_build": (C.c_int, [C.c_int32, vp, C.c_int32, c_i32p, vp]),
-    "nsb_set_row_groups": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, C.c_int32]),
+    "nsb_sched_build": (C.c_int, [C.c_int32, vp, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]),
+    "nsb_set_schedule": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp]),
     "nsb_set_scratch": (C.c_int, [vp, vp, C.c_int64]),
     "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),
     "nsb_set_coefficients": (C.c_int, [vp, c_f64p]),

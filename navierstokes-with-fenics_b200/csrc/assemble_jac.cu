@@ -6,19 +6,22 @@
 //   y_IM[k] = sum_L T_ILM z_L[k],  z_L[k] = detJ sum_i K[k][i] U_L[i]        
 //
 // Work unit = a "row group": consecutive rows (scalar P2 nodes) with at most 32 (row, cell)
-// incidence pairs (nsb_row_groups_build).  One warp per group:
-//   phase A  lane = pair: gather the cell, geometry, u*; evaluate in closed form the pair's
-//            scalar row S_I. (NL values) and the vertex velocity gradients (the Newton term),
-//            and park them in the warp's shared staging buffer.  Loops over the column index J
-//            and the vertex index M are fully unrolled against constexpr tables, so the zeros
+// incidence pairs and MAXB entries (nsb_sched_build).  One warp per group, lane = pair:
+//   phase A  gather the cell, geometry, u*; evaluate in closed form the pair's scalar row S_I.
+//            (NL values, parked in shared memory) and the scaled vertex velocity gradients
+//            g[b][a][M] = c_c detJ d_a u_b(x_M) (kept in REGISTERS).  Loops over the column index
+//            J and the vertex index M are fully unrolled against constexpr tables, so the zeros
 //            of the reference tensors cost nothing; only the row index I is a run-time index
-//            (tables in shared memory, no constant-cache serialisation).
-//   phase B  lane = (J, b): walk the pairs in order (ascending cell order inside a row = the
-//            summation order of dolfin's cell loop), form the d entries of block row b of
-//            block J and add them into the shared copy of the current matrix row; when the row
-//            changes the finished row is written out with fully coalesced stores.
+//            (tables in shared memory: no constant-cache serialisation).
+//   phase B  scheduled scatter: in round t the lane forms ONE d x d block (local column
+//            J = sched[t][lane]) as delta_ab S_J + sum_M T_IJM g[b][a][M] and adds it to the
+//            group's rows held in shared memory.  The host-built schedule is a proper edge
+//            colouring of the pair/entry graph: within a round all lanes hit distinct entries,
+//            so the shared-memory read-modify-writes need no atomics and the summation order
+//            is fixed.  Finally the group's rows -- one contiguous range of the BSR value
+//            array -- are written with fully coalesced stores.
 // Every value is written to global memory exactly once, by one warp, in a fixed order:
-// bit-reproducible, no atomics, no colouring, no read-modify-write traffic on HBM.
+// bit-reproducible, no atomics, no colouring of cells, no read-modify-write traffic on HBM.
 #define NSB_TABLE static __device__ constexpr
 #include "tables.h"
 #include "common.cuh"
@@ -46,13 +49,13 @@ template <int D>
 struct JacCfg {
     static constexpr int NL = CT<D>::NL, NV = D + 1, DD = D * D, NS = D * (D + 1) / 2;
     static constexpr int WARPS = 4;
-    static constexpr int MAXROW = (D == 3) ? 96 : 64;            // blocks in one row handled in shared memory
-    static constexpr int STAGE = NL + NV * DD + ((NL + NV * DD) % 2 == 0 ? 1 : 0);   // odd stride: conflict-free
-    // shared tables indexed by the run-time row index I
-    static constexpr int TAB_T = NL * NL * NV, TAB_M = NL * NL, TAB_D = NL * NL * NS;
+    static constexpr int MAXB = 160;                              // entries of one row group held in shared memory
+    static constexpr int SSTR = NL + 1 - (NL & 1);                // odd stride of the per-lane S rows: conflict-free
+    // shared tables indexed by the run-time row index I (T padded to 4 columns for 128-bit loads)
+    static constexpr int TAB_T = NL * NL * 4, TAB_M = NL * NL, TAB_D = NL * NL * NS;
     static constexpr int TAB = TAB_T + TAB_M + TAB_D;
-    static constexpr int PER_WARP = MAXROW * DD + 32 * STAGE;    // doubles
-    static constexpr size_t SMEM = sizeof(double) * (TAB + WARPS * PER_WARP) + WARPS * 32 * (NL + 8);
+    static constexpr int PER_WARP = MAXB * DD + 32 * SSTR + ((MAXB * DD + 32 * SSTR) & 1);   // doubles
+    static constexpr size_t SMEM = sizeof(double) * (TAB + WARPS * PER_WARP);
 };
 
 // symmetric index of (j,k), j <= k
@@ -62,30 +65,29 @@ __device__ constexpr int sym_index(int D, int j, int k) { return j * D - j * (j 
 
 template <int D>
 __global__ void __launch_bounds__(JacCfg<D>::WARPS * 32)
-k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, const int32_t* __restrict__ rowptr,
-                     const int32_t* __restrict__ pair_ptr, const int32_t* __restrict__ pair_row,
+k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, const int32_t* __restrict__ chunk_first,
+                     const int32_t* __restrict__ round_ptr, const uint16_t* __restrict__ sched,
+                     const int32_t* __restrict__ rowptr, const int32_t* __restrict__ pair_ptr,
                      const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
-                     const uint8_t* __restrict__ pair_slots, const double* __restrict__ coords,
-                     const int32_t* __restrict__ cell_nodes, const double* __restrict__ ustar, double mass_coef,
-                     double c_conv, double c_visc, int newton, double* __restrict__ vals) {
+                     const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
+                     const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc, int newton,
+                     double* __restrict__ vals) {
     using C = JacCfg<D>;
     using TB = CT<D>;
-    constexpr int NL = C::NL, NV = C::NV, DD = C::DD, NS = C::NS, STAGE = C::STAGE;
-    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int NL = C::NL, NV = C::NV, DD = C::DD, NS = C::NS, SSTR = C::SSTR;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* sT = reinterpret_cast<double*>(smem_raw);
     double* sM2 = sT + C::TAB_T;
     double* sD2 = sM2 + C::TAB_M;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     double* rowbuf = sD2 + C::TAB_D + (size_t)w * C::PER_WARP;
-    double* stage = rowbuf + C::MAXROW * DD;
-    uint8_t* sslot = reinterpret_cast<uint8_t*>(sT + C::TAB + C::WARPS * C::PER_WARP) + w * 32 * (NL + 8);
+    double* sS = rowbuf + C::MAXB * DD;
 
     // tables indexed by the run-time row index I -> shared memory
     for (int e = threadIdx.x; e < NL * NL; e += blockDim.x) {
         const int i = e / NL, j = e % NL;
         sM2[e] = TB::M2(i, j);
-        for (int m = 0; m < NV; ++m) sT[e * NV + m] = TB::T(i, j, m);
+        for (int m = 0; m < 4; ++m) sT[e * 4 + m] = m < NV ? TB::T(i, j, m) : 0.0;
         for (int a = 0; a < D; ++a)
             for (int b = a; b < D; ++b)
                 sD2[e * NS + sym_index(D, a, b)] = TB::D2(i, j, a, b) + (a < b ? TB::D2(i, j, b, a) : 0.0);
@@ -94,36 +96,38 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
 
     for (int32_t grp = blockIdx.x * C::WARPS + w; grp < ngroups; grp += gridDim.x * C::WARPS) {
         const int32_t row_lo = group_row[grp], row_hi = group_row[grp + 1];
+        const int32_t e_lo = rowptr[row_lo], nval = (rowptr[row_hi] - e_lo) * DD;
         const int32_t p_lo = pair_ptr[row_lo], p_hi = pair_ptr[row_hi];
-        int32_t cur = -1, cur_rp0 = 0, cur_len = 0;
-        for (int32_t chunk = p_lo; chunk < p_hi; chunk += 32) {
-            const int npc = min(32, p_hi - chunk);
-            const bool active = lane < npc;
-            const int32_t P = chunk + lane;
-            int32_t my_row = -1, my_rp0 = 0, my_len = 0;
+        const int32_t c_lo = chunk_first[grp], c_hi = chunk_first[grp + 1];
+        for (int e = lane; e < nval; e += 32) rowbuf[e] = 0.0;
+        for (int32_t ch = c_lo; ch < c_hi; ++ch) {
+            const int32_t q0 = p_lo + 32 * (ch - c_lo);
+            const int npc = min(32, p_hi - q0);
+            const int32_t r_lo = round_ptr[ch], r_hi = round_ptr[ch + 1];
+            unsigned e_next = r_lo < r_hi ? sched[(int64_t)r_lo * 32 + lane] : 0xFFFFu;
             int I = 0;
+            double g[DD][4];      // g[b*D+a][M] = c_c detJ d_a u_b (x_M), registers
+#pragma unroll
+            for (int i = 0; i < DD; ++i)
+#pragma unroll
+                for (int M = 0; M < 4; ++M) g[i][M] = 0.0;
             // ---------------------------------------------------------------- phase A: lane = pair
-            if (active) {
-                my_row = pair_row[P];
-                my_rp0 = rowptr[my_row];
-                my_len = rowptr[my_row + 1] - my_rp0;
+            if (lane < npc) {
+                const int32_t P = q0 + lane;
                 const int32_t c = pair_cell[P];
                 I = pair_iloc[P];
                 int32_t nodes[NL];
 #pragma unroll
                 for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
-#pragma unroll
-                for (int J = 0; J < NL; ++J) sslot[lane * (NL + 8) + J] = pair_slots[(int64_t)P * NL + J];
-                Geo<D> g;
-                cell_geometry(coords, nodes, g);
+                Geo<D> geo;
+                cell_geometry(coords, nodes, geo);
                 double U[NL][D];
 #pragma unroll
                 for (int L = 0; L < NL; ++L)
 #pragma unroll
                     for (int b = 0; b < D; ++b) U[L][b] = ustar[(int64_t)D * nodes[L] + b];
-                double* st = stage + lane * STAGE;
                 if (newton) {
-                    const double f = c_conv * g.detJ;
+                    const double f = c_conv * geo.detJ;
 #pragma unroll
                     for (int M = 0; M < NV; ++M) {
                         double ref[D][D];   // ref[b][k] = sum_L U_Lb dhat_k phi_L(x_M)
@@ -145,8 +149,8 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                             for (int a = 0; a < D; ++a) {
                                 double s = 0.0;
 #pragma unroll
-                                for (int k = 0; k < D; ++k) s += ref[b][k] * g.K[k][a];
-                                st[NL + M * DD + b * D + a] = f * s;
+                                for (int k = 0; k < D; ++k) s += ref[b][k] * geo.K[k][a];
+                                g[b * D + a][M] = f * s;
                             }
                     }
                 }
@@ -156,7 +160,7 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                 for (int M = 0; M < NV; ++M)
 #pragma unroll
                     for (int k = 0; k < D; ++k) y[M][k] = 0.0;
-                const double* tI = sT + I * NL * NV;
+                const double* tI = sT + I * NL * 4;
 #pragma unroll
                 for (int L = 0; L < NL; ++L) {
                     double z[D];
@@ -164,21 +168,22 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                     for (int k = 0; k < D; ++k) {
                         double s = 0.0;
 #pragma unroll
-                        for (int i = 0; i < D; ++i) s += g.K[k][i] * U[L][i];
-                        z[k] = s * g.detJ;
+                        for (int i = 0; i < D; ++i) s += geo.K[k][i] * U[L][i];
+                        z[k] = s * geo.detJ;
                     }
 #pragma unroll
                     for (int M = 0; M < NV; ++M) {
-                        const double t = tI[L * NV + M];
+                        const double t = tI[L * 4 + M];
 #pragma unroll
                         for (int k = 0; k < D; ++k) y[M][k] += t * z[k];
                     }
                 }
                 double G[D][D];
-                metric<D>(g, G);
-                const double mcd = mass_coef * g.detJ;
+                metric<D>(geo, G);
+                const double mcd = mass_coef * geo.detJ;
                 const double* mI = sM2 + I * NL;
                 const double* dI = sD2 + I * NL * NS;
+                double* st = sS + lane * SSTR;
 #pragma unroll
                 for (int J = 0; J < NL; ++J) {
                     double vis = 0.0;
@@ -196,60 +201,46 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                 }
             }
             __syncwarp();
-            // ---------------------------------------------------------------- phase B: lane = (J, b)
-            const int J = lane / D, b = lane - J * D;
-            for (int q = 0; q < npc; ++q) {
-                const int32_t rq = __shfl_sync(FULL, my_row, q);
-                if (rq != cur) {
-                    if (cur >= 0) {      // finished row: coalesced write-out, exactly once
-                        double* dst = vals + (int64_t)cur_rp0 * DD;
-                        for (int e = lane; e < cur_len * DD; e += 32) dst[e] = rowbuf[e];
-                    }
-                    cur = rq;
-                    cur_rp0 = __shfl_sync(FULL, my_rp0, q);
-                    cur_len = __shfl_sync(FULL, my_len, q);
-                    for (int e = lane; e < cur_len * DD; e += 32) rowbuf[e] = 0.0;
-                    __syncwarp();
-                }
-                const int Iq = __shfl_sync(FULL, I, q);
-                if (lane < NL * D) {
-                    const double* st = stage + q * STAGE;
-                    double v[D];
-                    const double S = st[J];
+            // ---------------------------------------------------------------- phase B: scheduled scatter
+            const double* myS = sS + lane * SSTR;
+            const double* myT = sT + I * NL * 4;
+            for (int32_t t = r_lo; t < r_hi; ++t) {
+                const unsigned e = e_next;
+                if (t + 1 < r_hi) e_next = sched[(int64_t)(t + 1) * 32 + lane];
+                if (e != 0xFFFFu) {
+                    const int J = e & 15u;
+                    double* dst = rowbuf + (e >> 4) * DD;
+                    const double S = myS[J];
+                    const double2 t01 = *reinterpret_cast<const double2*>(myT + J * 4);
+                    const double2 t23 = *reinterpret_cast<const double2*>(myT + J * 4 + 2);
 #pragma unroll
-                    for (int a = 0; a < D; ++a) v[a] = (a == b) ? S : 0.0;
-                    if (newton) {
-                        const double* t = sT + (Iq * NL + J) * NV;
+                    for (int b = 0; b < D; ++b)
 #pragma unroll
-                        for (int M = 0; M < NV; ++M) {
-                            const double tm = t[M];
-#pragma unroll
-                            for (int a = 0; a < D; ++a) v[a] += tm * st[NL + M * DD + b * D + a];
+                        for (int a = 0; a < D; ++a) {
+                            const double* gi = g[b * D + a];
+                            double v = (t01.x * gi[0] + t01.y * gi[1]) + (t23.x * gi[2] + t23.y * gi[3]);
+                            if (a == b) v += S;
+                            dst[b * D + a] += v;
                         }
-                    }
-                    double* dst = rowbuf + (int)sslot[q * (NL + 8) + J] * DD + b * D;
-#pragma unroll
-                    for (int a = 0; a < D; ++a) dst[a] += v[a];
                 }
                 __syncwarp();
             }
         }
-        if (cur >= 0) {
-            double* dst = vals + (int64_t)cur_rp0 * DD;
-            for (int e = lane; e < cur_len * DD; e += 32) dst[e] = rowbuf[e];
-        }
+        // the group's rows: one contiguous range of the value array, written once, coalesced
+        double* out = vals + (int64_t)e_lo * DD;
+        for (int e = lane; e < nval; e += 32) out[e] = rowbuf[e];
         __syncwarp();
     }
 }
-
 // launcher used by nsb_assemble_ipcs_momentum (assemble.cu); returns 1 when the row-group path
-// does not apply (groups not registered / a row longer than the shared row buffer) so that the
+// does not apply (scatter schedule not registered or a row longer than the shared row buffer) so that the
 // caller keeps the generic one-thread-per-row kernel.
 template <int D>
 static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double* ustar, double mass_coef,
                             int newton, double* A_out, cudaStream_t st) {
     using C = JacCfg<D>;
-    if (!P.group_row || !P.pair_row || P.ngroups <= 0 || P.max_row_len > C::MAXROW) return 1;
+    if (!P.group_row || !P.chunk_first || !P.round_ptr || !P.sched || P.ngroups <= 0 || P.group_max_entries > C::MAXB)
+        return 1;
     static bool configured = false;
     if (!configured) {
         NSB_CUDA(ctx, cudaFuncSetAttribute(k_jacobian_rowgroups<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
@@ -263,8 +254,8 @@ static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double
     const int64_t need = ((int64_t)P.ngroups + C::WARPS - 1) / C::WARPS;
     if (blocks > need) blocks = need;
     k_jacobian_rowgroups<D><<<(int)blocks, C::WARPS * 32, C::SMEM, st>>>(
-        P.ngroups, P.group_row, P.rowptr, P.pair_ptr, P.pair_row, P.pair_cell, P.pair_iloc, P.pair_slots, ctx->coords,
-        ctx->cell_nodes, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
+        P.ngroups, P.group_row, P.chunk_first, P.round_ptr, P.sched, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
+        ctx->coords, ctx->cell_nodes, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
     NSB_LAUNCH_CHECK(ctx, "k_jacobian_rowgroups");
     return 0;
 }

@@ -18,10 +18,12 @@ struct nsb_pattern_dev {
     const int32_t* pair_cell = nullptr;
     const uint8_t* pair_iloc = nullptr;
     const uint8_t* pair_slots = nullptr;
-    // row groups of the warp-cooperative assembly kernels (nsb_set_row_groups)
-    int32_t ngroups = 0, max_row_len = 0;
-    const int32_t* group_row = nullptr;   // [ngroups+1] first row of every group
-    const int32_t* pair_row = nullptr;    // [npairs] row of every (row, cell) pair
+    // scatter schedule of the warp-cooperative matrix assembly (nsb_sched_build / nsb_set_schedule)
+    int32_t ngroups = 0, group_max_entries = 0;
+    const int32_t* group_row = nullptr;     // [ngroups+1]
+    const int32_t* chunk_first = nullptr;   // [ngroups+1]
+    const int32_t* round_ptr = nullptr;     // [nchunks+1]
+    const uint16_t* sched = nullptr;        // [32 * nrounds]
 };
 
 struct nsb_coef {

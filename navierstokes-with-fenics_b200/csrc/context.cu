@@ -68,14 +68,17 @@ extern "C" int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows, const
     return 0;
 }
 
-extern "C" int nsb_set_row_groups(nsb_ctx* ctx, int32_t which, int32_t ngroups, const int32_t* group_row,
-                                  const int32_t* pair_row, int32_t max_row_len) {
+extern "C" int nsb_set_schedule(nsb_ctx* ctx, int32_t which, int32_t ngroups, int32_t group_max_entries,
+                                const int32_t* group_row, const int32_t* chunk_first, const int32_t* round_ptr,
+                                const uint16_t* sched) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, which >= 0 && which < 3, "unknown pattern id");
-    NSB_REQUIRE(ctx, ngroups > 0 && group_row && pair_row && max_row_len > 0, "bad row-group arrays");
+    NSB_REQUIRE(ctx, ngroups > 0 && group_max_entries > 0 && group_row && chunk_first && round_ptr && sched,
+                "bad schedule arrays");
     nsb_pattern_dev& P = ctx->pat[which];
-    NSB_REQUIRE(ctx, P.nrows > 0, "set the pattern before its row groups");
-    P.ngroups = ngroups; P.group_row = group_row; P.pair_row = pair_row; P.max_row_len = max_row_len;
+    NSB_REQUIRE(ctx, P.nrows > 0, "set the pattern before its schedule");
+    P.ngroups = ngroups; P.group_max_entries = group_max_entries; P.group_row = group_row;
+    P.chunk_first = chunk_first; P.round_ptr = round_ptr; P.sched = sched;
     return 0;
 }
 

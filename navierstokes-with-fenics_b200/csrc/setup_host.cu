@@ -173,22 +173,106 @@ extern "C" int nsb_tiles_build(int32_t nrows, const int32_t* rowptr, int32_t max
     return 0;
 }
 
-// ---- row groups of the warp-cooperative assembly kernels ------------------------------------------
-// Consecutive rows with at most max_pairs (row, cell) incidence pairs per group (a single row
-// with more pairs forms its own group).  group_row[ngroups + 1]; group_row == NULL only counts.
-extern "C" int nsb_row_groups_build(int32_t nrows, const int32_t* pair_ptr, int32_t max_pairs, int32_t* ngroups_out,
-                                    int32_t* group_row) {
-    if (!pair_ptr || nrows <= 0 || max_pairs < 1 || !ngroups_out)
-        return nsb_fail(nullptr, "nsb_row_groups_build: bad arguments%s%s");
-    int32_t ng = 0, r0 = 0;
-    while (r0 < nrows) {
+// ---- conflict-free scatter schedule of the warp-cooperative matrix assembly (assemble_jac.cu) -----
+// Rows are grouped (consecutive rows, <= 32 incidence pairs and <= max_blocks entries per group; a
+// bigger single row forms its own group and is processed in chunks of 32 pairs).  In a chunk, lane
+// q owns pair q and must add its nloc local columns into the shared copy of the group's rows.  The
+// schedule orders these additions in ROUNDS such that within a round all lanes hit distinct entries
+// (a proper edge colouring of the bipartite pair/entry graph): no atomics, fixed summation order.
+//   group_row[ng+1]    first row of every group
+//   chunk_first[ng+1]  first chunk of every group (chunk c covers pairs pair_ptr[row_lo] + 32 (c - first) ...)
+//   round_ptr[nc+1]    first round of every chunk
+//   sched[32 * rounds] per (round, lane): entry index inside the group << 4 | local column, 0xFFFF = idle
+// Call with group_row == NULL to count (ngroups, nchunks, nrounds), then again to fill.
+extern "C" int nsb_sched_build(int32_t nrows, const int32_t* rowptr, const int32_t* pair_ptr,
+                               const uint8_t* pair_slots, int32_t nloc, int32_t max_blocks, int64_t* counts3,
+                               int32_t* group_row, int32_t* chunk_first, int32_t* round_ptr, uint16_t* sched) {
+    if (!rowptr || !pair_ptr || !pair_slots || !counts3 || nrows <= 0 || nloc <= 0 || nloc > 15 || max_blocks < 1 ||
+        max_blocks > 4095)
+        return nsb_fail(nullptr, "nsb_sched_build: bad arguments%s%s");
+    // pass 1: groups
+    std::vector<int32_t> grow;
+    for (int32_t r0 = 0; r0 < nrows;) {
         int32_t r1 = r0 + 1;
-        while (r1 < nrows && pair_ptr[r1 + 1] - pair_ptr[r0] <= max_pairs) ++r1;
-        if (group_row) group_row[ng] = r0;
-        ++ng;
+        while (r1 < nrows && pair_ptr[r1 + 1] - pair_ptr[r0] <= 32 && rowptr[r1 + 1] - rowptr[r0] <= max_blocks) ++r1;
+        if (rowptr[r1] - rowptr[r0] > 4095) return nsb_fail(nullptr, "nsb_sched_build: row too long%s%s");
+        grow.push_back(r0);
         r0 = r1;
     }
-    if (group_row) group_row[ng] = nrows;
-    *ngroups_out = ng;
+    grow.push_back(nrows);
+    const int32_t ng = (int32_t)grow.size() - 1;
+    std::vector<int32_t> cfirst((size_t)ng + 1, 0);
+    for (int32_t g = 0; g < ng; ++g) {
+        const int32_t np = pair_ptr[grow[g + 1]] - pair_ptr[grow[g]];
+        cfirst[g + 1] = cfirst[g] + (np + 31) / 32;
+    }
+    const int32_t nc = cfirst[ng];
+    // pass 2: colour every chunk (greedy: entries by descending degree, smallest round free at lane and entry)
+    std::vector<int32_t> nround((size_t)nc, 0);
+    std::vector<std::vector<uint16_t>> tmp;
+    const bool fill = group_row != nullptr;
+    if (fill) tmp.resize((size_t)nc);
+#pragma omp parallel
+    {
+        std::vector<int32_t> ent, lane_of, col_of, order, deg;
+        std::vector<uint64_t> lane_busy, ent_busy;   // bitsets over rounds (<= 64 x words)
+        std::vector<uint16_t> buf;
+#pragma omp for schedule(dynamic, 256)
+        for (int32_t g = 0; g < ng; ++g) {
+            const int32_t row_lo = grow[g], row_hi = grow[g + 1];
+            const int32_t p_lo = pair_ptr[row_lo], p_hi = pair_ptr[row_hi], e_lo = rowptr[row_lo];
+            const int32_t nent = rowptr[row_hi] - e_lo;
+            int32_t row = row_lo;
+            for (int32_t c = cfirst[g]; c < cfirst[g + 1]; ++c) {
+                const int32_t q0 = p_lo + 32 * (c - cfirst[g]), q1 = std::min(p_hi, q0 + 32);
+                const int32_t nedge = (q1 - q0) * nloc;
+                ent.resize(nedge); lane_of.resize(nedge); col_of.resize(nedge);
+                deg.assign((size_t)nent, 0);
+                int32_t k = 0;
+                for (int32_t p = q0; p < q1; ++p) {
+                    while (pair_ptr[row + 1] <= p) ++row;
+                    for (int32_t j = 0; j < nloc; ++j, ++k) {
+                        ent[k] = rowptr[row] - e_lo + pair_slots[(size_t)p * nloc + j];
+                        lane_of[k] = p - q0; col_of[k] = j;
+                        deg[ent[k]]++;
+                    }
+                }
+                order.resize(nedge);
+                for (int32_t i = 0; i < nedge; ++i) order[i] = i;
+                std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return deg[ent[a]] > deg[ent[b]]; });
+                const int W = 4;   // up to 256 rounds
+                lane_busy.assign(32 * W, 0); ent_busy.assign((size_t)nent * W, 0);
+                int32_t rounds = 0;
+                std::vector<uint16_t>* out = fill ? &buf : nullptr;
+                if (out) out->assign((size_t)32 * 256, 0xFFFFu);
+                for (int32_t i = 0; i < nedge; ++i) {
+                    const int32_t e = order[i];
+                    int32_t t = -1;
+                    for (int wv = 0; wv < W && t < 0; ++wv) {
+                        const uint64_t freebits = ~(lane_busy[lane_of[e] * W + wv] | ent_busy[(size_t)ent[e] * W + wv]);
+                        if (freebits) t = wv * 64 + __builtin_ctzll(freebits);
+                    }
+                    if (t < 0) t = 255;   // cannot happen: degree <= 255
+                    lane_busy[lane_of[e] * W + t / 64] |= 1ull << (t % 64);
+                    ent_busy[(size_t)ent[e] * W + t / 64] |= 1ull << (t % 64);
+                    if (t + 1 > rounds) rounds = t + 1;
+                    if (out) (*out)[(size_t)t * 32 + lane_of[e]] = (uint16_t)((ent[e] << 4) | col_of[e]);
+                }
+                nround[c] = rounds;
+                if (out) tmp[c].assign(buf.begin(), buf.begin() + (size_t)rounds * 32);
+            }
+        }
+    }
+    int64_t total = 0;
+    for (int32_t c = 0; c < nc; ++c) total += nround[c];
+    counts3[0] = ng; counts3[1] = nc; counts3[2] = total;
+    if (!fill) return 0;
+    if (!chunk_first || !round_ptr || !sched) return nsb_fail(nullptr, "nsb_sched_build: null output%s%s");
+    memcpy(group_row, grow.data(), sizeof(int32_t) * ((size_t)ng + 1));
+    memcpy(chunk_first, cfirst.data(), sizeof(int32_t) * ((size_t)ng + 1));
+    round_ptr[0] = 0;
+    for (int32_t c = 0; c < nc; ++c) round_ptr[c + 1] = round_ptr[c] + nround[c];
+#pragma omp parallel for schedule(static, 1024)
+    for (int32_t c = 0; c < nc; ++c) memcpy(sched + (size_t)round_ptr[c] * 32, tmp[c].data(), sizeof(uint16_t) * tmp[c].size());
     return 0;
 }

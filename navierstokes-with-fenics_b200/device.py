@@ -42,14 +42,19 @@ class Pattern:
             lib.nsb_pattern_free(h)
         self.rowptr_host, self.col_host = rowptr, col
         self._dev, self._tiles = dev, {}
-        # row groups (<= 32 incidence pairs) + row of every pair: warp-cooperative assembly kernels
-        ng = C.c_int32()
-        L.check(lib.nsb_row_groups_build(nrows, pair_ptr.ctypes.data, 32, C.byref(ng), None))
-        group_row = np.empty(ng.value + 1, dtype=np.int32)
-        L.check(lib.nsb_row_groups_build(nrows, pair_ptr.ctypes.data, 32, C.byref(ng), group_row.ctypes.data))
-        pair_row = np.repeat(np.arange(nrows, dtype=np.int32), np.diff(pair_ptr))
-        self.ngroups = ng.value
-        self.group_row, self.pair_row = dev.upload(group_row), dev.upload(pair_row)
+        self.sched = None
+        if nlc <= 15 and nlr == nlc:
+            # conflict-free scatter schedule of the warp-cooperative matrix assembly
+            cnt = (C.c_int64 * 3)()
+            a_ = (nrows, rowptr.ctypes.data, pair_ptr.ctypes.data, pair_slots.ctypes.data, nlc, L.SCHED_MAX_BLOCKS)
+            if lib.nsb_sched_build(*a_, cnt, None, None, None, None) == 0:
+                g_row, c_first = np.empty(cnt[0] + 1, np.int32), np.empty(cnt[0] + 1, np.int32)
+                r_ptr, sched = np.empty(cnt[1] + 1, np.int32), np.empty(32 * cnt[2], np.uint16)
+                L.check(lib.nsb_sched_build(*a_, cnt, g_row.ctypes.data, c_first.ctypes.data, r_ptr.ctypes.data,
+                                            sched.ctypes.data))
+                # uint16 travels as int16 bit patterns (torch has no uint16 arithmetic, none is needed)
+                self.sched = (int(cnt[0]), dev.upload(g_row), dev.upload(c_first), dev.upload(r_ptr),
+                              dev.upload(sched.view(np.int16)))
         up = dev.upload
         self.rowptr, self.col = up(rowptr), up(col)
         self.pair_ptr, self.pair_cell = up(pair_ptr), up(pair_cell)
@@ -147,8 +152,10 @@ class Device:
             self.check(self.lib.nsb_set_pattern(self.ctx, which, pat.nrows, _ptr(pat.rowptr), _ptr(pat.col),
                                                 _ptr(pat.pair_ptr), _ptr(pat.pair_cell), _ptr(pat.pair_iloc),
                                                 _ptr(pat.pair_slots)))
-            self.check(self.lib.nsb_set_row_groups(self.ctx, which, pat.ngroups, _ptr(pat.group_row),
-                                                   _ptr(pat.pair_row), pat.max_row))
+            if pat.sched is not None:
+                ng, g_row, c_first, r_ptr, sched = pat.sched
+                self.check(self.lib.nsb_set_schedule(self.ctx, which, ng, L.SCHED_MAX_BLOCKS, _ptr(g_row),
+                                                     _ptr(c_first), _ptr(r_ptr), _ptr(sched)))
             self.patterns[name] = pat
         return self.patterns[name]
 
