@@ -64,7 +64,7 @@ __device__ constexpr int sym_index(int D, int j, int k) { return j * D - j * (j 
 }  // namespace
 
 template <int D>
-__global__ void __launch_bounds__(JacCfg<D>::WARPS * 32)
+__global__ void __launch_bounds__(JacCfg<D>::WARPS * 32, 3)
 k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, const int32_t* __restrict__ chunk_first,
                      const int32_t* __restrict__ round_ptr, const uint16_t* __restrict__ sched,
                      const int32_t* __restrict__ rowptr, const int32_t* __restrict__ pair_ptr,
