@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="nsb200", choices=["nsb200", "reference"])
-    ap.add_argument("--n", type=int, default=73, help="cells per edge of the unit cube (73 -> 9.93 M DOF)")
+    ap.add_argument("--n", "--cells", dest="n", type=int, default=73, help="cells per edge of the unit cube (73 -> 9.93 M DOF)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 

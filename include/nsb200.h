@@ -66,7 +66,13 @@ typedef struct nsb_pattern_builder nsb_pattern_builder;
 #define NSB_T_KRYLOV 6       /* Krylov vector kernels: fused updates, dots, Arnoldi (K11) */
 #define NSB_T_BC 7           /* Dirichlet rows (K9)                                  */
 #define NSB_T_VEC 8          /* vector ops, history shift, gather/scatter (K13, K15) */
-#define NSB_T_NCLASS 9
+#define NSB_T_COMM 9         /* halo pack + NCCL send/recv, NCCL all-reduce (K14)    */
+#define NSB_T_NCLASS 10
+
+/* index spaces with a halo plan (nsb_set_halo, nsb_matrix.halo) */
+#define NSB_HALO_NONE 0
+#define NSB_HALO_NODES 1     /* scalar P2 nodes (velocity vectors: bs = d)             */
+#define NSB_HALO_VERTS 2     /* vertices (pressure vectors)                            */
 
 typedef struct nsb_matrix {
     int32_t kind;            /* NSB_CSR | NSB_BSR                                        */
@@ -81,7 +87,9 @@ typedef struct nsb_matrix {
     const uint32_t* tiles;   /* dev [ntiles*64] or NULL: TMA row tiles of this pattern
                                 (nsb_tiles_build); enables the bulk-copy SpMV kernels       */
     int32_t ntiles;
-    int32_t reserved;
+    int32_t halo;            /* NSB_HALO_*: index space of the columns on a partitioned mesh.  Rows
+                                are the owned prefix; columns >= n_owned are ghosts, refreshed
+                                from their owners inside nsb_spmv / the Krylov solvers.  0 on one GPU */
 } nsb_matrix;
 
 /* preconditioners of nsb_cg / nsb_gmres (K12) */
@@ -227,6 +235,31 @@ int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x,
  * u2 <- u1 <- u0 ; p_old <- p */
 int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, double* u2,
                      int64_t nq, const double* p, double* p_old, void* stream);
+
+/* ---------------------------------------------------------------- multi-GPU (K14) -------- */
+/* Mesh-partitioned runs, one rank per GPU (the reference has no counterpart: it
+ * would be dolfin/PETSc MPI, which source/ never exercises).  Each rank registers its LOCAL mesh
+ * (owned cells + one ghost layer) with nsb_set_mesh, patterns whose rows are the owned prefix of
+ * the owned-first local numbering, and one halo plan per index space.  Vectors handed to the
+ * assembly calls hold [owned | ghost] entries; nsb_halo_exchange refreshes the ghost block from
+ * the owners.  nsb_spmv / nsb_cg / nsb_gmres / nsb_lambda_max refresh the ghosts of their
+ * operand themselves (matrix.halo) and all-reduce every inner product, nsb_vec_dot / _sum
+ * all-reduce their result.  NCCL (libnccl.so.2, the copy torch loads) is bound at run time. */
+int nsb_comm_unique_id(uint8_t* id_out128);                      /* ncclGetUniqueId (rank 0) */
+int nsb_comm_init(nsb_ctx* ctx, int32_t rank, int32_t nranks, const uint8_t* id128);
+/* which = NSB_HALO_*; peers/send_ptr/recv_ptr are host arrays ([npeers], [npeers+1], [npeers+1]):
+ * ghost slots recv_ptr[i]..recv_ptr[i+1] (offsets into the ghost block) come from peers[i];
+ * send_idx_dev[send_ptr[i]..send_ptr[i+1]] are the local owned indices peers[i] needs, in the
+ * order of its ghost slots.  sendbuf_dev [3*send_ptr[npeers]] and ghostbuf_dev [3*n_ghost] are
+ * caller-owned scratch.  n_global = size of the index space over all ranks. */
+int nsb_set_halo(nsb_ctx* ctx, int32_t which, int32_t n_owned, int32_t n_ghost, int64_t n_global,
+                 int32_t npeers, const int32_t* peers_host, const int32_t* send_ptr_host,
+                 const int32_t* send_idx_dev, const int32_t* recv_ptr_host, double* sendbuf_dev,
+                 double* ghostbuf_dev);
+/* ghost_dst[bs*g + c] = owner's x[bs*i + c]; ghost_dst NULL: the plan's ghostbuf.  x holds the
+ * owned entries; pass ghost_dst = x + bs*n_owned to refresh an [owned | ghost] vector in place. */
+int nsb_halo_exchange(nsb_ctx* ctx, int32_t which, int32_t bs, const double* x, double* ghost_dst,
+                      void* stream);
 
 /* ---------------------------------------------------------------- instrumentation ------- */
 /* Per-kernel-class CUDA-event timing on the launching stream (SURVEY.md 8b nsb_timer_*).

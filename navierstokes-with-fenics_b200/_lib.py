@@ -15,7 +15,8 @@ BC_LINEAR, BC_NEWTON = 0, 1
 TILE_ENTRIES = {(BSR, 3): 384, (BSR, 2): 768}
 SCHED_MAX_BLOCKS = 160     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
 TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
-                 "krylov_vec", "dirichlet", "vector")
+                 "krylov_vec", "dirichlet", "vector", "comm")
+HALO_NONE, HALO_NODES, HALO_VERTS = 0, 1, 2
 
 c_i32p = C.POINTER(C.c_int32)
 c_u8p = C.POINTER(C.c_uint8)
@@ -28,7 +29,7 @@ class Matrix(C.Structure):
     """struct nsb_matrix"""
     _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
                 ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp), ("tiles", vp),
-                ("ntiles", C.c_int32), ("reserved", C.c_int32)]
+                ("ntiles", C.c_int32), ("halo", C.c_int32)]
 
 
 class Precond(C.Structure):
@@ -83,6 +84,10 @@ PROTOTYPES = {
     "nsb_vec_gather": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp]),
     "nsb_ipcs_advance": (C.c_int, [vp, C.c_int64, vp, vp, vp, C.c_int64, vp, vp, vp]),
     "nsb_fp64_peak": (C.c_int, [vp, c_f64p]),
+    "nsb_comm_unique_id": (C.c_int, [vp]),
+    "nsb_comm_init": (C.c_int, [vp, C.c_int32, C.c_int32, vp]),
+    "nsb_set_halo": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_halo_exchange": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp]),
     "nsb_timer_enable": (C.c_int, [vp, C.c_int32]),
     "nsb_timer_report": (C.c_int, [vp, c_f64p, c_i64p]),
     "nsb_launch_count": (C.c_int, [vp, c_i64p]),

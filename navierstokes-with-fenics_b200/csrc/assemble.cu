@@ -87,6 +87,7 @@ k_momentum_jacobian(int32_t nrows, const int32_t* __restrict__ rowptr,
                     const int32_t* __restrict__ pair_ptr, const int32_t* __restrict__ pair_cell,
                     const uint8_t* __restrict__ pair_iloc, const uint8_t* __restrict__ pair_slots,
                     const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
+                    const int32_t* __restrict__ cell_verts,
                     const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc,
                     int newton, double* __restrict__ vals) {
     using TB = Tab<D>;
@@ -102,8 +103,11 @@ k_momentum_jacobian(int32_t nrows, const int32_t* __restrict__ rowptr,
         int32_t nodes[NL];
 #pragma unroll
         for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+        int32_t vtx[D + 1];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
         Geo<D> g;
-        cell_geometry(coords, nodes, g);
+        cell_geometry(coords, vtx, g);
         double U[NL][D];
 #pragma unroll
         for (int L = 0; L < NL; ++L)
@@ -184,6 +188,7 @@ __global__ void __launch_bounds__(128)
 k_momentum_residual(int32_t nrows, const int32_t* __restrict__ pair_ptr,
                     const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
                     const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
+                    const int32_t* __restrict__ cell_verts,
                     const double* __restrict__ ustar, const double* __restrict__ un,
                     const double* __restrict__ unm1, const double* __restrict__ pn, nsb_coef cf,
                     double* __restrict__ b_out) {
@@ -201,8 +206,11 @@ k_momentum_residual(int32_t nrows, const int32_t* __restrict__ pair_ptr,
         int32_t nodes[NL];
 #pragma unroll
         for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+        int32_t vtx[D + 1];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
         Geo<D> g;
-        cell_geometry(coords, nodes, g);
+        cell_geometry(coords, vtx, g);
         double U[NL][D];
 #pragma unroll
         for (int L = 0; L < NL; ++L)
@@ -246,7 +254,7 @@ k_momentum_residual(int32_t nrows, const int32_t* __restrict__ pair_ptr,
         // pressure
 #pragma unroll
         for (int M = 0; M <= D; ++M) {
-            const double pm = cf.c_p * g.detJ * pn[nodes[M]];
+            const double pm = cf.c_p * g.detJ * pn[vtx[M]];
 #pragma unroll
             for (int b = 0; b < D; ++b) {
                 double s = 0.0;
@@ -332,7 +340,8 @@ template <int D>
 __global__ void __launch_bounds__(128)
 k_poisson_rhs(int32_t nrows, const int32_t* __restrict__ pair_ptr, const int32_t* __restrict__ pair_cell,
               const uint8_t* __restrict__ pair_iloc, const double* __restrict__ coords,
-              const int32_t* __restrict__ cell_nodes, const double* __restrict__ pn,
+              const int32_t* __restrict__ cell_nodes, const int32_t* __restrict__ cell_verts,
+              const double* __restrict__ pn,
               const double* __restrict__ ustar, double a0_over_k, double* __restrict__ b_out) {
     using TB = Tab<D>;
     constexpr int NL = TB::NL2, NV = D + 1;
@@ -345,14 +354,17 @@ k_poisson_rhs(int32_t nrows, const int32_t* __restrict__ pair_ptr, const int32_t
         int32_t nodes[NL];
 #pragma unroll
         for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+        int32_t vtx[D + 1];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
         Geo<D> g;
-        cell_geometry(coords, nodes, g);
+        cell_geometry(coords, vtx, g);
         double e = 0.0;
 #pragma unroll
         for (int i = 0; i < D; ++i) {
             double gp = 0.0;
 #pragma unroll
-            for (int M = 0; M < NV; ++M) gp += pn[nodes[M]] * grad_lambda<D>(g, M, i);
+            for (int M = 0; M < NV; ++M) gp += pn[vtx[M]] * grad_lambda<D>(g, M, i);
             e += gp * grad_lambda<D>(g, Mr, i);
         }
         e *= g.detJ * TB::INV_FACT;
@@ -378,7 +390,8 @@ __global__ void __launch_bounds__(128)
 k_p2_mass(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ pair_ptr,
           const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
           const uint8_t* __restrict__ pair_slots, const double* __restrict__ coords,
-          const int32_t* __restrict__ cell_nodes, double* __restrict__ vals) {
+          const int32_t* __restrict__ cell_nodes, const int32_t* __restrict__ cell_verts,
+          double* __restrict__ vals) {
     using TB = Tab<D>;
     constexpr int NL = TB::NL2;
     const int32_t row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -390,7 +403,7 @@ k_p2_mass(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __re
         const int I = pair_iloc[p];
         int32_t v[D + 1];
 #pragma unroll
-        for (int M = 0; M <= D; ++M) v[M] = cell_nodes[(int64_t)c * NL + M];
+        for (int M = 0; M <= D; ++M) v[M] = cell_verts[(int64_t)c * (D + 1) + M];
         Geo<D> g;
         cell_geometry(coords, v, g);
         for (int J = 0; J < NL; ++J)
@@ -405,8 +418,8 @@ template <int D>
 __global__ void __launch_bounds__(128)
 k_correction_rhs(int32_t nrows, const int32_t* __restrict__ pair_ptr, const int32_t* __restrict__ pair_cell,
                  const uint8_t* __restrict__ pair_iloc, const double* __restrict__ coords,
-                 const int32_t* __restrict__ cell_nodes, const double* __restrict__ ustar,
-                 const double* __restrict__ pnew, const double* __restrict__ pold, double k_over_a0,
+                 const int32_t* __restrict__ cell_nodes, const int32_t* __restrict__ cell_verts,
+                 const double* __restrict__ ustar, const double* __restrict__ pnew, const double* __restrict__ pold, double k_over_a0,
                  double* __restrict__ b_out) {
     using TB = Tab<D>;
     constexpr int NL = TB::NL2, NV = D + 1;
@@ -421,14 +434,17 @@ k_correction_rhs(int32_t nrows, const int32_t* __restrict__ pair_ptr, const int3
         int32_t nodes[NL];
 #pragma unroll
         for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+        int32_t vtx[D + 1];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
         Geo<D> g;
-        cell_geometry(coords, nodes, g);
+        cell_geometry(coords, vtx, g);
         double Fe[D];
 #pragma unroll
         for (int b = 0; b < D; ++b) {
             double gp = 0.0;
 #pragma unroll
-            for (int M = 0; M < NV; ++M) gp += (pnew[nodes[M]] - pold[nodes[M]]) * grad_lambda<D>(g, M, b);
+            for (int M = 0; M < NV; ++M) gp += (pnew[vtx[M]] - pold[vtx[M]]) * grad_lambda<D>(g, M, b);
             Fe[b] = -k_over_a0 * TB::m2(I) * gp;
         }
         for (int L = 0; L < NL; ++L) {
@@ -615,9 +631,9 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
         if (tp == 1) {
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_residual<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                                     ctx->cell_nodes, ustar, un, unm1, pn, cf, b_out)),
+                                                     ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, cf, b_out)),
             (k_momentum_residual<3><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                                     ctx->cell_nodes, ustar, un, unm1, pn, cf, b_out)));
+                                                     ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, cf, b_out)));
         NSB_LAUNCH_CHECK(ctx, "k_momentum_residual");
         }
     }
@@ -631,10 +647,10 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
         if (rg == 0) return 0;
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_jacobian<2><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
-                                                     P.pair_slots, ctx->coords, ctx->cell_nodes, ustar, mc,
+                                                     P.pair_slots, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mc,
                                                      cf.c_conv, cf.c_visc, newton, A_out)),
             (k_momentum_jacobian<3><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
-                                                     P.pair_slots, ctx->coords, ctx->cell_nodes, ustar, mc,
+                                                     P.pair_slots, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mc,
                                                      cf.c_conv, cf.c_visc, newton, A_out)));
         NSB_LAUNCH_CHECK(ctx, "k_momentum_jacobian");
     }
@@ -664,9 +680,9 @@ extern "C" int nsb_assemble_poisson(nsb_ctx* ctx, int32_t flags, const double* p
         NSB_TIMED(ctx, NSB_T_ASM_RHS, st);
         NSB_DIM_DISPATCH(ctx,
             (k_poisson_rhs<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                               ctx->cell_nodes, pn, ustar, aok, b_out)),
+                                               ctx->cell_nodes, ctx->cell_verts, pn, ustar, aok, b_out)),
             (k_poisson_rhs<3><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                               ctx->cell_nodes, pn, ustar, aok, b_out)));
+                                               ctx->cell_nodes, ctx->cell_verts, pn, ustar, aok, b_out)));
         NSB_LAUNCH_CHECK(ctx, "k_poisson_rhs");
     }
     return 0;
@@ -685,9 +701,9 @@ extern "C" int nsb_assemble_correction(nsb_ctx* ctx, int32_t flags, const double
         NSB_TIMED(ctx, NSB_T_ASM_CONST, st);
         NSB_DIM_DISPATCH(ctx,
             (k_p2_mass<2><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc, P.pair_slots,
-                                           ctx->coords, ctx->cell_nodes, A_out)),
+                                           ctx->coords, ctx->cell_nodes, ctx->cell_verts, A_out)),
             (k_p2_mass<3><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc, P.pair_slots,
-                                           ctx->coords, ctx->cell_nodes, A_out)));
+                                           ctx->coords, ctx->cell_nodes, ctx->cell_verts, A_out)));
         NSB_LAUNCH_CHECK(ctx, "k_p2_mass");
     }
     if (flags & NSB_VEC) {
@@ -696,9 +712,9 @@ extern "C" int nsb_assemble_correction(nsb_ctx* ctx, int32_t flags, const double
         NSB_TIMED(ctx, NSB_T_ASM_RHS, st);
         NSB_DIM_DISPATCH(ctx,
             (k_correction_rhs<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                                  ctx->cell_nodes, ustar, pnew, pold, koa, b_out)),
+                                                  ctx->cell_nodes, ctx->cell_verts, ustar, pnew, pold, koa, b_out)),
             (k_correction_rhs<3><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                                  ctx->cell_nodes, ustar, pnew, pold, koa, b_out)));
+                                                  ctx->cell_nodes, ctx->cell_verts, ustar, pnew, pold, koa, b_out)));
         NSB_LAUNCH_CHECK(ctx, "k_correction_rhs");
     }
     return 0;

@@ -70,7 +70,7 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                      const int32_t* __restrict__ rowptr, const int32_t* __restrict__ pair_ptr,
                      const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
                      const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
-                     const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc, int newton,
+                     const int32_t* __restrict__ cell_verts, const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc, int newton,
                      double* __restrict__ vals) {
     using C = JacCfg<D>;
     using TB = CT<D>;
@@ -119,8 +119,11 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                 int32_t nodes[NL];
 #pragma unroll
                 for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+                int32_t vtx[D + 1];
+#pragma unroll
+                for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
                 Geo<D> geo;
-                cell_geometry(coords, nodes, geo);
+                cell_geometry(coords, vtx, geo);
                 double U[NL][D];
 #pragma unroll
                 for (int L = 0; L < NL; ++L)
@@ -255,7 +258,7 @@ static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double
     if (blocks > need) blocks = need;
     k_jacobian_rowgroups<D><<<(int)blocks, C::WARPS * 32, C::SMEM, st>>>(
         P.ngroups, P.group_row, P.chunk_first, P.round_ptr, P.sched, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
-        ctx->coords, ctx->cell_nodes, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
+        ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
     NSB_LAUNCH_CHECK(ctx, "k_jacobian_rowgroups");
     return 0;
 }

@@ -41,6 +41,7 @@ template <> struct RT<3> {
 template <int D>
 __global__ void __launch_bounds__(128)
 k_residual_cells(int32_t ncells, const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
+                 const int32_t* __restrict__ cell_verts,
                  const double* __restrict__ ustar, const double* __restrict__ un, const double* __restrict__ unm1,
                  const double* __restrict__ pn, nsb_coef cf, double* __restrict__ scratch) {
     using TB = RT<D>;
@@ -50,8 +51,11 @@ k_residual_cells(int32_t ncells, const double* __restrict__ coords, const int32_
     int32_t nodes[NL];
 #pragma unroll
     for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+    int32_t vtx[D + 1];
+#pragma unroll
+    for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
     Geo<D> g;
-    cell_geometry(coords, nodes, g);
+    cell_geometry(coords, vtx, g);
     double U[NL][D], A[NL][D];
 #pragma unroll
     for (int L = 0; L < NL; ++L)
@@ -64,7 +68,7 @@ k_residual_cells(int32_t ncells, const double* __restrict__ coords, const int32_
         }
     double P[NV];
 #pragma unroll
-    for (int M = 0; M < NV; ++M) P[M] = pn[nodes[M]];
+    for (int M = 0; M < NV; ++M) P[M] = pn[vtx[M]];
     double G[D][D];
     metric<D>(g, G);
     // vertex velocity gradients gM[M][b][j] = d_j u_b (x_M)
@@ -173,11 +177,11 @@ int nsb_launch_residual_cells(nsb_ctx* ctx, const double* ustar, const double* u
     if (!ctx->scratch || ctx->scratch_doubles < (int64_t)ctx->ncells * NL * D) return 1;
     const int B1 = nsb_blocks(ctx->ncells, 128), B2 = nsb_blocks(P.nrows, 256);
     if (D == 2) {
-        k_residual_cells<2><<<B1, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ustar, un, unm1, pn, ctx->coef,
+        k_residual_cells<2><<<B1, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, ctx->coef,
                                                ctx->scratch);
         k_gather_rows<2, 6><<<B2, 256, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->scratch, b_out);
     } else {
-        k_residual_cells<3><<<B1, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ustar, un, unm1, pn, ctx->coef,
+        k_residual_cells<3><<<B1, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, ctx->coef,
                                                ctx->scratch);
         k_gather_rows<3, 10><<<B2, 256, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->scratch, b_out);
     }

@@ -38,8 +38,22 @@ struct nsb_timer_class {
     int64_t regions = 0;           // timed regions since the last reset
 };
 
+// owner -> ghost exchange plan of one index space (comm.cu, nsb_set_halo)
+struct nsb_halo {
+    int32_t n_owned = 0, n_ghost = 0;
+    int64_t n_global = 0;
+    std::vector<int32_t> peers, send_ptr, recv_ptr;   // host copies
+    const int32_t* send_idx = nullptr;                // dev [send_ptr.back()] local owned indices
+    double* sendbuf = nullptr;                        // dev [send_ptr.back() * 3], caller-owned
+    double* ghostbuf = nullptr;                       // dev [n_ghost * 3], caller-owned (SpMV ghosts)
+};
+
 struct nsb_ctx {
     int device = 0;
+    // multi-GPU (comm.cu): one rank per GPU, NCCL communicator created by nsb_comm_init
+    int rank = 0, nranks = 1;
+    void* nccl_comm = nullptr;
+    nsb_halo halo[3];                 // [NSB_HALO_NODES], [NSB_HALO_VERTS]; [0] unused
     int sm_count = 148;
     std::string err;
     // mesh
@@ -69,6 +83,9 @@ struct nsb_ctx {
 };
 
 int nsb_timer_flush(nsb_ctx* ctx);
+// comm.cu: no-ops (return 0) on a single rank
+int nsb_allreduce_sum(nsb_ctx* ctx, double* dev_buf, int count, cudaStream_t st);
+int nsb_comm_destroy(nsb_ctx* ctx);
 // assemble_jac.cu: 0 = launched, 1 = not applicable (caller falls back), -1 = error
 int nsb_launch_residual_cells(nsb_ctx* ctx, const double* ustar, const double* un, const double* unm1,
                               const double* pn, double* b_out, cudaStream_t st);   // assemble_res.cu

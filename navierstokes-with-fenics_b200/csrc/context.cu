@@ -35,6 +35,7 @@ extern "C" int nsb_create(nsb_ctx** out, int device) {
 extern "C" int nsb_destroy(nsb_ctx* ctx) {
     if (!ctx) return 0;
     cudaSetDevice(ctx->device);
+    nsb_comm_destroy(ctx);
     cudaFree(ctx->d_partials);
     cudaFree(ctx->d_scalars);
     cudaFree(ctx->d_counter);

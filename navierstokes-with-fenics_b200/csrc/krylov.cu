@@ -228,10 +228,13 @@ extern "C" int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* i
     // slots S_H1 / S_H1+1 alternate: ||v_k||^2 with v_k = D^-1 A v_{k-1} / ||v_{k-1}||
     for (int k = 0; k <= iters; ++k) {
         if (nsb_launch_spmv(ctx, A, v, q, nullptr, nullptr, st)) return -1;
-        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-        k_pi_step<<<G, 256, 0, st>>>(n, inv_diag, q, k == 0 ? nullptr : ds + S_H1 + ((k - 1) & 1), v, ctx->d_partials,
-                                     ctx->d_counter, ds + S_H1 + (k & 1));
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_pi_step<<<G, 256, 0, st>>>(n, inv_diag, q, k == 0 ? nullptr : ds + S_H1 + ((k - 1) & 1), v, ctx->d_partials,
+                                         ctx->d_counter, ds + S_H1 + (k & 1));
+        }
         NSB_LAUNCH_CHECK(ctx, "k_pi_step");
+        if (nsb_allreduce_sum(ctx, ds + S_H1 + (k & 1), 1, st)) return -1;
     }
     // ||v_iters||^2 = || D^-1 A v_{iters-1} ||^2 / ||v_{iters-1}||^2   (the k = 0 step is unnormalised)
     if (fetch(ctx, S_H1, 2, st)) return -1;
@@ -258,14 +261,17 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     const bool jac = M->kind == NSB_PC_JACOBI;
     const double* dinv = M->inv_diag;
     double shift = 0.0;
+    // size of the system over all ranks (the zero-mean projection divides by it)
+    const double n_all = (ctx->nranks > 1 && A->halo) ? (double)ctx->halo[A->halo].n_global * A->bs : (double)n;
     if (nullspace) {
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
             k_reduce<false><<<G, 256, 0, st>>>(n, b, nullptr, ctx->d_partials, ctx->d_counter, ds + S_OUT);
         }
         NSB_LAUNCH_CHECK(ctx, "k_reduce");
+        if (nsb_allreduce_sum(ctx, ds + S_OUT, 1, st)) return -1;
         if (fetch(ctx, S_OUT, 1, st)) return -1;
-        shift = ctx->h_scalars[S_OUT] / (double)n;
+        shift = ctx->h_scalars[S_OUT] / n_all;
     }
     if (nsb_launch_spmv(ctx, A, x, q, nullptr, nullptr, st)) return -1;
     int cur = S_RZ0, nxt = S_RZ1;
@@ -273,6 +279,10 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         if (jac) k_cg_init<true><<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
         else k_cg_init<false><<<G, 256, 0, st>>>(n, b, q, dinv, shift, r, z, p, ctx->d_partials, ctx->d_counter, ds);
+    }
+    if (nsb_allreduce_sum(ctx, ds + S_TMP, 3, st)) return -1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_cg_init_finish<<<1, 1, 0, st>>>(ds, jac ? 1 : 0);
     }
     NSB_LAUNCH_CHECK(ctx, "k_cg_init");
@@ -281,6 +291,7 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
         if (apply_pc(ctx, A, M, r, z, scratch, n, st)) return -1;
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_reduce<true><<<G, 256, 0, st>>>(n, r, z, ctx->d_partials, ctx->d_counter, ds + cur);
+        if (nsb_allreduce_sum(ctx, ds + cur, 1, st)) return -1;
         k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, cur, 1, ds);
         NSB_LAUNCH_CHECK(ctx, "k_cg_init(pc)");
         NSB_COUNT(ctx, 1);
@@ -296,6 +307,10 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
             if (jac) k_cg_update1<true><<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
             else k_cg_update1<false><<<G, 256, 0, st>>>(n, p, q, dinv, x, r, z, cur, ctx->d_partials, ctx->d_counter, ds);
+        }
+        if (nsb_allreduce_sum(ctx, ds + S_TMP, 2, st)) return -1;
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
             k_cg_update1_finish<<<1, 1, 0, st>>>(ds, nxt, jac ? 1 : 0);
         }
         NSB_LAUNCH_CHECK(ctx, "k_cg_update1");
@@ -306,6 +321,7 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
             k_reduce<true><<<G, 256, 0, st>>>(n, r, z, ctx->d_partials, ctx->d_counter, ds + nxt);
             NSB_LAUNCH_CHECK(ctx, "k_reduce(rz)");
         }
+        if (!jac && nsb_allreduce_sum(ctx, ds + nxt, 1, st)) return -1;
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
             k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, nxt, 0, ds);
@@ -319,8 +335,9 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     }
     if (nullspace) {
         k_reduce<false><<<G, 256, 0, st>>>(n, x, nullptr, ctx->d_partials, ctx->d_counter, ds + S_OUT);
+        if (nsb_allreduce_sum(ctx, ds + S_OUT, 1, st)) return -1;
         if (fetch(ctx, S_OUT, 1, st)) return -1;
-        k_shift<<<G, 256, 0, st>>>(n, ctx->h_scalars[S_OUT] / (double)n, x);
+        k_shift<<<G, 256, 0, st>>>(n, ctx->h_scalars[S_OUT] / n_all, x);
         NSB_LAUNCH_CHECK(ctx, "k_shift");
         NSB_COUNT(ctx, 1);
     }
@@ -430,6 +447,7 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
         k_reduce<true><<<G, 256, 0, st>>>(n, b, b, ctx->d_partials, ctx->d_counter, ds + S_OUT);
     }
     NSB_LAUNCH_CHECK(ctx, "k_reduce");
+    if (nsb_allreduce_sum(ctx, ds + S_OUT, 1, st)) return -1;
     if (fetch(ctx, S_OUT, 1, st)) return -1;
     const double bnorm = sqrt(hs[S_OUT]);
     const double tol = fmax(rtol * bnorm, atol);
@@ -443,6 +461,7 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
             k_residual<<<G, 256, 0, st>>>(n, b, t, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
         }
         NSB_LAUNCH_CHECK(ctx, "k_residual");
+        if (nsb_allreduce_sum(ctx, ds + S_NRM, 1, st)) return -1;
         if (fetch(ctx, S_NRM, 1, st)) return -1;
         rnorm = sqrt(hs[S_NRM]);
         if (!(rnorm == rnorm)) return nsb_fail(ctx, "GMRES breakdown: residual is NaN%s%s");
@@ -460,10 +479,10 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
             if (apply_pc(ctx, A, M, V + (int64_t)j * n, t, scratch, n, st)) return -1;
             if (nsb_launch_spmv(ctx, A, t, w, nullptr, nullptr, st)) return -1;
             const int nk = j + 1;
-            {
-                NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-                for (int pass = 0; pass < 2; ++pass) {   // CGS-2
-                    double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
+            for (int pass = 0; pass < 2; ++pass) {   // CGS-2
+                double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
+                {
+                    NSB_TIMED(ctx, NSB_T_KRYLOV, st);
                     for (int k0 = 0; k0 < nk; k0 += 16) {
                         const int c = nk - k0 < 16 ? nk - k0 : 16;
                         if (c <= 4) k_multi_dot<4><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
@@ -471,8 +490,16 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
                         else k_multi_dot<16><<<G, 256, 0, st>>>(n, k0, c, V, w, ctx->d_partials, ctx->d_counter, hdev);
                         NSB_COUNT(ctx, 1);
                     }
+                }
+                if (nsb_allreduce_sum(ctx, hdev, nk, st)) return -1;
+                {
+                    NSB_TIMED(ctx, NSB_T_KRYLOV, st);
                     k_multi_axpy<<<G, 256, 0, st>>>(n, nk, V, hdev, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
                 }
+                if (nsb_allreduce_sum(ctx, ds + S_NRM, 1, st)) return -1;
+            }
+            {
+                NSB_TIMED(ctx, NSB_T_KRYLOV, st);
                 k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, V + (int64_t)(j + 1) * n);
             }
             NSB_LAUNCH_CHECK(ctx, "gmres arnoldi");

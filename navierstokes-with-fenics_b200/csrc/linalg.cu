@@ -5,8 +5,8 @@
 
 // ---- SpMV dispatch ---------------------------------------------------------------------------
 template <int KIND, int BS, int LANES>
-static int launch_spmv_t(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
-                         const double* dot_with, double* scalar_out, cudaStream_t st) {
+static int launch_spmv_t(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
+                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st) {
     constexpr int RPB = NSB_SPMV_THREADS / LANES;
     int64_t blocks = ((int64_t)A->nrows + RPB - 1) / RPB;
     nsb_timed_region region(ctx, KIND == NSB_BSR ? NSB_T_SPMV_BSR : NSB_T_SPMV_CSR, st);
@@ -14,48 +14,69 @@ static int launch_spmv_t(nsb_ctx* ctx, const nsb_matrix* A, const double* x, dou
         const int64_t cap = (int64_t)ctx->sm_count * 8;
         if (blocks > cap) blocks = cap;
         k_spmv<KIND, BS, LANES, true><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
-            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, y, dot_with, ctx->d_partials,
+            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, nown, xg, y, dot_with, ctx->d_partials,
             ctx->d_counter, scalar_out);
     } else {
         k_spmv<KIND, BS, LANES, false><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
-            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, y, nullptr, nullptr, nullptr, nullptr);
+            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, nown, xg, y, nullptr, nullptr, nullptr, nullptr);
     }
     NSB_LAUNCH_CHECK(ctx, "k_spmv");
     return 0;
 }
 
 template <int KIND, int BS>
-static int launch_spmv_bs(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
-                          const double* dot_with, double* scalar_out, cudaStream_t st) {
+static int launch_spmv_bs(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
+                          double* y, const double* dot_with, double* scalar_out, cudaStream_t st) {
     double per_row = A->nrows > 0 ? (double)A->nnz / (double)A->nrows : 0.0;
     if (KIND == NSB_BSR) per_row *= BS * BS;
-    if (per_row <= 10.0) return launch_spmv_t<KIND, BS, 4>(ctx, A, x, y, dot_with, scalar_out, st);
-    if (per_row <= 24.0) return launch_spmv_t<KIND, BS, 8>(ctx, A, x, y, dot_with, scalar_out, st);
-    if (per_row <= 64.0) return launch_spmv_t<KIND, BS, 16>(ctx, A, x, y, dot_with, scalar_out, st);
-    return launch_spmv_t<KIND, BS, 32>(ctx, A, x, y, dot_with, scalar_out, st);
+    if (per_row <= 10.0) return launch_spmv_t<KIND, BS, 4>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+    if (per_row <= 24.0) return launch_spmv_t<KIND, BS, 8>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+    if (per_row <= 64.0) return launch_spmv_t<KIND, BS, 16>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+    return launch_spmv_t<KIND, BS, 32>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
 }
+
+static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
+                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st);
 
 int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
                     const double* dot_with, double* scalar_out, cudaStream_t st) {
     NSB_REQUIRE(ctx, A && A->rowptr && A->col && A->vals && A->nrows > 0, "bad matrix descriptor");
     NSB_REQUIRE(ctx, x && y && x != y, "bad vectors (x must not alias y)");
+    int32_t nown = INT32_MAX;
+    const double* xg = x;
+    if (ctx->nranks > 1) {
+        // partitioned mesh: refresh the ghost columns of x from their owners, then multiply the owned rows
+        NSB_REQUIRE(ctx, A->halo == NSB_HALO_NODES || A->halo == NSB_HALO_VERTS, "matrix of a partitioned run needs a halo index space");
+        const nsb_halo& H = ctx->halo[A->halo];
+        NSB_REQUIRE(ctx, H.n_owned == A->nrows, "matrix rows are not the owned prefix of the halo plan");
+        if (nsb_halo_exchange(ctx, A->halo, A->bs, x, nullptr, st)) return -1;
+        nown = H.n_owned;
+        xg = H.ghostbuf - (int64_t)nown * A->bs;
+    }
+    if (spmv_dispatch(ctx, A, x, nown, xg, y, dot_with, scalar_out, st)) return -1;
+    if (dot_with && nsb_allreduce_sum(ctx, scalar_out, 1, st)) return -1;
+    return 0;
+}
+
+static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
+                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st) {
     if (A->kind == NSB_CSR) {
         switch (A->bs) {
-            case 1: return launch_spmv_bs<NSB_CSR, 1>(ctx, A, x, y, dot_with, scalar_out, st);
-            case 2: return launch_spmv_bs<NSB_CSR, 2>(ctx, A, x, y, dot_with, scalar_out, st);
-            case 3: return launch_spmv_bs<NSB_CSR, 3>(ctx, A, x, y, dot_with, scalar_out, st);
+            case 1: return launch_spmv_bs<NSB_CSR, 1>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+            case 2: return launch_spmv_bs<NSB_CSR, 2>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+            case 3: return launch_spmv_bs<NSB_CSR, 3>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
         }
     } else if (A->kind == NSB_BSR) {
         const bool tma_ok = A->tiles && A->ntiles > 0 && !dot_with &&
                             ((((uintptr_t)A->vals) | ((uintptr_t)A->col) | ((uintptr_t)A->tiles)) & 15) == 0;
         if (tma_ok) {
             nsb_timed_region region(ctx, NSB_T_SPMV_BSR, st);
-            if (A->bs == 3) return launch_spmv_bsr_tma<3>(ctx, A, x, y, st);
-            if (A->bs == 2) return launch_spmv_bsr_tma<2>(ctx, A, x, y, st);
+            if (A->bs == 3) return launch_spmv_bsr_tma<3>(ctx, A, x, nown, xg, y, st);
+            if (A->bs == 2) return launch_spmv_bsr_tma<2>(ctx, A, x, nown, xg, y, st);
         }
         switch (A->bs) {
-            case 2: return launch_spmv_bs<NSB_BSR, 2>(ctx, A, x, y, dot_with, scalar_out, st);
-            case 3: return launch_spmv_bs<NSB_BSR, 3>(ctx, A, x, y, dot_with, scalar_out, st);
+            case 2: return launch_spmv_bs<NSB_BSR, 2>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+            case 3: return launch_spmv_bs<NSB_BSR, 3>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
         }
     }
     return nsb_fail(ctx, "unsupported matrix kind / block size%s%s");
@@ -207,6 +228,7 @@ extern "C" int nsb_vec_dot(nsb_ctx* ctx, int64_t n, const double* x, const doubl
         k_dot<true><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, y, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
     }
     NSB_LAUNCH_CHECK(ctx, "k_dot");
+    if (nsb_allreduce_sum(ctx, ctx->d_scalars, 1, st)) return -1;
     return fetch_scalar(ctx, out_host, st);
 }
 extern "C" int nsb_vec_sum(nsb_ctx* ctx, int64_t n, const double* x, double* out_host, void* stream) {
@@ -217,5 +239,6 @@ extern "C" int nsb_vec_sum(nsb_ctx* ctx, int64_t n, const double* x, double* out
         k_dot<false><<<grid_for(ctx, n, 256), 256, 0, st>>>(n, x, nullptr, ctx->d_partials, ctx->d_counter, ctx->d_scalars);
     }
     NSB_LAUNCH_CHECK(ctx, "k_dot(sum)");
+    if (nsb_allreduce_sum(ctx, ctx->d_scalars, 1, st)) return -1;
     return fetch_scalar(ctx, out_host, st);
 }

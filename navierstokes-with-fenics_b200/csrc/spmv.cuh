@@ -2,6 +2,8 @@
 // components) and BSR-BS.  LANES cooperating lanes own one (block) row; value and column
 // streams are read coalesced along the row; x is gathered through L2 (x fits the 126 MB L2 for
 // every config of SURVEY.md 8).  Rows flagged in bc_mask act as identity rows (dolfin `ident`).
+// On a partitioned mesh the rows are the owned prefix and a column >= nown is a ghost, read from
+// xg (= ghost buffer - BS*nown, so that xg[BS*col + c] addresses it); one GPU: nown = INT32_MAX.
 // Optional fused epilogue: deterministic grid-wide dot(x-like vector, y)  (CG: p.Ap).
 #pragma once
 #include "common.cuh"
@@ -11,22 +13,25 @@
 template <int BS, int LANES>
 __device__ __forceinline__ void csr_row(int32_t row, int lane, const int32_t* __restrict__ rowptr,
                                         const int32_t* __restrict__ col, const double* __restrict__ vals,
-                                        const double* __restrict__ x, double (&acc)[BS]) {
+                                        const double* __restrict__ x, int32_t nown,
+                                        const double* __restrict__ xg, double (&acc)[BS]) {
 #pragma unroll
     for (int b = 0; b < BS; ++b) acc[b] = 0.0;
     const int32_t end = rowptr[row + 1];
     for (int32_t s = rowptr[row] + lane; s < end; s += LANES) {
         const double v = vals[s];
-        const int64_t c = (int64_t)col[s] * BS;
+        const int32_t cn = col[s];
+        const double* xs = (cn < nown ? x : xg) + (int64_t)cn * BS;
 #pragma unroll
-        for (int b = 0; b < BS; ++b) acc[b] += v * x[c + b];
+        for (int b = 0; b < BS; ++b) acc[b] += v * xs[b];
     }
 }
 
 template <int BS, int LANES>
 __device__ __forceinline__ void bsr_row(int32_t row, int lane, const int32_t* __restrict__ rowptr,
                                         const int32_t* __restrict__ col, const double* __restrict__ vals,
-                                        const double* __restrict__ x, double (&acc)[BS]) {
+                                        const double* __restrict__ x, int32_t nown,
+                                        const double* __restrict__ xg, double (&acc)[BS]) {
     constexpr int BB = BS * BS;
 #pragma unroll
     for (int b = 0; b < BS; ++b) acc[b] = 0.0;
@@ -36,7 +41,8 @@ __device__ __forceinline__ void bsr_row(int32_t row, int lane, const int32_t* __
     for (int e = lane; e < n; e += LANES) {
         const int blk = e / BB, rc = e - blk * BB;
         const int r = rc / BS, c = rc - r * BS;
-        const double t = v[e] * x[(int64_t)col[r0 + blk] * BS + c];
+        const int32_t cn = col[r0 + blk];
+        const double t = v[e] * (cn < nown ? x : xg)[(int64_t)cn * BS + c];
 #pragma unroll
         for (int b = 0; b < BS; ++b) acc[b] += (b == r) ? t : 0.0;
     }
@@ -47,6 +53,7 @@ template <int KIND, int BS, int LANES, bool DOT>
 __global__ void __launch_bounds__(NSB_SPMV_THREADS)
 k_spmv(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
        const double* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
+       int32_t nown, const double* __restrict__ xg,
        double* __restrict__ y, const double* __restrict__ dot_with, double* partials,
        unsigned int* counter, double* scalar_out) {
     constexpr int ROWS_PER_BLOCK = NSB_SPMV_THREADS / LANES;
@@ -58,8 +65,8 @@ k_spmv(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restr
         const bool valid = row < nrows;
         double acc[BS];
         if (valid) {
-            if (KIND == NSB_CSR) csr_row<BS, LANES>((int32_t)row, lane, rowptr, col, vals, x, acc);
-            else bsr_row<BS, LANES>((int32_t)row, lane, rowptr, col, vals, x, acc);
+            if (KIND == NSB_CSR) csr_row<BS, LANES>((int32_t)row, lane, rowptr, col, vals, x, nown, xg, acc);
+            else bsr_row<BS, LANES>((int32_t)row, lane, rowptr, col, vals, x, nown, xg, acc);
         } else {
 #pragma unroll
             for (int b = 0; b < BS; ++b) acc[b] = 0.0;

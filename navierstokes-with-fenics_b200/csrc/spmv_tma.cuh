@@ -31,7 +31,7 @@ template <int BS>
 __global__ void __launch_bounds__(SpmvTmaCfg<BS>::THREADS)
 k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* __restrict__ col,
                const double* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
-               double* __restrict__ y) {
+               int32_t nown, const double* __restrict__ xg, double* __restrict__ y) {
     using Cfg = SpmvTmaCfg<BS>;
     constexpr int BB = Cfg::BB, NW = Cfg::THREADS / 32;
     extern __shared__ __align__(128) unsigned char smem[];
@@ -75,7 +75,8 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
 #pragma unroll
         for (int b = 0; b < BS; ++b) acc[b] = 0.0;
         for (uint32_t k = o0 + lane; k < o1; k += 32) {
-            const double* xb = x + (int64_t)sc[k] * BS;
+            const int32_t cn = sc[k];
+            const double* xb = (cn < nown ? x : xg) + (int64_t)cn * BS;
             double xv[BS];
 #pragma unroll
             for (int c = 0; c < BS; ++c) xv[c] = __ldg(xb + c);
@@ -99,7 +100,8 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
 }
 
 template <int BS>
-static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, cudaStream_t st) {
+static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
+                               double* y, cudaStream_t st) {
     using Cfg = SpmvTmaCfg<BS>;
     static bool configured = false;
     if (!configured) {
@@ -108,7 +110,7 @@ static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const double* 
         configured = true;
     }
     k_spmv_bsr_tma<BS><<<A->ntiles, Cfg::THREADS, Cfg::SMEM, st>>>(A->tiles, (uint32_t)A->nnz, A->col, A->vals,
-                                                                 A->bc_mask, x, y);
+                                                                 A->bc_mask, x, nown, xg, y);
     NSB_LAUNCH_CHECK(ctx, "k_spmv_bsr_tma");
     return 0;
 }

@@ -16,7 +16,9 @@ def _ptr(t):
 class Pattern:
     """CSR pattern + row->(cell, local row, slots) incidence, resident on the device."""
 
-    def __init__(self, dev, nrows, cell_rows, cell_cols):
+    def __init__(self, dev, nrows, cell_rows, cell_cols, nrows_owned=None):
+        """``nrows_owned`` (partitioned meshes): keep only the owned prefix of the rows; the
+        columns still span every local index (owned + ghost)."""
         lib = dev.lib
         cell_rows = np.ascontiguousarray(cell_rows, dtype=np.int32)
         cell_cols = np.ascontiguousarray(cell_cols, dtype=np.int32)
@@ -40,6 +42,13 @@ class Pattern:
                                          pair_cell.ctypes.data, pair_iloc.ctypes.data, pair_slots.ctypes.data))
         finally:
             lib.nsb_pattern_free(h)
+        if nrows_owned is not None and nrows_owned < nrows:
+            nrows = int(nrows_owned)
+            rowptr, pair_ptr = rowptr[:nrows + 1].copy(), pair_ptr[:nrows + 1].copy()
+            col = col[:rowptr[nrows]].copy()
+            pair_cell, pair_iloc = pair_cell[:pair_ptr[nrows]].copy(), pair_iloc[:pair_ptr[nrows]].copy()
+            pair_slots = pair_slots[:int(pair_ptr[nrows]) * nlc].copy()
+            self.nrows, self.nnz, self.npairs = nrows, int(rowptr[nrows]), int(pair_ptr[nrows])
         self.rowptr_host, self.col_host = rowptr, col
         self._dev, self._tiles = dev, {}
         self.sched = None
@@ -80,7 +89,10 @@ class Pattern:
 class Device:
     """One GPU, one mesh.  Raises if CUDA or libnsb200.so is unavailable (no CPU fallback)."""
 
-    def __init__(self, mesh, device_index=0, mixed=False):
+    def __init__(self, mesh, device_index=0, mixed=False, partition=None):
+        """``partition`` (partition.Partition with finalized halo plans): this rank's share of a
+        mesh-partitioned run; ``mesh`` is then ignored in favour of the partition's local mesh and
+        torch.distributed must be initialised (it carries the NCCL id to the other ranks)."""
         if not torch.cuda.is_available():
             raise RuntimeError("nsb200 needs a CUDA device: there is no CPU fallback")
         self.lib = L.load()
@@ -88,9 +100,17 @@ class Device:
         torch.cuda.set_device(self.torch_device)
         self.ctx = C.c_void_p()
         L.check(self.lib.nsb_create(C.byref(self.ctx), device_index))
+        self.partition = partition
+        if partition is not None:
+            assert not mixed, "the monolithic solvers run on one GPU (SURVEY.md 8e: replicas only)"
+            mesh = partition.mesh
         self.mesh = mesh
-        self.spaces = sp = TaylorHoodSpaces(mesh)
+        self.spaces = sp = TaylorHoodSpaces(mesh, None if partition is None else partition.node_perm)
         self.dim = sp.dim
+        self.n_owned_nodes = sp.n_nodes if partition is None else partition.nodes.n_owned
+        self.n_owned_verts = sp.n_vertices if partition is None else partition.verts.n_owned
+        if partition is not None:
+            self._setup_comm(partition)
         self.coords = self.upload(mesh.coords)
         self.cell_verts = self.upload(mesh.cells)
         self.cell_nodes = self.upload(sp.cell_nodes)
@@ -115,6 +135,42 @@ class Device:
         except Exception:
             pass
 
+    # ---- multi-GPU ---------------------------------------------------------------------------
+    def _setup_comm(self, part):
+        """NCCL communicator (id broadcast through torch.distributed) and the two halo plans."""
+        import torch.distributed as dist
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if part.rank == 0:
+            buf = (C.c_uint8 * 128)()
+            L.check(self.lib.nsb_comm_unique_id(buf))
+            ident = torch.tensor(list(buf), dtype=torch.uint8)
+        if part.nranks > 1:
+            if dist.get_backend() == "nccl":
+                ident = ident.to(self.torch_device)
+            dist.broadcast(ident, src=0)
+        buf = (C.c_uint8 * 128)(*ident.cpu().tolist())
+        self.check(self.lib.nsb_comm_init(self.ctx, part.rank, part.nranks, buf))
+        self._halo_keep = []
+        for which, pl in ((L.HALO_NODES, part.nodes), (L.HALO_VERTS, part.verts)):
+            assert pl.peers is not None, "halo plan not finalized (partition.connect*)"
+            send_idx = self.upload(pl.send_idx) if len(pl.send_idx) else None
+            sendbuf = self.empty(3 * max(len(pl.send_idx), 1))
+            ghostbuf = self.empty(3 * max(pl.n_ghost, 1))
+            peers, sp_, rp_ = (np.ascontiguousarray(a, dtype=np.int32) for a in (pl.peers, pl.send_ptr, pl.recv_ptr))
+            self.check(self.lib.nsb_set_halo(self.ctx, which, pl.n_owned, pl.n_ghost, pl.n_global, len(peers),
+                                             peers.ctypes.data, sp_.ctypes.data, _ptr(send_idx), rp_.ctypes.data,
+                                             _ptr(sendbuf), _ptr(ghostbuf)))
+            self._halo_keep.append((send_idx, sendbuf, ghostbuf))
+
+    def halo_exchange(self, which, bs, x):
+        """refresh the ghost block of the [owned | ghost] vector ``x`` from the owners (no-op on
+        one GPU)"""
+        if self.partition is None or self.partition.nranks == 1:
+            return
+        n_owned = self.n_owned_nodes if which == L.HALO_NODES else self.n_owned_verts
+        ghost = C.c_void_p(x.data_ptr() + 8 * bs * n_owned)
+        self.check(self.lib.nsb_halo_exchange(self.ctx, which, bs, _ptr(x), ghost, self.stream))
+
     # ---- plumbing ---------------------------------------------------------------------------
     def check(self, status):
         L.check(status, self.ctx)
@@ -136,10 +192,12 @@ class Device:
         if name not in self.patterns:
             sp = self.spaces
             if name == "P2P2":
-                pat = Pattern(self, sp.n_nodes, sp.cell_nodes, sp.cell_nodes)
+                pat = Pattern(self, sp.n_nodes, sp.cell_nodes, sp.cell_nodes, self.n_owned_nodes)
+                pat.halo = L.HALO_NODES
                 which = L.PAT_P2P2
             elif name == "P1P1":
-                pat = Pattern(self, sp.n_vertices, self.mesh.cells, self.mesh.cells)
+                pat = Pattern(self, sp.n_vertices, self.mesh.cells, self.mesh.cells, self.n_owned_verts)
+                pat.halo = L.HALO_VERTS
                 which = L.PAT_P1P1
             elif name == "WW":
                 cd = sp.cell_dofs_W
@@ -165,7 +223,8 @@ class Device:
         tiles, ntiles = pat.tiles(L.TILE_ENTRIES[(kind, bs)]) if (kind, bs) in L.TILE_ENTRIES else (None, 0)
         m = L.Matrix(kind, bs, pat.nrows, pat.nnz, pat.rowptr.data_ptr(), pat.col.data_ptr(), vals.data_ptr(),
                      bc_mask.data_ptr() if bc_mask is not None else None,
-                     tiles.data_ptr() if tiles is not None else None, ntiles, 0)
+                     tiles.data_ptr() if tiles is not None else None, ntiles,
+                     getattr(pat, "halo", 0) if self.partition is not None else 0)
         m._keep = (pat, vals, bc_mask, tiles)
         return m
 

@@ -17,7 +17,13 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged, newton_conv
 class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
-                 momentum_preconditioner="chebyshev", chebyshev_degree=4, chebyshev_ratio=30.0):
+                 momentum_preconditioner="chebyshev", chebyshev_degree=4, chebyshev_ratio=30.0, partition=None):
+        """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
+        mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
+        the partition's local mesh and its carried-over markers.  Field vectors hold
+        [owned | ghost] entries, every linear system lives on the owned entries."""
+        if partition is not None:
+            mesh, boundary_markers = partition.mesh, partition.mesh.bfacet_marker
         super().__init__(mesh, boundary_markers, form_convective_term)
         assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
         assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
@@ -27,9 +33,10 @@ class IPCSSolver(SolverBase):
         self._cache = cache_constant_matrices
         assert momentum_preconditioner in ("jacobi", "chebyshev")
         self._mom_pc, self._cheb_degree, self._cheb_ratio = momentum_preconditioner, chebyshev_degree, chebyshev_ratio
-        self.dev = dev = Device(mesh, device_index)
+        self.dev = dev = Device(mesh, device_index, partition=partition)
         sp = dev.spaces
-        nV, nQ = sp.ndofs_V, sp.ndofs_Q
+        nV, nQ = sp.ndofs_V, sp.ndofs_Q                      # local: owned + ghost
+        self._nV_own, self._nQ_own = sp.dim * dev.n_owned_nodes, dev.n_owned_verts
         # fields (source/ns_ipcs_solver.py:66-82)
         self._velocities = [dev.zeros(nV) for _ in range(time_stepping.n_levels() + 1)]
         while len(self._velocities) < 3:
@@ -42,11 +49,12 @@ class IPCSSolver(SolverBase):
         self._A_mom = dev.empty(p22.nnz * d * d)
         self._A_mass = dev.empty(p22.nnz)
         self._A_lap = dev.empty(p11.nnz)
-        self._bV, self._dxV, self._dinvV = dev.empty(nV), dev.empty(nV), dev.empty(nV)
-        self._dinv_mass = dev.empty(nV)
-        self._bQ, self._dinvQ = dev.empty(nQ), dev.empty(nQ)
-        self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nV, gmres_restart),
-                                   dev.lib.nsb_cg_workspace_doubles(nV)))
+        nVo, nQo = self._nV_own, self._nQ_own
+        self._bV, self._dxV, self._dinvV = dev.empty(nVo), dev.empty(nVo), dev.empty(nVo)
+        self._dinv_mass = dev.empty(nVo)
+        self._bQ, self._dinvQ = dev.empty(nQo), dev.empty(nQo)
+        self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nVo, gmres_restart),
+                                   dev.lib.nsb_cg_workspace_doubles(nVo)))
         self._have_constant = False
         self._bc_ready = False
         self.newton_iterations, self.krylov_iterations = [], []
@@ -58,9 +66,16 @@ class IPCSSolver(SolverBase):
         dev, sp = self.dev, self.dev.spaces
         vd, vv = sp.dirichlet_table(self._velocity_bcs, "V")
         pd, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
-        assert len(vd) + len(pd) > 0
+        # Dirichlet rows exist for owned dofs only; ghosts receive their values from the owner
+        self._vbc_keep, self._pbc_keep = vd < self._nV_own, pd < self._nQ_own
+        vd, vv, pd, pv = vd[self._vbc_keep], vv[self._vbc_keep], pd[self._pbc_keep], pv[self._pbc_keep]
+        assert dev.partition is not None or len(vd) + len(pd) > 0
         self._vbc_dofs, self._vbc_vals = dev.upload(vd), dev.upload(vv)
         self._pbc_dofs, self._pbc_vals = dev.upload(pd), dev.upload(pv)
+        # Dirichlet or all-Neumann pressure problem: one decision for all ranks
+        self._pressure_dirichlet = len(pd) > 0
+        if dev.partition is not None:
+            self._pressure_dirichlet = dev.sum(dev.upload(np.array([float(len(pd))]))) > 0.0
         mV = np.zeros(sp.ndofs_V, dtype=np.uint8)
         mV[vd] = 1
         mQ = np.zeros(sp.ndofs_Q, dtype=np.uint8)
@@ -86,10 +101,10 @@ class IPCSSolver(SolverBase):
             self._pbc_host.copy_(self._pbc_vals)
         if self._time_dependent_bcs:
             _, vv = sp.dirichlet_table(self._velocity_bcs, "V")
-            self._vbc_host.copy_(torch.from_numpy(vv))
+            self._vbc_host.copy_(torch.from_numpy(vv[self._vbc_keep]))
             if self._pbc_dofs.numel():
                 _, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
-                self._pbc_host.copy_(torch.from_numpy(pv))
+                self._pbc_host.copy_(torch.from_numpy(pv[self._pbc_keep]))
         self._vbc_vals.copy_(self._vbc_host, non_blocking=True)
         nbytes = self._vbc_host.numel() * 8
         if self._pbc_dofs.numel():
@@ -114,7 +129,7 @@ class IPCSSolver(SolverBase):
         dev, d = self.dev, self.dev.dim
         dev.assemble_poisson(L.MAT, A=self._A_lap)
         dev.assemble_correction(L.MAT, A=self._A_mass)
-        self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pbc_dofs.numel() else None)
+        self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pressure_dirichlet else None)
         self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
         self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None)
         dev.inv_diagonal(self._lap, self._dinvQ)
@@ -201,6 +216,7 @@ class IPCSSolver(SolverBase):
                                 atol=self._linear_rtol * r0, restart=self._restart, work=self._work)
             kry.append(n_it)
             dev.axpy(-1.0, self._dxV, ustar)
+            dev.halo_exchange(L.HALO_NODES, d, ustar)
             r = self._residual()
             it += 1
             converged = newton_converged(r, r0, atol, rtol)
@@ -211,13 +227,14 @@ class IPCSSolver(SolverBase):
         # (2) pressure Poisson
         a0 = self._alpha[0]
         dev.assemble_poisson(L.VEC, pn=self._old_pressure, ustar=ustar, b=self._bQ)
-        if self._pbc_dofs.numel():
+        if self._pressure_dirichlet:
             dev.bc_apply_vector(L.BC_LINEAR, self._bQ, self._pbc_dofs, self._pbc_vals)
             dev.bc_apply_vector(L.BC_LINEAR, self._pressure, self._pbc_dofs, self._pbc_vals)
             n_p, _ = dev.cg(self._lap, self._dinvQ, self._bQ, self._pressure, rtol=self._linear_rtol, work=self._work)
         else:
             n_p, _ = dev.cg(self._lap, self._dinvQ, self._bQ, self._pressure, rtol=self._linear_rtol,
                             nullspace=True, work=self._work)
+        dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
         # (3) velocity correction
         dev.assemble_correction(L.VEC, ustar=ustar, pnew=self._pressure, pold=self._old_pressure, b=self._bV)
         dev.bc_apply_vector(L.BC_LINEAR, self._bV, self._vbc_dofs, self._vbc_vals)
@@ -225,6 +242,7 @@ class IPCSSolver(SolverBase):
         dev.bc_apply_vector(L.BC_LINEAR, self._velocities[0], self._vbc_dofs, self._vbc_vals)
         n_c, _ = dev.cg(self._mass, self._dinv_mass, self._bV, self._velocities[0], rtol=self._linear_rtol,
                         work=self._work)
+        dev.halo_exchange(L.HALO_NODES, d, self._velocities[0])
         self.krylov_iterations.append(dict(momentum=kry, pressure=n_p, correction=n_c))
         del a0
 
@@ -260,7 +278,7 @@ class IPCSSolver(SolverBase):
     def mean_pressure(self):
         dev = self.dev
         if not hasattr(self, "_p1_weights"):
-            self._p1_weights = dev.empty(dev.spaces.ndofs_Q)
+            self._p1_weights = dev.empty(self._nQ_own)
             dev.assemble_p1_mass(L.VEC, w=self._p1_weights)
             self._volume = dev.sum(self._p1_weights)
         return dev.dot(self._p1_weights, self._pressure) / self._volume

@@ -17,9 +17,12 @@ from .grid import SimplexMesh
 
 
 class TaylorHoodSpaces:
-    def __init__(self, mesh):
+    def __init__(self, mesh, node_perm=None):
+        """``node_perm`` (partitioned meshes only, partition.py): natural P2 node number
+        (vertex v / N0 + e) -> the owned-first local number used on the device."""
         assert isinstance(mesh, SimplexMesh)
         self.mesh = mesh
+        self.node_perm = None if node_perm is None else np.ascontiguousarray(node_perm, dtype=np.int32)
         d = self.dim = mesh.dim
         N0, N1 = mesh.num_vertices, mesh.num_edges
         self.n_vertices, self.n_nodes = N0, N0 + N1
@@ -27,6 +30,9 @@ class TaylorHoodSpaces:
         self.nloc1 = d + 1
         self.cell_nodes = np.ascontiguousarray(
             np.concatenate([mesh.cells, mesh.cell_edges + np.int32(N0)], axis=1), dtype=np.int32)
+        if self.node_perm is not None:
+            assert self.node_perm.shape == (N0 + N1,)
+            self.cell_nodes = np.ascontiguousarray(self.node_perm[self.cell_nodes])
         self.ndofs_V = d * self.n_nodes
         self.ndofs_Q = N0
         self.ndofs_W = d * self.n_nodes + N0
@@ -63,7 +69,12 @@ class TaylorHoodSpaces:
     def node_coordinates(self):
         m = self.mesh
         mid = 0.5 * (m.coords[m.edges[:, 0]] + m.coords[m.edges[:, 1]])
-        return np.concatenate([m.coords, mid], axis=0)
+        x = np.concatenate([m.coords, mid], axis=0)
+        if self.node_perm is not None:
+            out = np.empty_like(x)
+            out[self.node_perm] = x
+            return out
+        return x
 
     # ---- Dirichlet tables ---------------------------------------------------------------------
     def _facet_closure(self, marker):
@@ -79,6 +90,8 @@ class TaylorHoodSpaces:
         edges = np.concatenate([m.edge_index(fv[:, i], fv[:, j]) for i, j in pairs])
         verts = np.unique(fv.ravel())
         nodes = np.concatenate([verts, self.n_vertices + np.unique(edges)])
+        if self.node_perm is not None:
+            nodes = self.node_perm[nodes].astype(np.int64)
         return nodes, verts
 
     def dirichlet_table(self, bcs, space):
