@@ -96,6 +96,8 @@ class SimplexMesh:
 
     def boundary_ids(self):
         """``extract_all_boundary_markers`` (source/auxiliary_methods.py:56-67)"""
+        if getattr(self, "global_boundary_ids", None) is not None:   # local mesh of a partition
+            return set(self.global_boundary_ids)
         return set(int(m) for m in np.unique(self.bfacet_marker))
 
 

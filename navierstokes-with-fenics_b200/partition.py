@@ -129,6 +129,7 @@ def build_partition(mesh, rank, nranks, axis=None, crank=None):
     pos = np.clip(np.searchsorted(gk[gorder], lk), 0, len(gk) - 1)
     hit = gk[gorder][pos] == lk
     local.bfacet_marker[:] = np.where(hit, mesh.bfacet_marker[gorder][pos], 0)
+    local.global_boundary_ids = mesh.boundary_ids()      # a rank may not touch every boundary
     # P2 nodes: natural local numbering (vertices, then local edges) -> global ids -> owned first
     gedge = mesh.edge_index(lverts[local.edges[:, 0]], lverts[local.edges[:, 1]])
     nat_gid = np.concatenate([lverts, nvg + gedge.astype(np.int64)])

@@ -106,6 +106,8 @@ class TaylorHoodSpaces:
         xnodes = None
         for marker, comp, value in bcs:
             nodes, verts = self._facet_closure(marker)
+            if len(nodes) == 0:          # this rank's part of the mesh does not touch the boundary
+                continue
             if comp == "p":
                 if space == "V":
                     continue

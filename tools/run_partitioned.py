@@ -43,9 +43,10 @@ def make_problem(nsb200, dim, n, flow):
     return mesh, markers, bcs
 
 
-def run(nsb200, mesh, markers, bcs, steps, device_index, partition=None, axis=None):
+def run(nsb200, mesh, markers, bcs, steps, device_index, partition=None, pc="chebyshev"):
     ts = nsb200.BDFTimeStepping(0.0, 1.0e6, order=2, desired_start_time_step=0.01)
-    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=device_index, partition=partition)
+    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=device_index, partition=partition,
+                               momentum_preconditioner=pc)
     solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=0.02))
     solver.set_boundary_conditions(bcs)
     for _ in range(steps):
@@ -63,6 +64,8 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--flow", default="cavity", choices=["cavity", "channel"])
     ap.add_argument("--axis", type=int, default=None)
+    ap.add_argument("--pc", default="chebyshev", choices=["chebyshev", "jacobi"])
+    ap.add_argument("--single-first", action="store_true", help="debug: run the un-partitioned problem first")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -77,8 +80,11 @@ def main():
     import nsb200
     from nsb200 import partition as part
     mesh, markers, bcs = make_problem(nsb200, args.dim, args.n, args.flow)
+    if args.single_first and rank == 0:
+        ref = run(nsb200, mesh, markers, bcs, args.steps, local, pc=args.pc)
+        print("single-GPU run ok:", ref.newton_iterations, ref.krylov_iterations, flush=True)
     p = part.connect_distributed(part.build_partition(mesh, rank, world, axis=args.axis))
-    solver = run(nsb200, mesh, markers, bcs, args.steps, local, partition=p)
+    solver = run(nsb200, mesh, markers, bcs, args.steps, local, partition=p, pc=args.pc)
     d = mesh.dim
     nVo, nQo = solver._nV_own, solver._nQ_own
     mine = dict(node_gid=p.nodes.owned_gid, vert_gid=p.verts.owned_gid,
@@ -89,7 +95,7 @@ def main():
     dist.gather_object(mine, gathered if rank == 0 else None, dst=0)
     ok = True
     if rank == 0:
-        ref = run(nsb200, mesh, markers, bcs, args.steps, local)
+        ref = run(nsb200, mesh, markers, bcs, args.steps, local, pc=args.pc)
         uref, pref = ref._velocities[1].cpu().numpy(), ref._old_pressure.cpu().numpy()
         u, pr = np.full_like(uref, np.nan), np.full_like(pref, np.nan)
         for g in gathered:
