@@ -145,7 +145,7 @@ class Device:
             L.check(self.lib.nsb_comm_unique_id(buf))
             ident = torch.tensor(list(buf), dtype=torch.uint8)
         if part.nranks > 1:
-            if dist.get_backend() == "nccl":
+            if dist.get_backend() == "nccl":          # pure-NCCL process group: device tensors only
                 ident = ident.to(self.torch_device)
             dist.broadcast(ident, src=0)
         buf = (C.c_uint8 * 128)(*ident.cpu().tolist())
