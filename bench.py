@@ -248,6 +248,16 @@ def run_nsb200(args):
     launches = dev.launch_count() - l0
     clocks = sampler.result()
     ms_e2e, h2d, d2h = timed(args.steps, True)
+    if world > 1:
+        # collective tear-down BEFORE rank 0 goes off to format the result: every rank leaves together
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, dict(cells=dev.mesh.num_cells, owned_nodes=dev.n_owned_nodes,
+                                              ghost_nodes=dev.spaces.n_nodes - dev.n_owned_nodes))
+        barrier()
+        dev.close()                      # collective: ncclCommDestroy of libnsb200's communicator
+        dist.destroy_process_group()
+    else:
+        per_rank = None
     if rank != 0:
         return
     K = args.steps
@@ -295,9 +305,9 @@ def run_nsb200(args):
             "sample": "2 IPCS steps of the CPU oracle (C assembly, %d OpenMP threads; numpy Jacobi-GMRES/CG rtol 1e-12) "
                       "on the %d^3 x 6 cavity (%d DOF, %.3f s/step), scaled by the DOF ratio %.4g"
                       % (threads, CPU_SAMPLE_N, mixed_dofs(CPU_SAMPLE_N), sec, scale)}
+    if per_rank is not None:
+        line["partition"] = per_rank
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 def main():

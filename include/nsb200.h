@@ -247,6 +247,9 @@ int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, dou
  * all-reduce their result.  NCCL (libnccl.so.2, the copy torch loads) is bound at run time. */
 int nsb_comm_unique_id(uint8_t* id_out128);                      /* ncclGetUniqueId (rank 0) */
 int nsb_comm_init(nsb_ctx* ctx, int32_t rank, int32_t nranks, const uint8_t* id128);
+/* collective tear-down (every rank calls it, after its last kernel): ncclCommDestroy.  nsb_destroy
+ * alone leaves the communicator to process exit, because destroying it synchronises with the peers. */
+int nsb_comm_finalize(nsb_ctx* ctx);
 /* which = NSB_HALO_*; peers/send_ptr/recv_ptr are host arrays ([npeers], [npeers+1], [npeers+1]):
  * ghost slots recv_ptr[i]..recv_ptr[i+1] (offsets into the ghost block) come from peers[i];
  * send_idx_dev[send_ptr[i]..send_ptr[i+1]] are the local owned indices peers[i] needs, in the

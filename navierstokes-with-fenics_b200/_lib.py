@@ -86,6 +86,7 @@ PROTOTYPES = {
     "nsb_fp64_peak": (C.c_int, [vp, c_f64p]),
     "nsb_comm_unique_id": (C.c_int, [vp]),
     "nsb_comm_init": (C.c_int, [vp, C.c_int32, C.c_int32, vp]),
+    "nsb_comm_finalize": (C.c_int, [vp]),
     "nsb_set_halo": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "nsb_halo_exchange": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp]),
     "nsb_timer_enable": (C.c_int, [vp, C.c_int32]),

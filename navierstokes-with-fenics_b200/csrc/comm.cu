@@ -72,11 +72,22 @@ extern "C" int nsb_comm_init(nsb_ctx* ctx, int32_t rank, int32_t nranks, const u
     return 0;
 }
 
+// nsb_destroy path: the communicator is NOT torn down implicitly.  ncclCommDestroy synchronises with
+// the peers, so calling it from object finalisers (ranks exit in any order) can block forever;
+// the explicit, collective nsb_comm_finalize does it, process exit reclaims it otherwise.
 int nsb_comm_destroy(nsb_ctx* ctx) {
-    if (ctx && ctx->nccl_comm && g_nccl.CommDestroy) {
-        g_nccl.CommDestroy((nccl_comm_t)ctx->nccl_comm);
-        ctx->nccl_comm = nullptr;
+    if (ctx) ctx->nccl_comm = nullptr;
+    return 0;
+}
+
+extern "C" int nsb_comm_finalize(nsb_ctx* ctx) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    if (ctx->nccl_comm && g_nccl.CommDestroy) {
+        NSB_CUDA(ctx, cudaDeviceSynchronize());
+        NSB_NCCL(ctx, g_nccl.CommDestroy((nccl_comm_t)ctx->nccl_comm));
     }
+    ctx->nccl_comm = nullptr;
+    ctx->nranks = 1; ctx->rank = 0;
     return 0;
 }
 

@@ -162,6 +162,15 @@ class Device:
                                              _ptr(sendbuf), _ptr(ghostbuf)))
             self._halo_keep.append((send_idx, sendbuf, ghostbuf))
 
+    def close(self):
+        """collective on a partitioned run (every rank calls it): tears the NCCL communicator
+        down, then frees the context"""
+        if getattr(self, "ctx", None):
+            if self.partition is not None:
+                self.check(self.lib.nsb_comm_finalize(self.ctx))
+            self.lib.nsb_destroy(self.ctx)
+            self.ctx = None
+
     def halo_exchange(self, which, bs, x):
         """refresh the ghost block of the [owned | ghost] vector ``x`` from the owners (no-op on
         one GPU)"""

@@ -113,6 +113,7 @@ def main():
                           "cells_per_rank": [g["cells"] for g in gathered],
                           "ghost_nodes_per_rank": [g["ghosts"] for g in gathered],
                           "launches_per_rank": [g["launches"] for g in gathered]}), flush=True)
+    solver.dev.close()
     flag = [ok]
     dist.broadcast_object_list(flag, src=0)
     dist.destroy_process_group()
