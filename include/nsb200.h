@@ -236,6 +236,26 @@ int nsb_vec_gather(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x,
 int nsb_ipcs_advance(nsb_ctx* ctx, int64_t nv, const double* u0, double* u1, double* u2,
                      int64_t nq, const double* p, double* p_old, void* stream);
 
+/* ---------------------------------------------------------------- functionals (K15) ------ */
+/* F = -int_Gamma(-p n + c_visc sym(grad u) n) ds over the listed exterior facets: the drag / lift
+ * post-processing of demo/dfg_benchmark.py:44-66 (c_D = 2 F_x, c_L = 2 F_y).  facet_cell: owning
+ * cell of each facet, facet_opp: local number of the cell vertex opposite to it; u in V numbering
+ * (interleaved P2), p in Q numbering.  force_out_host3: 3 doubles (unused components 0). */
+int nsb_boundary_force(nsb_ctx* ctx, int32_t nfacets, const int32_t* facet_cell_dev,
+                       const uint8_t* facet_opp_dev, const double* u, const double* p, double c_visc,
+                       double* force_out_host3, void* stream);
+
+/* ---------------------------------------------------------------- direct solve (K16) ----- */
+/* x = A^-1 b for the indefinite mixed Newton system, which the reference hands to PETSc's sparse LU
+ * (source/ns_bdf_solver.py:91-100,106; source/ns_solver_base.py:938-949,974-983).  LIBRARY leg, not
+ * a hand-written kernel: cuSOLVER sparse QR on the device (cusolverSpDcsrlsvqr, bound at run
+ * time), reorder 0 none | 1 symrcm | 2 symamd | 3 metis.  Blocking.  Its wall time is accumulated
+ * apart from the kernel-class timers and read with nsb_direct_seconds (reset != 0 clears it). */
+int nsb_direct_solve(nsb_ctx* ctx, int32_t n, int32_t nnz, const int32_t* rowptr, const int32_t* col,
+                     const double* vals, const double* b, double* x, int32_t reorder,
+                     double* seconds_out, void* stream);
+int nsb_direct_seconds(nsb_ctx* ctx, double* seconds_out, int64_t* solves_out, int32_t reset);
+
 /* ---------------------------------------------------------------- multi-GPU (K14) -------- */
 /* Mesh-partitioned runs, one rank per GPU (the reference has no counterpart: it
  * would be dolfin/PETSc MPI, which source/ never exercises).  Each rank registers its LOCAL mesh

@@ -84,6 +84,9 @@ PROTOTYPES = {
     "nsb_vec_gather": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp]),
     "nsb_ipcs_advance": (C.c_int, [vp, C.c_int64, vp, vp, vp, C.c_int64, vp, vp, vp]),
     "nsb_fp64_peak": (C.c_int, [vp, c_f64p]),
+    "nsb_boundary_force": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, C.c_double, c_f64p, vp]),
+    "nsb_direct_solve": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, C.c_int32, c_f64p, vp]),
+    "nsb_direct_seconds": (C.c_int, [vp, c_f64p, c_i64p, C.c_int32]),
     "nsb_comm_unique_id": (C.c_int, [vp]),
     "nsb_comm_init": (C.c_int, [vp, C.c_int32, C.c_int32, vp]),
     "nsb_comm_finalize": (C.c_int, [vp]),

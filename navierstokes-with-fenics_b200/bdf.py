@@ -1,0 +1,100 @@
+"""ImplicitBDFSolver: mirror of ``source/ns_bdf_solver.py`` (monolithic BDF-2, Newton on the mixed
+space W) whose residual / Jacobian assembly, Dirichlet rows, history shift and linear solves run on
+the GPU.  Same constructor arguments and public methods as the reference class
+(``set_boundary_conditions``, ``set_equation_coefficients``, ``set_initial_conditions``, ``solve``,
+``advance_time``, ``solution``); non-convergence raises ``RuntimeError`` like dolfin does.
+
+The Newton update is the K16 library leg (cuSOLVER sparse QR, ``monolithic.py``), whose time is
+reported apart (``direct_solve_seconds``), as BASELINE.json's north star asks.
+"""
+import numpy as np
+
+from . import _lib as L
+from .monolithic import MixedSolverBase
+
+
+class ImplicitBDFSolver(MixedSolverBase):
+    def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
+                 device_index=0, reorder=3):
+        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder)
+        assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
+        assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
+        self._time_stepping = time_stepping
+        self._tol, self._maxiter = tol, max_iter
+        # source/ns_solver_base.py:1106-1121: n_levels + 1 mixed solutions (BDF-2: 3)
+        self._solutions = [self.dev.zeros(self._nW) for _ in range(max(time_stepping.n_levels() + 1, 3))]
+
+    def _update_time_stepping_coefficients(self):
+        """source/ns_bdf_solver.py:108-126"""
+        ts = self._time_stepping
+        alpha = list(ts.coefficients(1))
+        while len(alpha) < 3:
+            alpha.append(0.0)
+        self._alpha, self._next_step_size = tuple(alpha), ts.get_next_step_size()
+        co = self._equation_coefficients
+        self.dev.set_coefficients(self._next_step_size, self._alpha, co["convective_term"], co["pressure_term"],
+                                  co["viscous_term"])
+
+    def set_initial_conditions(self, initial_conditions):
+        """source/ns_solver_base.py:1123-1171: nodal data of degree <= 2 / 1, for which dolfin's
+        projection is the identity; written to solutions[0] and [1]."""
+        assert isinstance(initial_conditions, dict) and "velocity" in initial_conditions
+        sp, dev = self.dev.spaces, self.dev
+        d, nn = sp.dim, sp.n_nodes
+        w = np.zeros(self._nW)
+        v = initial_conditions["velocity"]
+        x = sp.node_coordinates()
+        u0 = np.asarray(v(x), dtype=np.float64).reshape(nn, d) if callable(v) else \
+            np.broadcast_to(np.asarray(v, dtype=np.float64), (nn, d))
+        for c in range(d):
+            w[c * nn:(c + 1) * nn] = u0[:, c]
+        if "pressure" in initial_conditions:
+            p = initial_conditions["pressure"]
+            xv = sp.mesh.coords
+            w[d * nn:] = np.asarray(p(xv), dtype=np.float64).reshape(-1) if callable(p) else float(p)
+        w = dev.upload(w)
+        self._solutions[0].copy_(w)
+        self._solutions[1].copy_(w)
+
+    # ---- one time step (source/ns_solver_base.py:1174-1203, source/ns_bdf_solver.py:102-106) -----
+    def solve(self):
+        if not self._bc_ready:
+            self._setup_boundary_conditions()
+        self._set_time(self._time_stepping.next_time)
+        self._update_bc_values()
+        self._update_time_stepping_coefficients()
+        self._solve_time_step()
+
+    def _residual(self):
+        dev, w = self.dev, self._solutions
+        dev.assemble_mixed(L.VEC | L.BDF, w[0], w[1], w[2], b=self._b)
+        dev.bc_apply_vector(L.BC_NEWTON, self._b, self._bc_dofs, self._bc_vals, x=w[0])
+        return dev.norm(self._b)
+
+    def _jacobian(self):
+        dev, w = self.dev, self._solutions
+        dev.assemble_mixed(L.MAT | L.BDF, w[0], w[1], w[2], A=self._A)
+        dev.bc_apply_matrix("WW", self._A, L.CSR, 1, self._bc_dofs)
+
+    def _solve_time_step(self):
+        it = self._newton(self._residual, self._jacobian, self._solutions[0], atol=self._tol, rtol=10.0 * self._tol,
+                          maxit=self._maxiter, error_on_nonconvergence=True)
+        self.newton_iterations.append(it)
+
+    def advance_time(self):
+        """``_advance_solution`` source/ns_solver_base.py:1012-1016"""
+        dev, w = self.dev, self._solutions
+        dev.copy(w[1], w[2])
+        dev.copy(w[0], w[1])
+
+    @property
+    def solution(self):
+        return self._solutions[0]
+
+    @property
+    def velocity(self):
+        return self.split(self._solutions[0])[0]
+
+    @property
+    def pressure(self):
+        return self.split(self._solutions[0])[1]

@@ -76,6 +76,10 @@ struct nsb_ctx {
     // caller-owned workspace of the two-phase (cell -> row) assembly kernels (nsb_set_scratch)
     double* scratch = nullptr;
     int64_t scratch_doubles = 0;
+    // K16 library leg (direct.cu): accumulated wall time of the sparse direct solves, kept apart
+    // from the kernel-class timers
+    double direct_seconds = 0.0;
+    int64_t direct_solves = 0;
     // instrumentation
     int64_t launch_count = 0;         // kernels launched by this context (all classes)
     bool timing = false;

@@ -330,6 +330,45 @@ class Device:
         self.check(st)
         return it.value, res.value
 
+    def facet_table(self, boundary_id):
+        """(owning cell, local number of the opposite vertex) of every exterior facet marked
+        ``boundary_id``, on the device (cached)"""
+        key = int(boundary_id)
+        if not hasattr(self, "_facet_tables"):
+            self._facet_tables = {}
+        if key not in self._facet_tables:
+            m = self.mesh
+            sel = np.nonzero(m.bfacet_marker == key)[0]
+            cells = m.bfacet_cell[sel].astype(np.int32)
+            cv, fv = m.cells[cells], m.bfacets[sel]
+            inside = (cv[:, :, None] == fv[:, None, :]).any(axis=2)
+            opp = np.argmin(inside, axis=1).astype(np.uint8)
+            assert len(sel) == 0 or (inside.sum(axis=1) == m.dim).all()
+            self._facet_tables[key] = (self.upload(cells), self.upload(opp), len(sel))
+        return self._facet_tables[key]
+
+    def boundary_force(self, table, u, p, c_visc):
+        cells, opp, n = table
+        out = (C.c_double * 3)()
+        if n == 0 and self.partition is None:
+            return np.zeros(self.dim)
+        self.check(self.lib.nsb_boundary_force(self.ctx, n, _ptr(cells), _ptr(opp), _ptr(u), _ptr(p), float(c_visc), out,
+                                               self.stream))
+        return np.array(out[:self.dim])
+
+    def direct_solve(self, pattern, vals, b, x, reorder=3):
+        """K16 (library leg): x = A^-1 b by cuSOLVER sparse QR; returns the seconds it took."""
+        pat = self.patterns[pattern]
+        sec = C.c_double()
+        self.check(self.lib.nsb_direct_solve(self.ctx, pat.nrows, pat.nnz, _ptr(pat.rowptr), _ptr(pat.col), _ptr(vals),
+                                             _ptr(b), _ptr(x), reorder, C.byref(sec), self.stream))
+        return sec.value
+
+    def direct_seconds(self, reset=False):
+        sec, n = C.c_double(), C.c_int64()
+        self.check(self.lib.nsb_direct_seconds(self.ctx, C.byref(sec), C.byref(n), 1 if reset else 0))
+        return sec.value, n.value
+
     def copy(self, x, y):
         self.check(self.lib.nsb_vec_copy(self.ctx, x.numel(), _ptr(x), _ptr(y), self.stream))
 

@@ -1,0 +1,118 @@
+"""Shared machinery of the two monolithic solver mirrors (``bdf.py``, ``stationary.py``): the mixed
+Taylor-Hood space W on the device, its Dirichlet table, dolfin's NewtonSolver loop and the GPU
+direct solve of the saddle-point Newton system (K16, library leg timed apart from the kernels).
+
+Reference: ``NonlinearVariationalSolver`` / ``NewtonSolver`` as driven by
+source/ns_bdf_solver.py:91-106 and source/ns_solver_base.py:938-988 (semantics: SURVEY.md App. A.5).
+"""
+import numpy as np
+
+from . import _lib as L
+from .device import Device
+from .solver_base import SolverBase, Expression, NewtonNotConverged
+
+
+class MixedSolverBase(SolverBase):
+    def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=3):
+        super().__init__(mesh, boundary_markers, form_convective_term)
+        self.dev = dev = Device(mesh, device_index, mixed=True)
+        self._nW = dev.spaces.ndofs_W
+        self._pat = dev.patterns["WW"]
+        self._A = dev.empty(self._pat.nnz)
+        self._b, self._dx = dev.empty(self._nW), dev.empty(self._nW)
+        self._reorder = reorder
+        self.pin_pressure = True
+        self._bc_ready = False
+        self.newton_iterations, self.newton_history = [], []
+
+    # ---- Dirichlet data on W.sub(0) / W.sub(1) (source/ns_solver_base.py:546-660) ----------------
+    def _setup_boundary_conditions(self):
+        dev, sp = self.dev, self.dev.spaces
+        dofs, vals = self._dirichlet_table()
+        assert len(dofs) > 0
+        self._bc_dofs, self._bc_vals = dev.upload(dofs), dev.upload(vals)
+        mask = np.zeros(self._nW, dtype=np.uint8)
+        mask[dofs] = 1
+        g = np.zeros(self._nW)
+        g[dofs] = vals
+        self._bc_mask, self._bc_g = dev.upload(mask), dev.upload(g)
+        dev.set_mixed_bc(self._bc_mask, self._bc_g)
+        self._time_dependent_bcs = any(isinstance(v, Expression) for _, _, v in
+                                       self._velocity_bcs + self._pressure_bcs)
+        self._bc_ready = True
+
+    def _dirichlet_table(self):
+        """Dirichlet dofs / values on W.  Without any pressure condition (cavity flows) the mixed
+        Jacobian is singular in p and the reference leans on LU pivoting: here the
+        first pressure dof is pinned to 0, which selects one member of the same solution family
+        (the velocity is unaffected; pressures compare up to a constant)."""
+        sp = self.dev.spaces
+        dofs, vals = sp.dirichlet_table(self._velocity_bcs + self._pressure_bcs, "W")
+        if not self._pressure_bcs and self.pin_pressure:
+            pin = int(sp.Q_to_W()[0])
+            dofs, vals = np.append(dofs, pin), np.append(vals, 0.0)
+            order = np.argsort(dofs, kind="stable")
+            dofs, vals = dofs[order].astype(np.int32), vals[order]
+        return dofs, vals
+
+    def _update_bc_values(self):
+        if not self._time_dependent_bcs:
+            return
+        dev = self.dev
+        dofs, vals = self._dirichlet_table()
+        self._bc_vals.copy_(dev.upload(vals))
+        dev.scatter(self._bc_dofs, self._bc_vals, self._bc_g)
+
+    # ---- dolfin NewtonSolver (convergence_criterion "residual", relaxation 1) -------------------
+    def _newton(self, residual, jacobian, x, atol, rtol, maxit, error_on_nonconvergence=True):
+        """``residual()`` fills self._b from x and returns its l2 norm, ``jacobian()`` fills self._A.
+        The update dx = J^-1 b is the K16 direct solve; x -= dx."""
+        dev = self.dev
+        r0 = r = residual()
+        hist, it = [r], 0
+        converged = (r / r0 < rtol if r0 > 0 else False) or r < atol
+        while not converged and it < maxit:
+            jacobian()
+            dev.direct_solve("WW", self._A, self._b, self._dx, self._reorder)
+            dev.axpy(-1.0, self._dx, x)
+            r = residual()
+            hist.append(r)
+            it += 1
+            converged = (r / r0 < rtol) or (r < atol)
+        self.newton_history = hist
+        if not converged and error_on_nonconvergence:
+            raise NewtonNotConverged("Newton solver did not converge (%d iterations, residual %g)" % (it, r))
+        return it
+
+    # ---- sub-space views of a mixed vector (FunctionAssigner, source/ns_solver_base.py:424-476) --
+    def _maps(self):
+        if not hasattr(self, "_v2w"):
+            sp = self.dev.spaces
+            self._v2w, self._q2w = self.dev.upload(sp.V_to_W()), self.dev.upload(sp.Q_to_W())
+        return self._v2w, self._q2w
+
+    def split(self, w):
+        """(velocity in V numbering, pressure in Q numbering) of the mixed vector ``w``"""
+        dev, sp = self.dev, self.dev.spaces
+        v2w, q2w = self._maps()
+        u, p = dev.empty(sp.ndofs_V), dev.empty(sp.ndofs_Q)
+        dev.gather(v2w, w, u)
+        dev.gather(q2w, w, p)
+        return u, p
+
+    def direct_solve_seconds(self, reset=False):
+        """(seconds, solves) spent in the K16 library leg since the last reset"""
+        return self.dev.direct_seconds(reset)
+
+    # ---- drag / lift (a13) ---------------------------------------------------------------------
+    def boundary_force(self, w, boundary_id):
+        """F = -int_Gamma ( -p n + c_visc * sym(grad u) n ) ds over the facets marked ``boundary_id``
+        (demo/dfg_benchmark.py:44-66; drag = 2 F_x, lift = 2 F_y for the DFG 2D-2 scaling)."""
+        u, p = self.split(w)
+        return boundary_force(self.dev, u, p, boundary_id, self._equation_coefficients["viscous_term"])
+
+
+def boundary_force(dev, u, p, boundary_id, c_visc):
+    """Exterior-facet functional on the device (nsb_boundary_force): returns the d force components."""
+    tab = dev.facet_table(boundary_id)
+    return dev.boundary_force(tab, u, p, c_visc)
