@@ -35,7 +35,7 @@ class StationarySolver(MixedSolverBase):
         """source/ns_solver_base.py:951-988"""
         if not self._bc_ready:
             co = self._equation_coefficients
-            self.dev.set_coefficients(1.0, (0.0, 0.0, 0.0), co["convective_term"], co["pressure_term"],
+            self.dev.set_coefficients(1.0, (1.0, -1.0, 0.0), co["convective_term"], co["pressure_term"],
                                       co["viscous_term"])
             self._setup_boundary_conditions()
         residual = self._system(True, False)
