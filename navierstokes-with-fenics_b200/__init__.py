@@ -8,7 +8,8 @@ PyTorch only provides device buffers / streams, all per-step arithmetic is in li
 without the built library or without a GPU raises.
 """
 from . import _lib                                                            # noqa: F401
-from .grid import SimplexMesh, HyperCubeBoundaryMarkers, hyper_cube, hyper_rectangle   # noqa: F401
+from .grid import (SimplexMesh, HyperCubeBoundaryMarkers, hyper_cube, hyper_rectangle,   # noqa: F401
+                   channel_with_cylinder, DFG_BOUNDARY_IDS)
 from .spaces import TaylorHoodSpaces                                          # noqa: F401
 from .timestepping import BDFTimeStepping                                     # noqa: F401
 from .solver_base import (VelocityBCType, PressureBCType, WeakFormConvectiveTerm,      # noqa: F401

@@ -155,3 +155,70 @@ def hyper_rectangle(first_point, second_point, n_points=10):
     assert all(second_point[i] > first_point[i] for i in range(dim))
     mesh = _structured(tuple(first_point), tuple(second_point), tuple(int(v) for v in n_points))
     return mesh, mesh.bfacet_marker
+
+
+# DFG 2D-2 geometry and physical ids of gmsh-collection/meshes/DFGBenchmark.geo:7-12,105-109
+DFG_BOUNDARY_IDS = {"inlet": 100, "outlet": 101, "lower wall": 102, "upper wall": 103, "cylinder": 104}
+
+
+def channel_with_cylinder(m=16, n_radial=None, n_downstream=None, grading=1.6):
+    """``grid_generator.channel_with_cylinder`` (source/grid_generator.py:452-455) on a SYNTHETIC
+    block-structured triangulation: the reference reads a gmsh mesh of DFGBenchmark.geo, and gmsh
+    is not available here.  Same geometry (channel 22 x 4.1, cylinder
+    centre (2, 2), radius 0.5) and the same physical ids.  An O-grid of 4 m angular x n_radial
+    cells joins the cylinder to the box [0, 4] x [0, 4.1] (m segments per box side, straight rays,
+    radial cells graded towards the cylinder), a rectangular block of n_downstream x m cells covers
+    [4, 22]; every quadrilateral is cut along the diagonal that keeps the triangles best shaped.
+    Returns (mesh, boundary markers, boundary marker map) like the reference."""
+    xc, yc, rc, h, length, xb = 2.0, 2.0, 0.5, 4.1, 22.0, 4.0
+    n_radial = n_radial or max(2, (3 * m) // 4)
+    n_downstream = n_downstream or max(2, int(round((length - xb) / (h / m) / 1.5)))
+    # box boundary points, counter-clockwise from the corner (xb, 0): right, top, left, bottom side
+    t = np.arange(m) / m
+    right = np.stack([np.full(m, xb), h * t], axis=1)
+    top = np.stack([xb - xb * t, np.full(m, h)], axis=1)
+    left = np.stack([np.zeros(m), h - h * t], axis=1)
+    bottom = np.stack([xb * t, np.zeros(m)], axis=1)
+    Q = np.concatenate([right, top, left, bottom])                   # [4m, 2]
+    ang = np.arctan2(Q[:, 1] - yc, Q[:, 0] - xc)
+    Cpt = np.stack([xc + rc * np.cos(ang), yc + rc * np.sin(ang)], axis=1)
+    s = (np.arange(n_radial + 1) / n_radial) ** grading               # 0 at the cylinder, 1 at the box
+    ring = (1.0 - s)[:, None, None] * Cpt[None, :, :] + s[:, None, None] * Q[None, :, :]   # [nr+1, 4m, 2]
+    nth = 4 * m
+    pts = [ring.reshape(-1, 2)]
+    quads = []
+    for r in range(n_radial):
+        for k in range(nth):
+            k1 = (k + 1) % nth
+            quads.append((r * nth + k, r * nth + k1, (r + 1) * nth + k1, (r + 1) * nth + k))
+    # downstream block [xb, length] x [0, h]; its left column coincides with the right side of the box
+    xs = xb + (length - xb) * np.arange(n_downstream + 1) / n_downstream
+    ys = h * np.arange(m + 1) / m
+    X, Y = np.meshgrid(xs, ys, indexing="ij")
+    off = ring.shape[0] * ring.shape[1]
+    pts.append(np.stack([X.ravel(), Y.ravel()], axis=1))
+    for i in range(n_downstream):
+        for j in range(m):
+            a = off + i * (m + 1) + j
+            quads.append((a, a + (m + 1), a + (m + 1) + 1, a + 1))
+    P = np.concatenate(pts)
+    # merge coincident points (box side x = xb is shared by the two blocks)
+    key = np.round(P / 1e-9).astype(np.int64)
+    _, first, inv = np.unique(key, axis=0, return_index=True, return_inverse=True)
+    inv = inv.reshape(-1)
+    coords = P[first]
+    quads = inv[np.asarray(quads, dtype=np.int64)]
+    # shorter diagonal
+    d02 = np.linalg.norm(coords[quads[:, 0]] - coords[quads[:, 2]], axis=1)
+    d13 = np.linalg.norm(coords[quads[:, 1]] - coords[quads[:, 3]], axis=1)
+    use02 = d02 <= d13
+    tri_a = np.where(use02[:, None], quads[:, [0, 1, 2]], quads[:, [0, 1, 3]])
+    tri_b = np.where(use02[:, None], quads[:, [0, 2, 3]], quads[:, [1, 2, 3]])
+    mesh = SimplexMesh(coords, np.concatenate([tri_a, tri_b]))
+    ids = DFG_BOUNDARY_IDS
+    mesh.mark_near(0, 0.0, ids["inlet"])
+    mesh.mark_near(0, length, ids["outlet"])
+    mesh.mark_near(1, 0.0, ids["lower wall"])
+    mesh.mark_near(1, h, ids["upper wall"])
+    mesh.mark_where(lambda x: np.abs(np.hypot(x[:, 0] - xc, x[:, 1] - yc) - rc) < 0.05 * rc, ids["cylinder"])
+    return mesh, mesh.bfacet_marker, dict(ids)
