@@ -277,8 +277,17 @@ def run_nsb200(args):
     dom = max((k for k in classes if alg.get(k)), key=lambda k: classes[k][0])
     dur_ms = classes[dom][0] / max(classes[dom][1], 1)
     achieved = alg[dom] / (dur_ms * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum of one launch of the same kernel on the same workload,
+    # from the committed `ncu --set full` capture (profiles/): only valid for the full C5 mesh on one GPU
+    traffic = None
+    if n == 73 and world == 1:
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_g_ncu_full_summary.json")) as f:
+                traffic = json.load(f)[dom]["traffic_bytes"]
+        except (OSError, ValueError, KeyError):
+            traffic = None
     roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg[dom], "avg_launch_ms": dur_ms,
                 "launches_timed": classes[dom][1]}
     for k in ("asm_jacobian", "asm_residual", "spmv_bsr"):
