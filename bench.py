@@ -108,7 +108,9 @@ def workload_config(n, gpus):
                            "before every SpMV / assembly, all-reduced Krylov inner products); roofline and breakdown "
                            "are rank 0's share" % gpus,
             "l2_policy": "inputs larger than L2 (Jacobian 6.5 GB, Krylov basis 3.3 GB per GPU at n=73)",
-            "linear_solvers": "GMRES(40) right-preconditioned by a degree-4 Chebyshev polynomial in D^-1 J, rtol 1e-12 (velocity); Jacobi-CG rtol 1e-12 (pressure, mass)"}
+            "linear_solvers": "FP64 GMRES(40) right-preconditioned by a degree-4 Chebyshev polynomial in D^-1 J whose 3 inner "
+                              "SpMVs read a single-precision copy of the Jacobian values (operator, residuals and solution "
+                              "stay FP64), rtol 1e-12 (velocity); Jacobi-CG rtol 1e-12 (pressure, mass)"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -168,6 +170,7 @@ def algorithmic_bytes(solver):
     geo = 8 * 3 * nverts + 4 * 4 * ncells + 4 * 10 * ncells    # coords + cell->vertex + cell->node maps
     return {
         "spmv_bsr": 8 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,
+        "spmv_bsr_f32": 4 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,   # FP32 value copy (preconditioner only)
         "spmv_csr": None,                                       # two different matrices share the class
         "asm_jacobian": 8 * 9 * nnz22 + geo + 8 * nV,
         "asm_residual": 8 * nV + geo + 8 * (3 * nV + nQ),
@@ -290,7 +293,7 @@ def run_nsb200(args):
                 "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg[dom], "avg_launch_ms": dur_ms,
                 "launches_timed": classes[dom][1]}
-    for k in ("asm_jacobian", "asm_residual", "spmv_bsr"):
+    for k in ("asm_jacobian", "asm_residual", "spmv_bsr", "spmv_bsr_f32"):
         if classes[k][1]:
             d_ms = classes[k][0] / classes[k][1]
             breakdown[k]["GB/s"] = alg[k] / (d_ms * 1e-3) / 1e9

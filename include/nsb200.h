@@ -67,7 +67,8 @@ typedef struct nsb_pattern_builder nsb_pattern_builder;
 #define NSB_T_BC 7           /* Dirichlet rows (K9)                                  */
 #define NSB_T_VEC 8          /* vector ops, history shift, gather/scatter (K13, K15) */
 #define NSB_T_COMM 9         /* halo pack + NCCL send/recv, NCCL all-reduce (K14)    */
-#define NSB_T_NCLASS 10
+#define NSB_T_SPMV_BSR32 10  /* BSR-d SpMV on the single-precision value copy (Chebyshev preconditioner only) */
+#define NSB_T_NCLASS 11
 
 /* index spaces with a halo plan (nsb_set_halo, nsb_matrix.halo) */
 #define NSB_HALO_NONE 0
@@ -90,6 +91,9 @@ typedef struct nsb_matrix {
     int32_t halo;            /* NSB_HALO_*: index space of the columns on a partitioned mesh.  Rows
                                 are the owned prefix; columns >= n_owned are ghosts, refreshed
                                 from their owners inside nsb_spmv / the Krylov solvers.  0 on one GPU */
+    const float* vals32;     /* dev [nnz*bs*bs] or NULL: single-precision copy of a BSR matrix's values
+                                (nsb_vec_to_f32).  Read ONLY by the SpMVs inside the Chebyshev
+                                preconditioner; every operator application of the solvers stays FP64 */
 } nsb_matrix;
 
 /* preconditioners of nsb_cg / nsb_gmres (K12) */
@@ -226,6 +230,7 @@ int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, in
 int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y, void* stream);
 int nsb_vec_axpy(nsb_ctx* ctx, int64_t n, double a, const double* x, double* y, void* stream); /* y += a x */
 int nsb_vec_scale(nsb_ctx* ctx, int64_t n, double a, double* x, void* stream);
+int nsb_vec_to_f32(nsb_ctx* ctx, int64_t n, const double* x, float* y, void* stream);   /* y = (float) x */
 int nsb_vec_dot(nsb_ctx* ctx, int64_t n, const double* x, const double* y, double* out_host, void* stream);
 int nsb_vec_sum(nsb_ctx* ctx, int64_t n, const double* x, double* out_host, void* stream);
 /* FunctionAssigner (source/ns_solver_base.py:424-476): y[idx[i]] = x[i] / y[i] = x[idx[i]] */

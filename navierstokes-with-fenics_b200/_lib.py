@@ -15,7 +15,7 @@ BC_LINEAR, BC_NEWTON = 0, 1
 TILE_ENTRIES = {(BSR, 3): 384, (BSR, 2): 768}
 SCHED_MAX_BLOCKS = 160     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
 TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
-                 "krylov_vec", "dirichlet", "vector", "comm")
+                 "krylov_vec", "dirichlet", "vector", "comm", "spmv_bsr_f32")
 HALO_NONE, HALO_NODES, HALO_VERTS = 0, 1, 2
 
 c_i32p = C.POINTER(C.c_int32)
@@ -29,7 +29,7 @@ class Matrix(C.Structure):
     """struct nsb_matrix"""
     _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
                 ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp), ("tiles", vp),
-                ("ntiles", C.c_int32), ("halo", C.c_int32)]
+                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp)]
 
 
 class Precond(C.Structure):
@@ -78,6 +78,7 @@ PROTOTYPES = {
     "nsb_vec_copy": (C.c_int, [vp, C.c_int64, vp, vp, vp]),
     "nsb_vec_axpy": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp, vp]),
     "nsb_vec_scale": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp]),
+    "nsb_vec_to_f32": (C.c_int, [vp, C.c_int64, vp, vp, vp]),
     "nsb_vec_dot": (C.c_int, [vp, C.c_int64, vp, vp, c_f64p, vp]),
     "nsb_vec_sum": (C.c_int, [vp, C.c_int64, vp, c_f64p, vp]),
     "nsb_vec_scatter": (C.c_int, [vp, C.c_int64, vp, vp, vp, vp]),

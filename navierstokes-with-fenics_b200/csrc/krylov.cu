@@ -170,7 +170,7 @@ static int apply_pc(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, con
         NSB_LAUNCH_CHECK(ctx, "k_cheb_first");
     }
     for (int k = 1; k < M->degree; ++k) {
-        if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st)) return -1;
+        if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st, /*lowp=*/true)) return -1;
         const double rho = 1.0 / (2.0 * sigma1 - rho_old);
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_cheb_step<<<G, 256, 0, st>>>(n, M->inv_diag, q, rho * rho_old, 2.0 * rho / delta, r, d, z);

@@ -36,10 +36,10 @@ static int launch_spmv_bs(nsb_ctx* ctx, const nsb_matrix* A, const double* x, in
 }
 
 static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
-                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st);
+                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st, bool lowp);
 
 int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
-                    const double* dot_with, double* scalar_out, cudaStream_t st) {
+                    const double* dot_with, double* scalar_out, cudaStream_t st, bool lowp) {
     NSB_REQUIRE(ctx, A && A->rowptr && A->col && A->vals && A->nrows > 0, "bad matrix descriptor");
     NSB_REQUIRE(ctx, x && y && x != y, "bad vectors (x must not alias y)");
     int32_t nown = INT32_MAX;
@@ -53,13 +53,13 @@ int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* 
         nown = H.n_owned;
         xg = H.ghostbuf - (int64_t)nown * A->bs;
     }
-    if (spmv_dispatch(ctx, A, x, nown, xg, y, dot_with, scalar_out, st)) return -1;
+    if (spmv_dispatch(ctx, A, x, nown, xg, y, dot_with, scalar_out, st, lowp)) return -1;
     if (dot_with && nsb_allreduce_sum(ctx, scalar_out, 1, st)) return -1;
     return 0;
 }
 
 static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
-                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st) {
+                         double* y, const double* dot_with, double* scalar_out, cudaStream_t st, bool lowp) {
     if (A->kind == NSB_CSR) {
         switch (A->bs) {
             case 1: return launch_spmv_bs<NSB_CSR, 1>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
@@ -70,9 +70,15 @@ static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int
         const bool tma_ok = A->tiles && A->ntiles > 0 && !dot_with &&
                             ((((uintptr_t)A->vals) | ((uintptr_t)A->col) | ((uintptr_t)A->tiles)) & 15) == 0;
         if (tma_ok) {
-            nsb_timed_region region(ctx, NSB_T_SPMV_BSR, st);
-            if (A->bs == 3) return launch_spmv_bsr_tma<3>(ctx, A, x, nown, xg, y, st);
-            if (A->bs == 2) return launch_spmv_bsr_tma<2>(ctx, A, x, nown, xg, y, st);
+            const bool f32 = lowp && A->vals32 && (((uintptr_t)A->vals32) & 15) == 0;
+            nsb_timed_region region(ctx, f32 ? NSB_T_SPMV_BSR32 : NSB_T_SPMV_BSR, st);
+            // preconditioner-only single-precision copy of the values (see spmv_tma.cuh)
+            if (f32) {
+                if (A->bs == 3) return launch_spmv_bsr_tma<3, float>(ctx, A, A->vals32, x, nown, xg, y, st);
+                if (A->bs == 2) return launch_spmv_bsr_tma<2, float>(ctx, A, A->vals32, x, nown, xg, y, st);
+            }
+            if (A->bs == 3) return launch_spmv_bsr_tma<3, double>(ctx, A, A->vals, x, nown, xg, y, st);
+            if (A->bs == 2) return launch_spmv_bsr_tma<2, double>(ctx, A, A->vals, x, nown, xg, y, st);
         }
         switch (A->bs) {
             case 2: return launch_spmv_bs<NSB_BSR, 2>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
@@ -84,7 +90,7 @@ static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int
 
 extern "C" int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void* stream) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
-    return nsb_launch_spmv(ctx, A, x, y, nullptr, nullptr, (cudaStream_t)stream);
+    return nsb_launch_spmv(ctx, A, x, y, nullptr, nullptr, (cudaStream_t)stream, false);
 }
 
 // ---- Jacobi: inverse diagonal ------------------------------------------------------------------
@@ -189,6 +195,24 @@ extern "C" int nsb_vec_scale(nsb_ctx* ctx, int64_t n, double a, double* x, void*
     nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
     k_scale<<<grid_for(ctx, n, 256), 256, 0, (cudaStream_t)stream>>>(n, a, x);
     NSB_LAUNCH_CHECK(ctx, "k_scale");
+    return 0;
+}
+// y = (float) x, 4 entries per thread (the FP32 value copy read by the Chebyshev SpMVs)
+__global__ void __launch_bounds__(256)
+k_to_f32(int64_t n, const double* __restrict__ x, float* __restrict__ y) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const double2 a = reinterpret_cast<const double2*>(x)[2 * i], b = reinterpret_cast<const double2*>(x)[2 * i + 1];
+        reinterpret_cast<float4*>(y)[i] = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) y[(n4 << 2) + threadIdx.x] = (float)x[(n4 << 2) + threadIdx.x];
+}
+extern "C" int nsb_vec_to_f32(nsb_ctx* ctx, int64_t n, const double* x, float* y, void* stream) {
+    NSB_REQUIRE(ctx, ctx && x && y && n >= 0, "bad arguments");
+    NSB_REQUIRE(ctx, ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0, "buffers must be 16-byte aligned");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
+    k_to_f32<<<grid_for(ctx, (n >> 2) + 1, 256), 256, 0, (cudaStream_t)stream>>>(n, x, y);
+    NSB_LAUNCH_CHECK(ctx, "k_to_f32");
     return 0;
 }
 extern "C" int nsb_vec_scatter(nsb_ctx* ctx, int64_t n, const int32_t* idx, const double* x, double* y, void* stream) {

@@ -91,5 +91,6 @@ k_spmv(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restr
 }
 
 // host-side launcher (defined in linalg.cu)
+// lowp: the caller accepts the single-precision value copy A->vals32 (preconditioner applications only)
 int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y,
-                    const double* dot_with, double* scalar_out, cudaStream_t st);
+                    const double* dot_with, double* scalar_out, cudaStream_t st, bool lowp = false);

@@ -16,26 +16,30 @@
 
 #define NSB_TILE_WORDS 64
 
-template <int BS>
+// VT = double: the operator itself.  VT = float: a single-precision COPY of the values, used only
+// inside the Chebyshev preconditioner (krylov.cu): the polynomial is a fixed linear operator either
+// way, the outer GMRES keeps the FP64 matrix, so the solution accuracy is unchanged while three of
+// the four SpMVs per Arnoldi step stream 40 instead of 76 bytes per block.
+template <int BS, typename VT = double>
 struct SpmvTmaCfg {
     static constexpr int BB = BS * BS;
     static constexpr int TILE = (BS == 3) ? 384 : 768;     // entries per tile (== _lib.TILE_ENTRIES)
     static constexpr int THREADS = 256;
     static constexpr int CAP = TILE + 8;                   // + the 4-entry alignment hull on both sides
-    static constexpr size_t VAL_BYTES = (size_t)CAP * BB * 8;
+    static constexpr size_t VAL_BYTES = (size_t)CAP * BB * sizeof(VT);
     static constexpr size_t COL_BYTES = (size_t)CAP * 4;
     static constexpr size_t SMEM = VAL_BYTES + COL_BYTES + NSB_TILE_WORDS * 4 + 16;
 };
 
-template <int BS>
-__global__ void __launch_bounds__(SpmvTmaCfg<BS>::THREADS)
+template <int BS, typename VT>
+__global__ void __launch_bounds__(SpmvTmaCfg<BS, VT>::THREADS)
 k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* __restrict__ col,
-               const double* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
+               const VT* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
                int32_t nown, const double* __restrict__ xg, double* __restrict__ y) {
-    using Cfg = SpmvTmaCfg<BS>;
+    using Cfg = SpmvTmaCfg<BS, VT>;
     constexpr int BB = Cfg::BB, NW = Cfg::THREADS / 32;
     extern __shared__ __align__(128) unsigned char smem[];
-    double* sv = reinterpret_cast<double*>(smem);
+    VT* sv = reinterpret_cast<VT*>(smem);
     int32_t* sc = reinterpret_cast<int32_t*>(smem + Cfg::VAL_BYTES);
     uint32_t* rec = reinterpret_cast<uint32_t*>(smem + Cfg::VAL_BYTES + Cfg::COL_BYTES);
     uint64_t* bar = reinterpret_cast<uint64_t*>(rec + NSB_TILE_WORDS);
@@ -53,10 +57,10 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(bar, NSB_TILE_WORDS * 4 + nal * (BB * 8 + 4));
+        mbar_arrive_expect_tx(bar, NSB_TILE_WORDS * 4 + nal * (BB * (uint32_t)sizeof(VT) + 4));
         tma_load_1d(rec, trec, NSB_TILE_WORDS * 4, bar);
         if (nal) {
-            tma_load_1d(sv, vals + (size_t)a0 * BB, nal * BB * 8, bar);
+            tma_load_1d(sv, vals + (size_t)a0 * BB, nal * BB * (uint32_t)sizeof(VT), bar);
             tma_load_1d(sc, col + a0, nal * 4, bar);
         }
     }
@@ -80,11 +84,11 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
             double xv[BS];
 #pragma unroll
             for (int c = 0; c < BS; ++c) xv[c] = __ldg(xb + c);
-            const double* v = sv + (size_t)k * BB;
+            const VT* v = sv + (size_t)k * BB;
 #pragma unroll
             for (int r = 0; r < BS; ++r)
 #pragma unroll
-                for (int c = 0; c < BS; ++c) acc[r] += v[r * BS + c] * xv[c];
+                for (int c = 0; c < BS; ++c) acc[r] += (double)v[r * BS + c] * xv[c];
         }
 #pragma unroll
         for (int b = 0; b < BS; ++b) acc[b] = warp_sum(acc[b]);
@@ -99,17 +103,17 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
     }
 }
 
-template <int BS>
-static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
-                               double* y, cudaStream_t st) {
-    using Cfg = SpmvTmaCfg<BS>;
+template <int BS, typename VT>
+static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const VT* vals, const double* x, int32_t nown,
+                               const double* xg, double* y, cudaStream_t st) {
+    using Cfg = SpmvTmaCfg<BS, VT>;
     static bool configured = false;
     if (!configured) {
-        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS, VT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         configured = true;
     }
-    k_spmv_bsr_tma<BS><<<A->ntiles, Cfg::THREADS, Cfg::SMEM, st>>>(A->tiles, (uint32_t)A->nnz, A->col, A->vals,
+    k_spmv_bsr_tma<BS, VT><<<A->ntiles, Cfg::THREADS, Cfg::SMEM, st>>>(A->tiles, (uint32_t)A->nnz, A->col, vals,
                                                                  A->bc_mask, x, nown, xg, y);
     NSB_LAUNCH_CHECK(ctx, "k_spmv_bsr_tma");
     return 0;

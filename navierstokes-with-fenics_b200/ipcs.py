@@ -17,7 +17,8 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged, newton_conv
 class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
-                 momentum_preconditioner="chebyshev", chebyshev_degree=4, chebyshev_ratio=30.0, partition=None):
+                 momentum_preconditioner="chebyshev", chebyshev_degree=4, chebyshev_ratio=30.0, partition=None,
+                 preconditioner_precision="f32"):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -47,6 +48,11 @@ class IPCSSolver(SolverBase):
         p22, p11 = dev.patterns["P2P2"], dev.patterns["P1P1"]
         d = sp.dim
         self._A_mom = dev.empty(p22.nnz * d * d)
+        # single-precision copy of the Jacobian values, read only by the SpMVs INSIDE the Chebyshev
+        # polynomial (a fixed linear preconditioner either way; GMRES itself applies the FP64 matrix)
+        assert preconditioner_precision in ("f32", "f64")
+        self._A_mom32 = dev.empty(p22.nnz * d * d, dtype=torch.float32) \
+            if (momentum_preconditioner == "chebyshev" and preconditioner_precision == "f32") else None
         self._A_mass = dev.empty(p22.nnz)
         self._A_lap = dev.empty(p11.nnz)
         nVo, nQo = self._nV_own, self._nQ_own
@@ -132,7 +138,7 @@ class IPCSSolver(SolverBase):
         dev.assemble_correction(L.MAT, A=self._A_mass)
         self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pressure_dirichlet else None)
         self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
-        self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None)
+        self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None, vals32=self._A_mom32)
         dev.inv_diagonal(self._lap, self._dinvQ)
         dev.inv_diagonal(self._mass, self._dinv_mass)
         self._have_constant = True
@@ -203,6 +209,8 @@ class IPCSSolver(SolverBase):
             dev.assemble_ipcs_momentum(L.MAT, ustar, A=self._A_mom)
             dev.bc_apply_matrix("P2P2", self._A_mom, L.BSR, d, self._vbc_dofs)
             dev.inv_diagonal(self._jac, self._dinvV)
+            if self._A_mom32 is not None:
+                dev.to_f32(self._A_mom, self._A_mom32)
             if self._mom_pc == "chebyshev":
                 if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step
                     self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=8, work=self._work)
