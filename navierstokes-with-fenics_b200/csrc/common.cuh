@@ -9,6 +9,8 @@
 #include "../../include/nsb200.h"
 
 #define NSB_MAX_PARTIALS 4096
+#define NSB_CG_RING 8
+#define NSB_CG_LAG 4
 
 struct nsb_pattern_dev {
     int32_t nrows = 0;
@@ -73,6 +75,9 @@ struct nsb_ctx {
     double* d_scalars = nullptr;      // [64] device-resident Krylov scalars
     unsigned int* d_counter = nullptr;
     double* h_scalars = nullptr;      // pinned [256]
+    // look-ahead convergence check of CG (krylov.cu): pinned ring of residual norms + their events
+    double* cg_ring = nullptr;
+    cudaEvent_t cg_ev[8] = {};
     // caller-owned workspace of the two-phase (cell -> row) assembly kernels (nsb_set_scratch)
     double* scratch = nullptr;
     int64_t scratch_doubles = 0;

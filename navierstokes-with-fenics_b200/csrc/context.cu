@@ -40,6 +40,10 @@ extern "C" int nsb_destroy(nsb_ctx* ctx) {
     cudaFree(ctx->d_scalars);
     cudaFree(ctx->d_counter);
     cudaFreeHost(ctx->h_scalars);
+    if (ctx->cg_ring) {
+        cudaFreeHost(ctx->cg_ring);
+        for (int i = 0; i < NSB_CG_RING; ++i) cudaEventDestroy(ctx->cg_ev[i]);
+    }
     delete ctx;
     return 0;
 }

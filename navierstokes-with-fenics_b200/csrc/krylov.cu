@@ -92,7 +92,8 @@ __global__ void __launch_bounds__(256)
 k_cg_update1(int64_t n, const double* __restrict__ p, const double* __restrict__ q,
              const double* __restrict__ dinv, double* __restrict__ x, double* __restrict__ r,
              double* __restrict__ z, int slot_rz, double* partials, unsigned int* counter, double* scal) {
-    const double alpha = scal[slot_rz] / scal[S_PQ];
+    const double pq = scal[S_PQ];
+    const double alpha = pq != 0.0 ? scal[slot_rz] / pq : 0.0;   // r = 0 reached (look-ahead iterations): no-op
     double s[2] = {0.0, 0.0};
     GRID_STRIDE(i, n) {
         x[i] += alpha * p[i];
@@ -118,7 +119,8 @@ __global__ void k_cg_update1_finish(double* scal, int slot_rz_new, int jac) {
 __global__ void __launch_bounds__(256)
 k_cg_update2(int64_t n, const double* __restrict__ z, double* __restrict__ p, int slot_rz, int slot_rz_new,
              int first, const double* __restrict__ scal) {
-    const double beta = first ? 0.0 : scal[slot_rz_new] / scal[slot_rz];
+    const double rz_old = scal[slot_rz];
+    const double beta = (first || rz_old == 0.0) ? 0.0 : scal[slot_rz_new] / rz_old;
     GRID_STRIDE(i, n) p[i] = z[i] + beta * p[i];
 }
 
@@ -245,6 +247,13 @@ extern "C" int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* i
 // ---------------------------------------------------------------------------------------------
 // CG
 // ---------------------------------------------------------------------------------------------
+static int ensure_cg_ring(nsb_ctx* ctx) {
+    if (ctx->cg_ring) return 0;
+    NSB_CUDA(ctx, cudaMallocHost(&ctx->cg_ring, sizeof(double) * NSB_CG_RING));
+    for (int i = 0; i < NSB_CG_RING; ++i) NSB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->cg_ev[i], cudaEventDisableTiming));
+    return 0;
+}
+
 extern "C" int64_t nsb_cg_workspace_doubles(int64_t n) { return 7 * n; }
 
 extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
@@ -301,6 +310,13 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     double rnorm = sqrt(ctx->h_scalars[S_RR]);
     const double tol = fmax(rtol * bnorm, atol);
     int it = 0;
+    // Convergence look-ahead: on small systems (the pressure problem: SURVEY.md H10) an iteration is a few
+    // 10-us kernels and a blocking read of ||r|| per iteration leaves the GPU idle for as long again.  The
+    // norm of iteration k is therefore copied to a pinned ring and examined LAG iterations later, while the
+    // next ones are already queued; the loop ends with a blocking read of the newest norm, so the exit
+    // criterion ||r|| <= tol is unchanged (at most LAG extra iterations are spent).
+    const int lag = (n < (int64_t)1500000 && maxit > 16) ? NSB_CG_LAG : 0;
+    if (lag && ensure_cg_ring(ctx)) return -1;
     while (rnorm > tol && it < maxit) {
         if (nsb_launch_spmv(ctx, A, p, q, p, ds + S_PQ, st)) return -1;
         {
@@ -327,11 +343,27 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
             k_cg_update2<<<G, 256, 0, st>>>(n, z, p, cur, nxt, 0, ds);
         }
         NSB_LAUNCH_CHECK(ctx, "k_cg_update2");
-        if (fetch(ctx, S_RR, 1, st)) return -1;
-        rnorm = sqrt(ctx->h_scalars[S_RR]);
-        if (!(rnorm == rnorm)) return nsb_fail(ctx, "CG breakdown: residual is NaN%s%s");
         const int t = cur; cur = nxt; nxt = t;
         ++it;
+        if (lag == 0) {
+            if (fetch(ctx, S_RR, 1, st)) return -1;
+            rnorm = sqrt(ctx->h_scalars[S_RR]);
+        } else {
+            const int slot = (it - 1) % NSB_CG_RING;
+            NSB_CUDA(ctx, cudaMemcpyAsync(ctx->cg_ring + slot, ds + S_RR, sizeof(double), cudaMemcpyDeviceToHost, st));
+            NSB_CUDA(ctx, cudaEventRecord(ctx->cg_ev[slot], st));
+            if (it > lag || it >= maxit) {
+                const int old = it >= maxit ? slot : (it - 1 - lag) % NSB_CG_RING;
+                NSB_CUDA(ctx, cudaEventSynchronize(ctx->cg_ev[old]));
+                double r_old = sqrt(ctx->cg_ring[old]);
+                if (r_old <= tol && old != slot) {      // looks converged: confirm on the newest iterate
+                    NSB_CUDA(ctx, cudaEventSynchronize(ctx->cg_ev[slot]));
+                    r_old = sqrt(ctx->cg_ring[slot]);
+                }
+                rnorm = r_old;
+            }
+        }
+        if (!(rnorm == rnorm)) return nsb_fail(ctx, "CG breakdown: residual is NaN%s%s");
     }
     if (nullspace) {
         k_reduce<false><<<G, 256, 0, st>>>(n, x, nullptr, ctx->d_partials, ctx->d_counter, ds + S_OUT);
