@@ -110,7 +110,8 @@ def workload_config(n, gpus):
             "l2_policy": "inputs larger than L2 (Jacobian 6.5 GB, Krylov basis 3.3 GB per GPU at n=73)",
             "linear_solvers": "FP64 GMRES(40) right-preconditioned by a degree-4 Chebyshev polynomial in D^-1 J whose 3 inner "
                               "SpMVs read a single-precision copy of the Jacobian values (operator, residuals and solution "
-                              "stay FP64), rtol 1e-12 (velocity); Jacobi-CG rtol 1e-12 (pressure, mass)"}
+                              "stay FP64), rtol 1e-12 (velocity); CG rtol 1e-12 with a degree-8 Chebyshev polynomial "
+                              "preconditioner (pressure) / Jacobi (mass)"}
 
 
 # ---------------------------------------------------------------------------------------------

@@ -18,7 +18,8 @@ class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
                  momentum_preconditioner="chebyshev", chebyshev_degree=4, chebyshev_ratio=30.0, partition=None,
-                 preconditioner_precision="f32"):
+                 preconditioner_precision="f32", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
+                 pressure_chebyshev_ratio=300.0):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -33,6 +34,11 @@ class IPCSSolver(SolverBase):
         self._linear_rtol, self._restart = linear_rtol, gmres_restart
         self._cache = cache_constant_matrices
         assert momentum_preconditioner in ("jacobi", "chebyshev")
+        assert pressure_preconditioner in ("jacobi", "chebyshev")
+        # pressure Poisson: CG preconditioned by a Chebyshev polynomial in D^-1 L (SPD: always safe).  About as
+        # many SpMVs as Jacobi-CG but 7x fewer CG iterations, i.e. 7x fewer inner products -- the all-reduces
+        # that bound the partitioned runs -- and fewer launches on one GPU
+        self._p_pc = (pressure_preconditioner, pressure_chebyshev_degree, pressure_chebyshev_ratio)
         self._mom_pc, self._cheb_degree, self._cheb_ratio = momentum_preconditioner, chebyshev_degree, chebyshev_ratio
         self.dev = dev = Device(mesh, device_index, partition=partition)
         sp = dev.spaces
@@ -140,6 +146,11 @@ class IPCSSolver(SolverBase):
         self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
         self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None, vals32=self._A_mom32)
         dev.inv_diagonal(self._lap, self._dinvQ)
+        if self._p_pc[0] == "chebyshev":
+            lmax = 1.1 * dev.lambda_max(self._lap, self._dinvQ, iters=30, work=self._work)
+            self._pcQ = dev.precond(self._dinvQ, L.PC_CHEBYSHEV, self._p_pc[1], lmax / self._p_pc[2], lmax)
+        else:
+            self._pcQ = dev.precond(self._dinvQ)
         dev.inv_diagonal(self._mass, self._dinv_mass)
         self._have_constant = True
 
@@ -252,9 +263,9 @@ class IPCSSolver(SolverBase):
         if self._pressure_dirichlet:
             dev.bc_apply_vector(L.BC_LINEAR, self._bQ, self._pbc_dofs, self._pbc_vals)
             dev.bc_apply_vector(L.BC_LINEAR, self._pressure, self._pbc_dofs, self._pbc_vals)
-            n_p, _ = dev.cg(self._lap, self._dinvQ, self._bQ, self._pressure, rtol=self._linear_rtol, work=self._work)
+            n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol, work=self._work)
         else:
-            n_p, _ = dev.cg(self._lap, self._dinvQ, self._bQ, self._pressure, rtol=self._linear_rtol,
+            n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol,
                             nullspace=True, work=self._work)
         dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
         # (3) velocity correction
