@@ -70,7 +70,11 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
         for (uint32_t e = nal + threadIdx.x; e < n1; e += Cfg::THREADS) sc[e] = col[a0 + e];
         __syncthreads();
     }
-    mbar_wait(bar, 0);
+    // one warp polls the barrier, the others park on the CTA barrier: ncu (r1_j) showed the try_wait polls
+    // of all 8 warps (~54 per warp and tile, one shared-memory wavefront each) to be 41 % of the L1
+    // wavefronts of this L1-bound kernel.  try_wait acquires at CTA scope and bar.sync orders the rest.
+    if (threadIdx.x < 32) mbar_wait(bar, 0);
+    __syncthreads();
     const uint16_t* off = reinterpret_cast<const uint16_t*>(rec + 4);
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (uint32_t lr = w; lr < nrows; lr += NW) {
