@@ -15,7 +15,7 @@ from .monolithic import MixedSolverBase
 
 class ImplicitBDFSolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
-                 device_index=0, reorder=3):
+                 device_index=0, reorder=1):
         super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder)
         assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
         assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")

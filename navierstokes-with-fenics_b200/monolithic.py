@@ -13,7 +13,7 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged
 
 
 class MixedSolverBase(SolverBase):
-    def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=3):
+    def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=1):
         super().__init__(mesh, boundary_markers, form_convective_term)
         self.dev = dev = Device(mesh, device_index, mixed=True)
         self._nW = dev.spaces.ndofs_W
