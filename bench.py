@@ -320,6 +320,7 @@ def run_nsb200(args):
                       % (threads, CPU_SAMPLE_N, mixed_dofs(CPU_SAMPLE_N), sec, scale)}
     if per_rank is not None:
         line["partition"] = per_rank
+        line["halo_transport"] = solver.dev.halo_transport
     print(json.dumps(line), flush=True)
 
 

@@ -289,6 +289,34 @@ int nsb_set_halo(nsb_ctx* ctx, int32_t which, int32_t n_owned, int32_t n_ghost, 
 int nsb_halo_exchange(nsb_ctx* ctx, int32_t which, int32_t bs, const double* x, double* ghost_dst,
                       void* stream);
 
+/* Halo exchange and scalar all-reduce through NVLink peer memory instead of NCCL (optional, after
+ * nsb_comm_init / nsb_set_halo; single node, CUDA IPC).
+ * nsb_p2p_export allocates this rank's IPC-shared block for `which` and returns its
+ * cudaIpcMemHandle (64 bytes):
+ *   which = NSB_HALO_NODES / NSB_HALO_VERTS: acknowledgement words + a ring of receive slots shaped
+ *           like the ghost block of that index space;
+ *   which = NSB_HALO_NONE: the all-reduce block of the Krylov scalars (2..8 ranks).
+ * The host gathers the handles of all ranks and calls nsb_p2p_connect
+ *   - for a halo plan with, per neighbour in plan order: its handle, its ghost count, the offset
+ *     (entries) of this rank's part inside its ghost block (its recv_ptr for this rank) and this
+ *     rank's index in its peer list;
+ *   - for NSB_HALO_NONE with npeers = nranks handles in rank order (own entry ignored), other
+ *     tables NULL.
+ * From then on nsb_halo_exchange (and the exchanges inside nsb_spmv / the Krylov solvers) is ONE
+ * kernel: gather the boundary values and store them, each double with the exchange's epoch beside
+ * it, into the neighbours' ring slots over NVLink; poll the local slot until every line carries the
+ * epoch, write the ghosts, acknowledge.  The all-reduce of the inner products (<= 64 doubles) is one
+ * single-block kernel of the same kind, summing in rank order (bit-identical on all ranks).
+ * Waits are bounded; nsb_p2p_status returns a non-zero error word if one ever timed out (1: a
+ * neighbour stopped consuming, 2: a neighbour stopped sending, 3: all-reduce).  All ranks must use
+ * the same transport: nsb_p2p_disconnect (after a host barrier) returns to NCCL;
+ * nsb_comm_finalize unmaps and frees the blocks (call it after a host barrier). */
+int nsb_p2p_export(nsb_ctx* ctx, int32_t which, uint8_t* handle_out64);
+int nsb_p2p_connect(nsb_ctx* ctx, int32_t which, int32_t npeers, const uint8_t* handles64,
+                    const int32_t* peer_n_ghost, const int32_t* peer_off, const int32_t* my_slot);
+int nsb_p2p_status(nsb_ctx* ctx, int32_t* error_out);
+int nsb_p2p_disconnect(nsb_ctx* ctx);   /* back to NCCL send/recv (all ranks, after a host barrier) */
+
 /* ---------------------------------------------------------------- instrumentation ------- */
 /* Per-kernel-class CUDA-event timing on the launching stream (SURVEY.md 8b nsb_timer_*).
  * enable != 0 starts recording an event pair around every launch group of every class;

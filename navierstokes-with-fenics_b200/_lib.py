@@ -92,6 +92,10 @@ PROTOTYPES = {
     "nsb_comm_init": (C.c_int, [vp, C.c_int32, C.c_int32, vp]),
     "nsb_comm_finalize": (C.c_int, [vp]),
     "nsb_set_halo": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_p2p_export": (C.c_int, [vp, C.c_int32, vp]),
+    "nsb_p2p_connect": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp]),
+    "nsb_p2p_status": (C.c_int, [vp, c_i32p]),
+    "nsb_p2p_disconnect": (C.c_int, [vp]),
     "nsb_halo_exchange": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp]),
     "nsb_timer_enable": (C.c_int, [vp, C.c_int32]),
     "nsb_timer_report": (C.c_int, [vp, c_f64p, c_i64p]),

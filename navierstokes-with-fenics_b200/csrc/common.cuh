@@ -48,13 +48,66 @@ struct nsb_halo {
     const int32_t* send_idx = nullptr;                // dev [send_ptr.back()] local owned indices
     double* sendbuf = nullptr;                        // dev [send_ptr.back() * 3], caller-owned
     double* ghostbuf = nullptr;                       // dev [n_ghost * 3], caller-owned (SpMV ghosts)
+    // peer-memory path (comm.cu, nsb_p2p_*): a library-owned, IPC-shared block per rank = header of
+    // uint64 acknowledgement words (ack[j][b] = newest of my epochs block b of neighbour j has consumed)
+    // followed by a ring of NSB_P2P_RING receive slots of p2p_cap 16-byte lines {lo, epoch, hi, epoch},
+    // each slot shaped like the ghost block (x3 components)
+    void* p2p_block = nullptr;
+    int64_t p2p_cap = 0;
+    uint64_t p2p_epoch = 0;
+    bool p2p_ready = false;
+    std::vector<void*> peer_block;                    // mapped blocks of the neighbours
+    std::vector<long long> peer_cap;                  // doubles per ring slot of neighbour i
+    std::vector<int32_t> peer_off;                    // offset (entries) of my part inside neighbour i's ghost block
+    std::vector<int32_t> my_slot;                     // my index in neighbour i's peer list
 };
+#define NSB_P2P_RING 4
+#define NSB_P2P_HDR_BYTES 8192
+#define NSB_AR_RING 4
+#define NSB_AR_MAX 64
+
+// ---- peer-memory lines (comm.cu): one double travels as a 16-byte line {lo, epoch, hi, epoch}; a reader
+// polls until both flags carry the epoch it waits for (8-byte store atomicity is all this needs)
+#ifdef __CUDACC__
+__device__ __forceinline__ void nsb_st_line(uint4* p, double v, unsigned int flag) {
+    const unsigned long long u = (unsigned long long)__double_as_longlong(v);
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned int)u), "r"(flag),
+                 "r"((unsigned int)(u >> 32)), "r"(flag) : "memory");
+}
+__device__ __forceinline__ uint4 nsb_ld_line(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+#define NSB_P2P_SPIN_CYCLES 60000000000ll        // bounded waits: ~30 s, then the error word is raised
+// wait for line p of epoch `flag`; on a timeout (or once the error word is set) return what is there
+__device__ __forceinline__ double nsb_wait_line(const uint4* p, unsigned int flag, int* err, int code) {
+    uint4 v = nsb_ld_line(p);
+    if (v.y != flag || v.w != flag) {
+        if (*(volatile int*)err == 0) {
+            const long long t0 = clock64();
+            do {
+                if (clock64() - t0 > NSB_P2P_SPIN_CYCLES) { *err = code; break; }
+                v = nsb_ld_line(p);
+            } while (v.y != flag || v.w != flag);
+        }
+    }
+    return __longlong_as_double((long long)(((unsigned long long)v.z << 32) | v.x));
+}
+#endif
 
 struct nsb_ctx {
     int device = 0;
     // multi-GPU (comm.cu): one rank per GPU, NCCL communicator created by nsb_comm_init
     int rank = 0, nranks = 1;
     void* nccl_comm = nullptr;
+    int* d_p2p_err = nullptr;         // device error word of the peer-memory kernels (0 = fine)
+    // peer-memory all-reduce of the Krylov scalars (comm.cu): IPC block = ring of NSB_AR_RING slots x
+    // nranks senders x NSB_AR_MAX 16-byte lines; ar_peer[r] = rank r's block (own block at [rank])
+    void* ar_block = nullptr;
+    std::vector<void*> ar_peer;
+    uint64_t ar_epoch = 0;
+    bool ar_ready = false;
     nsb_halo halo[3];                 // [NSB_HALO_NODES], [NSB_HALO_VERTS]; [0] unused
     int sm_count = 148;
     std::string err;

@@ -1,6 +1,7 @@
 """Device-side state of one mesh: PyTorch tensors as device buffers (plumbing only), the
 nsb_ctx of libnsb200.so, patterns and the thin typed wrappers around the C-ABI calls."""
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -161,15 +162,89 @@ class Device:
                                              peers.ctypes.data, sp_.ctypes.data, _ptr(send_idx), rp_.ctypes.data,
                                              _ptr(sendbuf), _ptr(ghostbuf)))
             self._halo_keep.append((send_idx, sendbuf, ghostbuf))
+        self.halo_transport = "nccl"
+        if part.nranks > 1 and os.environ.get("NSB_HALO", "p2p") != "nccl":
+            self._connect_peer_memory(part)
+
+    def _connect_peer_memory(self, part):
+        """Halo exchange over NVLink peer memory (nsb_p2p_*): every rank exports its IPC block, the
+        handles and ghost layouts travel through torch.distributed, every rank maps its neighbours.
+        All-or-nothing: if any rank cannot map a neighbour, every rank stays on NCCL send/recv."""
+        import torch.distributed as dist
+        mine, ok = {}, True
+        try:
+            for which, pl in ((L.HALO_NODES, part.nodes), (L.HALO_VERTS, part.verts)):
+                buf = (C.c_uint8 * 64)()
+                self.check(self.lib.nsb_p2p_export(self.ctx, which, buf))
+                mine[which] = dict(handle=bytes(buf), peers=[int(r) for r in pl.peers],
+                                   recv_ptr=[int(v) for v in pl.recv_ptr], n_ghost=int(pl.n_ghost))
+            if part.nranks <= 8:                          # all-reduce block of the Krylov scalars
+                buf = (C.c_uint8 * 64)()
+                self.check(self.lib.nsb_p2p_export(self.ctx, L.HALO_NONE, buf))
+                mine[L.HALO_NONE] = dict(handle=bytes(buf))
+        except RuntimeError:
+            ok = False
+        everyone = [None] * part.nranks
+        dist.all_gather_object(everyone, (ok, mine))
+        ok = all(e[0] for e in everyone)
+        if ok:
+            try:
+                for which, pl in ((L.HALO_NODES, part.nodes), (L.HALO_VERTS, part.verts)):
+                    handles, nghost, off, slot = b"", [], [], []
+                    for r in pl.peers:
+                        theirs = everyone[int(r)][1][which]
+                        s = theirs["peers"].index(part.rank)
+                        handles += theirs["handle"]
+                        nghost.append(theirs["n_ghost"])
+                        off.append(theirs["recv_ptr"][s])
+                        slot.append(s)
+                    hb = (C.c_uint8 * max(len(handles), 1)).from_buffer_copy(handles or b"\0")
+                    ng, of, sl = (np.asarray(a, dtype=np.int32) for a in (nghost, off, slot))
+                    self.check(self.lib.nsb_p2p_connect(self.ctx, which, len(pl.peers), hb, ng.ctypes.data,
+                                                        of.ctypes.data, sl.ctypes.data))
+                if part.nranks <= 8:
+                    handles = b"".join(e[1][L.HALO_NONE]["handle"] for e in everyone)
+                    hb = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
+                    self.check(self.lib.nsb_p2p_connect(self.ctx, L.HALO_NONE, part.nranks, hb, None, None, None))
+            except (RuntimeError, ValueError, KeyError):
+                ok = False
+        verdict = [None] * part.nranks
+        dist.all_gather_object(verdict, ok)              # also the barrier between connect and first use
+        if all(verdict):
+            self.halo_transport = "p2p"
+        else:
+            self.check(self.lib.nsb_p2p_disconnect(self.ctx))
+            dist.barrier()
+
+    def halo_status(self):
+        """raise if a bounded wait of the peer-memory halo exchange ever timed out"""
+        if self.partition is None or self.halo_transport != "p2p":
+            return
+        err = C.c_int32(0)
+        self.check(self.lib.nsb_p2p_status(self.ctx, C.byref(err)))
+        if err.value:
+            raise RuntimeError("peer-memory halo exchange timed out (code %d: %s)" % (
+                err.value, {1: "a neighbour stopped consuming", 2: "a neighbour stopped sending"}.get(err.value, "?")))
 
     def close(self):
         """collective on a partitioned run (every rank calls it): tears the NCCL communicator
         down, then frees the context"""
         if getattr(self, "ctx", None):
             if self.partition is not None:
+                if self.partition.nranks > 1:
+                    import torch.distributed as dist
+                    torch.cuda.synchronize(self.torch_device)
+                    try:
+                        self.halo_status()
+                        failure = None
+                    except RuntimeError as e:
+                        failure = e
+                    dist.barrier()                       # nobody pushes into a block that is being freed
                 self.check(self.lib.nsb_comm_finalize(self.ctx))
             self.lib.nsb_destroy(self.ctx)
             self.ctx = None
+            if self.partition is not None and self.partition.nranks > 1 and failure is not None:
+                raise failure
 
     def halo_exchange(self, which, bs, x):
         """refresh the ghost block of the [owned | ghost] vector ``x`` from the owners (no-op on
@@ -358,7 +433,7 @@ class Device:
                                                self.stream))
         return np.array(out[:self.dim])
 
-    def direct_solve(self, pattern, vals, b, x, reorder=3):
+    def direct_solve(self, pattern, vals, b, x, reorder=1):
         """K16 (library leg): x = A^-1 b by cuSOLVER sparse QR; returns the seconds it took."""
         pat = self.patterns[pattern]
         sec = C.c_double()

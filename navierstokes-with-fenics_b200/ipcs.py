@@ -276,6 +276,7 @@ class IPCSSolver(SolverBase):
         n_c, _ = dev.cg(self._mass, self._dinv_mass, self._bV, self._velocities[0], rtol=self._linear_rtol,
                         work=self._work)
         dev.halo_exchange(L.HALO_NODES, d, self._velocities[0])
+        dev.halo_status()
         self.krylov_iterations.append(dict(momentum=kry, pressure=n_p, correction=n_c))
         del a0
 

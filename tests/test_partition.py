@@ -127,19 +127,23 @@ def test_halo_plans_over_gloo_world_size_2(tmp_path, dim, n):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("transport", ["p2p", "nccl"])
 @pytest.mark.parametrize("cfg", ["--dim 3 --cells 6 --flow cavity", "--dim 3 --cells 5 --flow channel",
                                  "--dim 2 --cells 12 --flow channel"])
-def test_partitioned_ipcs_matches_single_gpu(cfg):
+def test_partitioned_ipcs_matches_single_gpu(cfg, transport):
     """2 ranks / 2 GPUs through torchrun: fields of the partitioned run equal the single-GPU run to
-    1e-8 (observed 1e-13) with identical Newton and Krylov iteration counts."""
+    1e-8 (observed 1e-13) with identical Newton and Krylov iteration counts, with the halo exchange
+    over NVLink peer memory (default) and over NCCL send/recv (NSB_HALO=nccl)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
            "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tools", "run_partitioned.py")] + cfg.split()
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT,
+                         env=dict(os.environ, NSB_HALO=transport))
     lines = [l for l in res.stdout.splitlines() if l.startswith("{")]
     assert res.returncode == 0 and lines, res.stderr[-3000:]
     rep = json.loads(lines[-1])
+    assert rep["halo_transport"] == transport
     assert rep["ok"] and rep["rel_err_velocity"] < 1e-8 and rep["rel_err_pressure"] < 1e-8
     assert rep["newton"]["partitioned"] == rep["newton"]["single"]

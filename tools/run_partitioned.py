@@ -112,7 +112,8 @@ def main():
                           "krylov": {"partitioned": gathered[0]["krylov"], "single": ref.krylov_iterations},
                           "cells_per_rank": [g["cells"] for g in gathered],
                           "ghost_nodes_per_rank": [g["ghosts"] for g in gathered],
-                          "launches_per_rank": [g["launches"] for g in gathered]}), flush=True)
+                          "launches_per_rank": [g["launches"] for g in gathered],
+                          "halo_transport": solver.dev.halo_transport}), flush=True)
     solver.dev.close()
     flag = [ok]
     dist.broadcast_object_list(flag, src=0)
