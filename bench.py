@@ -171,7 +171,8 @@ def algorithmic_bytes(solver):
     geo = 8 * 3 * nverts + 4 * 4 * ncells + 4 * 10 * ncells    # coords + cell->vertex + cell->node maps
     return {
         "spmv_bsr": 8 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,
-        "spmv_bsr_f32": 4 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,   # FP32 value copy (preconditioner only)
+        # all-FP32 SpMV of the preconditioner: FP32 values, x and y as one float4 per node
+        "spmv_bsr_f32": 4 * 9 * nnz22 + 4 * nnz22 + 2 * 16 * nnodes + 4 * nnodes,
         "spmv_csr": None,                                       # two different matrices share the class
         "asm_jacobian": 8 * 9 * nnz22 + geo + 8 * nV,
         "asm_residual": 8 * nV + geo + 8 * (3 * nV + nQ),

@@ -106,6 +106,12 @@ typedef struct nsb_precond {
     int32_t degree;
     const double* inv_diag;  /* dev [nrows*bs], nsb_inv_diagonal */
     double lambda_min, lambda_max;
+    int32_t lowp;            /* Chebyshev inside nsb_gmres on a BSR matrix with vals32 and tiles: 1 = the whole
+                                polynomial runs in single precision (values, vectors padded to a float4 per
+                                node, arithmetic) and GMRES runs FLEXIBLE (keeps z_j = M^-1 v_j, x += Z y), so
+                                the rounding inside M never enters the solution: Arnoldi, the residual test and
+                                the operator stay FP64.  Ignored by nsb_cg. */
+    int32_t reserved;
 } nsb_precond;
 
 /* ---------------------------------------------------------------- life cycle ---------- */
@@ -208,7 +214,7 @@ int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void
 /* inv_diag[i] = 1/A_ii (1 on masked rows): Jacobi preconditioner (K12) */
 int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_diag, void* stream);
 int64_t nsb_cg_workspace_doubles(int64_t n);
-int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart);
+int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart, int32_t flexible /* = M->lowp */);
 /* Preconditioned CG for the SPD pressure-Poisson and mass systems which the reference solves by
  * LU (source/ns_ipcs_solver.py:171,195-196).  nullspace != 0: the operator has the constant
  * null space (all-Neumann pressure): rhs and solution are projected to zero

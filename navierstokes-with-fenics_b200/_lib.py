@@ -35,7 +35,7 @@ class Matrix(C.Structure):
 class Precond(C.Structure):
     """struct nsb_precond"""
     _fields_ = [("kind", C.c_int32), ("degree", C.c_int32), ("inv_diag", vp), ("lambda_min", C.c_double),
-                ("lambda_max", C.c_double)]
+                ("lambda_max", C.c_double), ("lowp", C.c_int32), ("reserved", C.c_int32)]
 
 
 PC_NONE, PC_JACOBI, PC_CHEBYSHEV = 0, 1, 2
@@ -69,7 +69,7 @@ PROTOTYPES = {
     "nsb_spmv": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp]),
     "nsb_inv_diagonal": (C.c_int, [vp, C.POINTER(Matrix), vp, vp]),
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
-    "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32]),
+    "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, vp, c_f64p, vp]),
     "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                          vp, c_i32p, c_f64p, vp]),

@@ -55,6 +55,73 @@ k_cheb_step(int64_t n, const double* __restrict__ dinv, const double* __restrict
     }
 }
 
+// ---- the same recurrences in single precision, one thread per node, vectors padded to NSB_PAD32(BS)
+// floats per node (float4 for BS = 3) so that every access is one aligned vector and the SpMV gathers a
+// block column with one load.  Input v and the result zout are ordinary FP64 dof vectors.
+template <int BS> struct Pad32;
+template <> struct Pad32<3> {
+    static __device__ __forceinline__ void ld(const float* p, int64_t i, float (&v)[3]) {
+        const float4 t = reinterpret_cast<const float4*>(p)[i];
+        v[0] = t.x; v[1] = t.y; v[2] = t.z;
+    }
+    static __device__ __forceinline__ void st(float* p, int64_t i, const float (&v)[3]) {
+        reinterpret_cast<float4*>(p)[i] = make_float4(v[0], v[1], v[2], 0.0f);
+    }
+};
+template <> struct Pad32<2> {
+    static __device__ __forceinline__ void ld(const float* p, int64_t i, float (&v)[2]) {
+        const float2 t = reinterpret_cast<const float2*>(p)[i];
+        v[0] = t.x; v[1] = t.y;
+    }
+    static __device__ __forceinline__ void st(float* p, int64_t i, const float (&v)[2]) {
+        reinterpret_cast<float2*>(p)[i] = make_float2(v[0], v[1]);
+    }
+};
+
+// r = D^-1 v ; d = r / theta ; z = d      (zout != null: degree 1, the result goes straight to zout)
+template <int BS>
+__global__ void __launch_bounds__(256)
+k_cheb32_first(int64_t nnodes, const double* __restrict__ dinv, const double* __restrict__ v, float inv_theta,
+               float* __restrict__ r, float* __restrict__ d, float* __restrict__ z, double* __restrict__ zout) {
+    GRID_STRIDE(i, nnodes) {
+        float c[BS], di[BS];
+#pragma unroll
+        for (int b = 0; b < BS; ++b) {
+            c[b] = (float)(dinv[i * BS + b] * v[i * BS + b]);
+            di[b] = c[b] * inv_theta;
+        }
+        if (zout) {
+#pragma unroll
+            for (int b = 0; b < BS; ++b) zout[i * BS + b] = (double)di[b];
+        } else {
+            Pad32<BS>::st(r, i, c); Pad32<BS>::st(d, i, di); Pad32<BS>::st(z, i, di);
+        }
+    }
+}
+
+// r -= D^-1 q ; d = a d + b r ; z += d     (zout != null: last step, only zout = z + d is written)
+template <int BS>
+__global__ void __launch_bounds__(256)
+k_cheb32_step(int64_t nnodes, const double* __restrict__ dinv, const float* __restrict__ q, float a, float b,
+              float* __restrict__ r, float* __restrict__ d, float* __restrict__ z, double* __restrict__ zout) {
+    GRID_STRIDE(i, nnodes) {
+        float qi[BS], ri[BS], di[BS], zi[BS];
+        Pad32<BS>::ld(q, i, qi); Pad32<BS>::ld(r, i, ri); Pad32<BS>::ld(d, i, di); Pad32<BS>::ld(z, i, zi);
+#pragma unroll
+        for (int c = 0; c < BS; ++c) {
+            ri[c] -= (float)dinv[i * BS + c] * qi[c];
+            di[c] = a * di[c] + b * ri[c];
+            zi[c] += di[c];
+        }
+        if (zout) {
+#pragma unroll
+            for (int c = 0; c < BS; ++c) zout[i * BS + c] = (double)zi[c];
+        } else {
+            Pad32<BS>::st(r, i, ri); Pad32<BS>::st(d, i, di); Pad32<BS>::st(z, i, zi);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // CG kernels
 // ---------------------------------------------------------------------------------------------
@@ -148,9 +215,48 @@ static int fetch(nsb_ctx* ctx, int slot, int count, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 // preconditioner application  z = M^-1 v   (scratch: 3 n doubles for Chebyshev)
 // ---------------------------------------------------------------------------------------------
+bool nsb_spmv32_available(const nsb_matrix* A);
+int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st);
+
+// the single-precision Chebyshev polynomial is not exactly linear in v (FP32 rounding): only the flexible
+// GMRES may use it
+static bool pc_single_precision(const nsb_matrix* A, const nsb_precond* M) {
+    return M->kind == NSB_PC_CHEBYSHEV && M->lowp && nsb_spmv32_available(A);
+}
+
+template <int BS>
+static int apply_cheb32(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* v, double* zout,
+                        double* scratch, cudaStream_t st) {
+    constexpr int PB = BS == 3 ? 4 : BS;
+    const int64_t nn = A->nrows;
+    const int G = krylov_grid(ctx, nn);
+    float* r = reinterpret_cast<float*>(((uintptr_t)scratch + 15) & ~(uintptr_t)15);   // 4 x PB nn floats <= 3 n doubles
+    float *d = r + PB * nn, *q = d + PB * nn, *z = q + PB * nn;
+    const double theta = 0.5 * (M->lambda_max + M->lambda_min), delta = 0.5 * (M->lambda_max - M->lambda_min);
+    const double sigma1 = theta / delta;
+    double rho_old = 1.0 / sigma1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cheb32_first<BS><<<G, 256, 0, st>>>(nn, M->inv_diag, v, (float)(1.0 / theta), r, d, z, M->degree == 1 ? zout : nullptr);
+        NSB_LAUNCH_CHECK(ctx, "k_cheb32_first");
+    }
+    for (int k = 1; k < M->degree; ++k) {
+        if (nsb_launch_spmv32(ctx, A, d, q, st)) return -1;
+        const double rho = 1.0 / (2.0 * sigma1 - rho_old);
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cheb32_step<BS><<<G, 256, 0, st>>>(nn, M->inv_diag, q, (float)(rho * rho_old), (float)(2.0 * rho / delta), r, d, z,
+                                            k == M->degree - 1 ? zout : nullptr);
+        NSB_LAUNCH_CHECK(ctx, "k_cheb32_step");
+        rho_old = rho;
+    }
+    return 0;
+}
+
 static int apply_pc(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* v, double* z,
-                    double* scratch, int64_t n, cudaStream_t st) {
+                    double* scratch, int64_t n, cudaStream_t st, bool flexible = false) {
     const int G = krylov_grid(ctx, n);
+    if (flexible && pc_single_precision(A, M))
+        return A->bs == 3 ? apply_cheb32<3>(ctx, A, M, v, z, scratch, st) : apply_cheb32<2>(ctx, A, M, v, z, scratch, st);
     if (M->kind == NSB_PC_NONE) {
         NSB_CUDA(ctx, cudaMemcpyAsync(z, v, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
         return 0;
@@ -453,7 +559,11 @@ k_add(int64_t n, const double* __restrict__ t, double* __restrict__ x) {
 
 #define NSB_GMRES_MAX_RESTART 60
 
-extern "C" int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart) { return (int64_t)(restart + 6) * n; }
+// V (restart+1), w, t, Chebyshev scratch (3), and restart more for the preconditioned basis Z of the
+// flexible variant (M->lowp)
+extern "C" int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart, int32_t flexible) {
+    return (int64_t)(restart + 6 + (flexible ? restart : 0)) * n;
+}
 
 extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
                          double rtol, double atol, int32_t maxit, int32_t restart, double* work,
@@ -469,6 +579,11 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
     double* w = work + (int64_t)(m + 1) * n;
     double* t = w + n;
     double* scratch = t + n;                // 3 n (Chebyshev)
+    // Flexible GMRES (Saad 1993) when the preconditioner runs in single precision: z_j = M^-1 v_j is kept
+    // (Z, restart x n behind the scratch) and x += Z y, so the preconditioner need not be a fixed linear
+    // operator; Arnoldi, the Hessenberg system and the residual test stay FP64 on the FP64 matrix.
+    const bool flex = pc_single_precision(A, M);
+    double* Z = scratch + 3 * n;
     double* ds = ctx->d_scalars;
     double* hs = ctx->h_scalars;
     const int G = krylov_grid(ctx, n);
@@ -508,8 +623,9 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
         int j = 0;
         for (; j < m && it < maxit; ++j) {
             // w = A M^-1 v_j
-            if (apply_pc(ctx, A, M, V + (int64_t)j * n, t, scratch, n, st)) return -1;
-            if (nsb_launch_spmv(ctx, A, t, w, nullptr, nullptr, st)) return -1;
+            double* zj = flex ? Z + (int64_t)j * n : t;
+            if (apply_pc(ctx, A, M, V + (int64_t)j * n, zj, scratch, n, st, flex)) return -1;
+            if (nsb_launch_spmv(ctx, A, zj, w, nullptr, nullptr, st)) return -1;
             const int nk = j + 1;
             for (int pass = 0; pass < 2; ++pass) {   // CGS-2
                 double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
@@ -559,7 +675,7 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
             if (!(rnorm == rnorm)) return nsb_fail(ctx, "GMRES breakdown: NaN in the Arnoldi process%s%s");
             if (rnorm <= tol) { ++j; break; }
         }
-        // back substitution, x += M^-1 (V y)
+        // back substitution, x += M^-1 (V y)   [flexible: x += Z y]
         const int nk = j;
         for (int i = nk - 1; i >= 0; --i) {
             double s = g[i];
@@ -570,10 +686,10 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
         NSB_CUDA(ctx, cudaMemcpyAsync(ds + S_Y, hs + S_Y, sizeof(double) * nk, cudaMemcpyHostToDevice, st));
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-            k_combine<<<G, 256, 0, st>>>(n, nk, V, ds + S_Y, w);
+            k_combine<<<G, 256, 0, st>>>(n, nk, flex ? Z : V, ds + S_Y, flex ? t : w);
         }
         NSB_LAUNCH_CHECK(ctx, "k_combine");
-        if (apply_pc(ctx, A, M, w, t, scratch, n, st)) return -1;
+        if (!flex && apply_pc(ctx, A, M, w, t, scratch, n, st)) return -1;
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
             k_add<<<G, 256, 0, st>>>(n, t, x);

@@ -58,6 +58,34 @@ int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* 
     return 0;
 }
 
+// y = A32 x in single precision throughout (FP32 Chebyshev preconditioner, krylov.cu): x, y hold
+// NSB_PAD32(bs) floats per node.  On a partitioned mesh the padded node is moved as 8-byte words by the
+// ordinary halo exchange (a float4 = 2 doubles, a float2 = 1).
+bool nsb_spmv32_available(const nsb_matrix* A) {
+    return A->kind == NSB_BSR && A->vals32 && A->tiles && A->ntiles > 0 && (A->bs == 3 || A->bs == 2) &&
+           ((((uintptr_t)A->vals32) | ((uintptr_t)A->col) | ((uintptr_t)A->tiles)) & 15) == 0;
+}
+
+int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st) {
+    NSB_REQUIRE(ctx, A && nsb_spmv32_available(A), "matrix has no single-precision copy / row tiles");
+    NSB_REQUIRE(ctx, x && y && x != y, "bad vectors (x must not alias y)");
+    const int pb = NSB_PAD32(A->bs);
+    int32_t nown = INT32_MAX;
+    const float* xg = x;
+    if (ctx->nranks > 1) {
+        NSB_REQUIRE(ctx, A->halo == NSB_HALO_NODES || A->halo == NSB_HALO_VERTS, "matrix of a partitioned run needs a halo index space");
+        const nsb_halo& H = ctx->halo[A->halo];
+        NSB_REQUIRE(ctx, H.n_owned == A->nrows, "matrix rows are not the owned prefix of the halo plan");
+        if (nsb_halo_exchange(ctx, A->halo, pb / 2, reinterpret_cast<const double*>(x), nullptr, st)) return -1;
+        nown = H.n_owned;
+        xg = reinterpret_cast<const float*>(H.ghostbuf) - (int64_t)nown * pb;
+    }
+    NSB_TIMED(ctx, NSB_T_SPMV_BSR32, st);
+    NSB_COUNT(ctx, 1);
+    if (A->bs == 3) return launch_spmv_bsr_tma<3, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);
+    return launch_spmv_bsr_tma<2, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);
+}
+
 static int spmv_dispatch(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int32_t nown, const double* xg,
                          double* y, const double* dot_with, double* scalar_out, cudaStream_t st, bool lowp) {
     if (A->kind == NSB_CSR) {

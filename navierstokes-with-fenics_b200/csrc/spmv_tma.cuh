@@ -31,13 +31,28 @@ struct SpmvTmaCfg {
     static constexpr size_t SMEM = VAL_BYTES + COL_BYTES + NSB_TILE_WORDS * 4 + 16;
 };
 
-template <int BS, typename VT>
+// XT = double: x, y are ordinary dof vectors (BS doubles per node).  XT = float (with VT = float): the
+// all-single-precision SpMV of the FP32 Chebyshev preconditioner -- x and y hold NSB_PAD32(BS) floats per
+// node (BS = 3 padded to a float4), so a lane gathers a block column with ONE 16-byte load instead of
+// three scattered 8-byte ones (the FP64-vector kernel is L1TEX-wavefront bound on exactly those),
+// multiplies in FP32 and lane 0 stores the row as one vector.
+#define NSB_PAD32(BS) ((BS) == 3 ? 4 : (BS))
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int BS, typename VT, typename XT>
 __global__ void __launch_bounds__(SpmvTmaCfg<BS, VT>::THREADS)
 k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* __restrict__ col,
-               const VT* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
-               int32_t nown, const double* __restrict__ xg, double* __restrict__ y) {
+               const VT* __restrict__ vals, const uint8_t* __restrict__ mask, const XT* __restrict__ x,
+               int32_t nown, const XT* __restrict__ xg, XT* __restrict__ y) {
     using Cfg = SpmvTmaCfg<BS, VT>;
     constexpr int BB = Cfg::BB, NW = Cfg::THREADS / 32;
+    constexpr bool X32 = sizeof(XT) == 4;
+    constexpr int PB = X32 ? NSB_PAD32(BS) : BS;              // components stored per node in x / y
     extern __shared__ __align__(128) unsigned char smem[];
     VT* sv = reinterpret_cast<VT*>(smem);
     int32_t* sc = reinterpret_cast<int32_t*>(smem + Cfg::VAL_BYTES);
@@ -79,26 +94,45 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (uint32_t lr = w; lr < nrows; lr += NW) {
         const uint32_t o0 = shift + off[lr], o1 = shift + off[lr + 1];
-        double acc[BS];
+        XT acc[BS];
 #pragma unroll
-        for (int b = 0; b < BS; ++b) acc[b] = 0.0;
+        for (int b = 0; b < BS; ++b) acc[b] = (XT)0;
         for (uint32_t k = o0 + lane; k < o1; k += 32) {
             const int32_t cn = sc[k];
-            const double* xb = (cn < nown ? x : xg) + (int64_t)cn * BS;
-            double xv[BS];
+            const XT* xb = (cn < nown ? x : xg) + (int64_t)cn * PB;
+            XT xv[BS];
+            if constexpr (X32 && BS == 3) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(xb));
+                xv[0] = t.x; xv[1] = t.y; xv[2] = t.z;
+            } else if constexpr (X32 && BS == 2) {
+                const float2 t = __ldg(reinterpret_cast<const float2*>(xb));
+                xv[0] = t.x; xv[1] = t.y;
+            } else {
 #pragma unroll
-            for (int c = 0; c < BS; ++c) xv[c] = __ldg(xb + c);
+                for (int c = 0; c < BS; ++c) xv[c] = __ldg(xb + c);
+            }
             const VT* v = sv + (size_t)k * BB;
 #pragma unroll
             for (int r = 0; r < BS; ++r)
 #pragma unroll
-                for (int c = 0; c < BS; ++c) acc[r] += (double)v[r * BS + c] * xv[c];
+                for (int c = 0; c < BS; ++c) acc[r] += (XT)v[r * BS + c] * xv[c];
         }
 #pragma unroll
         for (int b = 0; b < BS; ++b) acc[b] = warp_sum(acc[b]);
-        if (lane < BS) {
+        if constexpr (X32) {
+            if (lane == 0) {
+                const int64_t node = (int64_t)(row0 + lr);
+                if (mask != nullptr) {
+#pragma unroll
+                    for (int b = 0; b < BS; ++b)
+                        if (mask[node * BS + b]) acc[b] = x[node * PB + b];
+                }
+                if constexpr (BS == 3) reinterpret_cast<float4*>(y)[node] = make_float4(acc[0], acc[1], acc[2], 0.0f);
+                else reinterpret_cast<float2*>(y)[node] = make_float2(acc[0], acc[1]);
+            }
+        } else if (lane < BS) {
             const int64_t d = (int64_t)(row0 + lr) * BS + lane;
-            double v = acc[0];
+            XT v = acc[0];
 #pragma unroll
             for (int b = 1; b < BS; ++b) v = (lane == b) ? acc[b] : v;
             if (mask != nullptr && mask[d]) v = x[d];
@@ -107,17 +141,17 @@ k_spmv_bsr_tma(const uint32_t* __restrict__ tiles, uint32_t nnz, const int32_t* 
     }
 }
 
-template <int BS, typename VT>
-static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const VT* vals, const double* x, int32_t nown,
-                               const double* xg, double* y, cudaStream_t st) {
+template <int BS, typename VT, typename XT = double>
+static int launch_spmv_bsr_tma(nsb_ctx* ctx, const nsb_matrix* A, const VT* vals, const XT* x, int32_t nown,
+                               const XT* xg, XT* y, cudaStream_t st) {
     using Cfg = SpmvTmaCfg<BS, VT>;
     static bool configured = false;
     if (!configured) {
-        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS, VT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS, VT, XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        NSB_CUDA(ctx, cudaFuncSetAttribute(k_spmv_bsr_tma<BS, VT, XT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         configured = true;
     }
-    k_spmv_bsr_tma<BS, VT><<<A->ntiles, Cfg::THREADS, Cfg::SMEM, st>>>(A->tiles, (uint32_t)A->nnz, A->col, vals,
+    k_spmv_bsr_tma<BS, VT, XT><<<A->ntiles, Cfg::THREADS, Cfg::SMEM, st>>>(A->tiles, (uint32_t)A->nnz, A->col, vals,
                                                                  A->bc_mask, x, nown, xg, y);
     NSB_LAUNCH_CHECK(ctx, "k_spmv_bsr_tma");
     return 0;

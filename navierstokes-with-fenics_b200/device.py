@@ -365,9 +365,11 @@ class Device:
     def inv_diagonal(self, A, out):
         self.check(self.lib.nsb_inv_diagonal(self.ctx, C.byref(A), _ptr(out), self.stream))
 
-    def precond(self, inv_diag, kind=L.PC_JACOBI, degree=1, lambda_min=0.0, lambda_max=0.0):
-        """nsb_precond descriptor; a plain tensor passed to cg/gmres means Jacobi."""
-        m = L.Precond(kind, degree, inv_diag.data_ptr() if inv_diag is not None else None, lambda_min, lambda_max)
+    def precond(self, inv_diag, kind=L.PC_JACOBI, degree=1, lambda_min=0.0, lambda_max=0.0, lowp=False):
+        """nsb_precond descriptor; a plain tensor passed to cg/gmres means Jacobi.  ``lowp``: the Chebyshev
+        polynomial runs in single precision inside a flexible GMRES (needs the matrix's vals32 copy)."""
+        m = L.Precond(kind, degree, inv_diag.data_ptr() if inv_diag is not None else None, lambda_min, lambda_max,
+                      1 if lowp else 0, 0)
         m._keep = inv_diag
         return m
 
@@ -397,11 +399,11 @@ class Device:
 
     def gmres(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None):
         n = A.nrows * A.bs
-        need = self.lib.nsb_gmres_workspace_doubles(n, restart)
+        M = self._pc(M)
+        need = self.lib.nsb_gmres_workspace_doubles(n, restart, M.lowp)
         if work is None or work.numel() < need:
             work = self.empty(need)
         it, res = C.c_int32(), C.c_double()
-        M = self._pc(M)
         st = self.lib.nsb_gmres(self.ctx, C.byref(A), C.byref(M), _ptr(b), _ptr(x), rtol, atol, maxit, restart,
                                 _ptr(work), C.byref(it), C.byref(res), self.stream)
         self.check(st)

@@ -55,17 +55,22 @@ class IPCSSolver(SolverBase):
         d = sp.dim
         self._A_mom = dev.empty(p22.nnz * d * d)
         # single-precision copy of the Jacobian values, read only by the SpMVs INSIDE the Chebyshev
-        # polynomial (a fixed linear preconditioner either way; GMRES itself applies the FP64 matrix)
-        assert preconditioner_precision in ("f32", "f64")
+        # polynomial; GMRES itself applies the FP64 matrix and tests the FP64 residual.
+        #   "f32"        the whole polynomial in single precision (values, padded vectors, arithmetic)
+        #                inside a flexible GMRES, which keeps z_j = M^-1 v_j and so tolerates the rounding
+        #   "f32-matrix" single-precision values only, FP64 vectors: still a fixed linear preconditioner
+        #   "f64"        everything FP64
+        assert preconditioner_precision in ("f32", "f32-matrix", "f64")
+        self._pc_lowp = momentum_preconditioner == "chebyshev" and preconditioner_precision == "f32"
         self._A_mom32 = dev.empty(p22.nnz * d * d, dtype=torch.float32) \
-            if (momentum_preconditioner == "chebyshev" and preconditioner_precision == "f32") else None
+            if (momentum_preconditioner == "chebyshev" and preconditioner_precision != "f64") else None
         self._A_mass = dev.empty(p22.nnz)
         self._A_lap = dev.empty(p11.nnz)
         nVo, nQo = self._nV_own, self._nQ_own
         self._bV, self._dxV, self._dinvV = dev.empty(nVo), dev.empty(nVo), dev.empty(nVo)
         self._dinv_mass = dev.empty(nVo)
         self._bQ, self._dinvQ = dev.empty(nQo), dev.empty(nQo)
-        self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nVo, gmres_restart),
+        self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nVo, gmres_restart, 1 if self._pc_lowp else 0),
                                    dev.lib.nsb_cg_workspace_doubles(nVo)))
         self._have_constant = False
         self._bc_ready = False
@@ -226,7 +231,7 @@ class IPCSSolver(SolverBase):
                 if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step
                     self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=8, work=self._work)
                 pc = dev.precond(self._dinvV, L.PC_CHEBYSHEV, self._cheb_degree, self._lmax / self._cheb_ratio,
-                                 self._lmax)
+                                 self._lmax, lowp=self._pc_lowp)
             else:
                 pc = dev.precond(self._dinvV)
             self._dxV.zero_()

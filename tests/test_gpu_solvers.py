@@ -172,6 +172,43 @@ def test_gmres_momentum_system(case):
         assert rel_max_err(x.cpu().numpy(), ref) < 1e-9
 
 
+def test_gmres_chebyshev_precisions(case):
+    """Chebyshev-preconditioned GMRES on the momentum Jacobian in its three precisions: FP64, FP32 value
+    copy with FP64 vectors (a fixed linear preconditioner), and the all-FP32 polynomial inside the
+    flexible GMRES.  All three must reach the sparse-LU solution: the rounding inside the
+    preconditioner must never enter the result."""
+    import torch
+    import nsb200._lib as L
+    dev, d = case["dev"], case["d"]
+    us = case["fields"][0]
+    pat = dev.patterns["P2P2"]
+    A = dev.empty(pat.nnz * d * d)
+    dev.assemble_ipcs_momentum(L.MAT, up(dev, us), A=A)
+    dofs, _ = dev.spaces.dirichlet_table([(1, None, (0.0,) * d), (3, None, (0.0,) * d)], "V")
+    dev.bc_apply_matrix("P2P2", A, L.BSR, d, up(dev, dofs))
+    A32 = dev.empty(A.numel(), dtype=torch.float32)
+    dev.to_f32(A, A32)
+    n = pat.nrows * d
+    rng = np.random.default_rng(17)
+    b = rng.uniform(-1, 1, n)
+    ref = spla.spsolve(bsr_to_csr(pat.rowptr_host, pat.col_host, A.cpu().numpy(), d).tocsc(), b)
+    its = {}
+    for mode in ("f64", "f32-matrix", "f32"):
+        mat = dev.matrix("P2P2", A, L.BSR, d, None, vals32=None if mode == "f64" else A32)
+        dinv = dev.empty(n)
+        dev.inv_diagonal(mat, dinv)
+        lmax = 1.1 * dev.lambda_max(mat, dinv, iters=10)
+        for degree in (1, 4):
+            pc = dev.precond(dinv, L.PC_CHEBYSHEV, degree, lmax / 30.0, lmax, lowp=(mode == "f32"))
+            x = dev.zeros(n)
+            for restart in (40, 6):      # the short restart exercises x += Z y across several cycles
+                x.zero_()
+                its[mode, degree, restart], _ = dev.gmres(mat, pc, up(dev, b), x, rtol=1e-13, restart=restart, maxit=5000)
+                assert rel_max_err(x.cpu().numpy(), ref) < 1e-9, (mode, degree, restart)
+    # the single-precision polynomial preconditions as well as the FP64 one
+    assert its["f32", 4, 40] <= its["f64", 4, 40] + 2, its
+
+
 def _channel_bcs(d):
     import nsb200
     V, P = nsb200.VelocityBCType, nsb200.PressureBCType
