@@ -104,14 +104,14 @@ def workload_config(n, gpus):
                         % (n, mixed_dofs(n)),
             "cells_per_edge": n, "mixed_dofs": mixed_dofs(n),
             "parallelism": "1 GPU" if gpus == 1 else
-                           "mesh partitioned into %d z-slabs, one rank per GPU (owned/ghost dofs, NCCL halo exchange "
-                           "before every SpMV / assembly, all-reduced Krylov inner products); roofline and breakdown "
-                           "are rank 0's share" % gpus,
+                           "mesh partitioned into %d z-slabs, one rank per GPU (owned/ghost dofs, halo exchange before "
+                           "every SpMV / assembly and all-reduced Krylov inner products, both over NVLink peer memory "
+                           "[NCCL with NSB_HALO=nccl]); roofline and breakdown are rank 0's share" % gpus,
             "l2_policy": "inputs larger than L2 (Jacobian 6.5 GB, Krylov basis 3.3 GB per GPU at n=73)",
-            "linear_solvers": "FP64 GMRES(40) right-preconditioned by a degree-4 Chebyshev polynomial in D^-1 J whose 3 inner "
-                              "SpMVs read a single-precision copy of the Jacobian values (operator, residuals and solution "
-                              "stay FP64), rtol 1e-12 (velocity); CG rtol 1e-12 with a degree-8 Chebyshev polynomial "
-                              "preconditioner (pressure) / Jacobi (mass)"}
+            "linear_solvers": "FP64 flexible GMRES(40), rtol 1e-12, right-preconditioned by a degree-8 Chebyshev polynomial "
+                              "in D^-1 J that runs in single precision (FP32 copy of the Jacobian values, float4-padded "
+                              "vectors; operator, Arnoldi basis, residual test and solution stay FP64) (velocity); CG rtol "
+                              "1e-12 with a degree-8 Chebyshev polynomial preconditioner (pressure) / Jacobi (mass)"}
 
 
 # ---------------------------------------------------------------------------------------------

@@ -542,6 +542,31 @@ k_multi_axpy(int64_t n, int nk, const double* __restrict__ V, const double* __re
     grid_sum<1, 256>(s, partials, counter, out, red);
 }
 
+// CGS-2, middle pass in one sweep over V (nk <= NV):  w -= sum_k h[k] V_k  and, with the V_k entries still
+// in registers, h2[k] = V_k . w  of the UPDATED w (the second Gram-Schmidt projection)
+template <int NV>
+__global__ void __launch_bounds__(256)
+k_multi_axpy_dot(int64_t n, int nk, const double* __restrict__ V, const double* __restrict__ h,
+                 double* __restrict__ w, double* partials, unsigned int* counter, double* out) {
+    double s[NV], hk[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) { s[k] = 0.0; hk[k] = k < nk ? h[k] : 0.0; }
+    GRID_STRIDE(i, n) {
+        double v[NV];
+        double wi = w[i];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            v[k] = k < nk ? V[(int64_t)k * n + i] : 0.0;
+            wi -= hk[k] * v[k];
+        }
+        w[i] = wi;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) s[k] += v[k] * wi;
+    }
+    __shared__ double red[NV * 8];
+    grid_sum<NV, 256>(s, partials, counter, out, red);
+}
+
 // u = sum_k y[k] V_k
 __global__ void __launch_bounds__(256)
 k_combine(int64_t n, int nk, const double* __restrict__ V, const double* __restrict__ y, double* __restrict__ u) {
@@ -627,7 +652,32 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
             if (apply_pc(ctx, A, M, V + (int64_t)j * n, zj, scratch, n, st, flex)) return -1;
             if (nsb_launch_spmv(ctx, A, zj, w, nullptr, nullptr, st)) return -1;
             const int nk = j + 1;
-            for (int pass = 0; pass < 2; ++pass) {   // CGS-2
+            // CGS-2.  Up to 16 basis vectors: three sweeps over V (dot | axpy + second dot | axpy + norm)
+            // instead of four, and one all-reduce less.
+            const bool fused = nk <= 16;
+            if (fused) {
+                {
+                    NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+                    if (nk <= 4) k_multi_dot<4><<<G, 256, 0, st>>>(n, 0, nk, V, w, ctx->d_partials, ctx->d_counter, ds + S_H1);
+                    else if (nk <= 8) k_multi_dot<8><<<G, 256, 0, st>>>(n, 0, nk, V, w, ctx->d_partials, ctx->d_counter, ds + S_H1);
+                    else k_multi_dot<16><<<G, 256, 0, st>>>(n, 0, nk, V, w, ctx->d_partials, ctx->d_counter, ds + S_H1);
+                }
+                if (nsb_allreduce_sum(ctx, ds + S_H1, nk, st)) return -1;
+                {
+                    NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+                    if (nk <= 4) k_multi_axpy_dot<4><<<G, 256, 0, st>>>(n, nk, V, ds + S_H1, w, ctx->d_partials, ctx->d_counter, ds + S_H2);
+                    else if (nk <= 8) k_multi_axpy_dot<8><<<G, 256, 0, st>>>(n, nk, V, ds + S_H1, w, ctx->d_partials, ctx->d_counter, ds + S_H2);
+                    else k_multi_axpy_dot<16><<<G, 256, 0, st>>>(n, nk, V, ds + S_H1, w, ctx->d_partials, ctx->d_counter, ds + S_H2);
+                }
+                if (nsb_allreduce_sum(ctx, ds + S_H2, nk, st)) return -1;
+                {
+                    NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+                    k_multi_axpy<<<G, 256, 0, st>>>(n, nk, V, ds + S_H2, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+                }
+                if (nsb_allreduce_sum(ctx, ds + S_NRM, 1, st)) return -1;
+                NSB_COUNT(ctx, 1);
+            }
+            for (int pass = 0; pass < 2 && !fused; ++pass) {   // CGS-2, more than 16 vectors: chunked dots
                 double* hdev = ds + (pass == 0 ? S_H1 : S_H2);
                 {
                     NSB_TIMED(ctx, NSB_T_KRYLOV, st);

@@ -17,7 +17,7 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged, newton_conv
 class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
-                 momentum_preconditioner="chebyshev", chebyshev_degree=4, chebyshev_ratio=30.0, partition=None,
+                 momentum_preconditioner="chebyshev", chebyshev_degree=8, chebyshev_ratio=30.0, partition=None,
                  preconditioner_precision="f32", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a

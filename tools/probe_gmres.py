@@ -42,9 +42,13 @@ torch.cuda.synchronize()
 print("lambda_max(8 its) = %.4f (%.1f ms); 30 its: %.4f" % (lmax, (time.time() - t) * 1e3,
                                                           dev.lambda_max(solver._jac, solver._dinvV, iters=30)))
 ref = None
-for kind, deg, ratio in [("jacobi", 1, 0)] + [("cheb", d, r) for d in (2, 3, 4, 6, 8) for r in (10.0, 30.0, 100.0)]:
+lowp = solver._pc_lowp
+if solver._A_mom32 is not None:
+    dev.to_f32(solver._A_mom, solver._A_mom32)
+print("single-precision polynomial / flexible GMRES:", lowp)
+for kind, deg, ratio in [("jacobi", 1, 0)] + [("cheb", d, r) for d in (3, 4, 5, 6, 8, 10) for r in (15.0, 30.0, 60.0)]:
     pc = dev.precond(solver._dinvV) if kind == "jacobi" else \
-        dev.precond(solver._dinvV, L.PC_CHEBYSHEV, deg, 1.1 * lmax / ratio, 1.1 * lmax)
+        dev.precond(solver._dinvV, L.PC_CHEBYSHEV, deg, 1.1 * lmax / ratio, 1.1 * lmax, lowp=lowp)
     solver._dxV.zero_()
     torch.cuda.synchronize()
     t = time.time()
