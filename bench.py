@@ -109,8 +109,9 @@ def workload_config(n, gpus):
                            "[NCCL with NSB_HALO=nccl]); roofline and breakdown are rank 0's share" % gpus,
             "l2_policy": "inputs larger than L2 (Jacobian 6.5 GB, Krylov basis 3.3 GB per GPU at n=73)",
             "linear_solvers": "FP64 flexible GMRES(40), rtol 1e-12, right-preconditioned by a degree-8 Chebyshev polynomial "
-                              "in D^-1 J that runs in single precision (FP32 copy of the Jacobian values, float4-padded "
-                              "vectors; operator, Arnoldi basis, residual test and solution stay FP64) (velocity); CG rtol "
+                              "in D^-1 J that runs in single precision on the block-scalar part of J (mean block diagonals as "
+                              "FP32, float4-padded vectors; operator, Arnoldi basis, residual test and solution stay FP64) "
+                              "(velocity); CG rtol "
                               "1e-12 with a degree-8 Chebyshev polynomial preconditioner (pressure) / Jacobi (mass)"}
 
 
@@ -171,8 +172,9 @@ def algorithmic_bytes(solver):
     geo = 8 * 3 * nverts + 4 * 4 * ncells + 4 * 10 * ncells    # coords + cell->vertex + cell->node maps
     return {
         "spmv_bsr": 8 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,
-        # all-FP32 SpMV of the preconditioner: FP32 values, x and y as one float4 per node
-        "spmv_bsr_f32": 4 * 9 * nnz22 + 4 * nnz22 + 2 * 16 * nnodes + 4 * nnodes,
+        # single-precision SpMV of the preconditioner on the block-scalar part of J: one float + one column
+        # index per block entry, x and y as one float4 per node, row offsets
+        "spmv_bsr_f32": 4 * nnz22 + 4 * nnz22 + 2 * 16 * nnodes + 4 * nnodes,
         "spmv_csr": None,                                       # two different matrices share the class
         "asm_jacobian": 8 * 9 * nnz22 + geo + 8 * nV,
         "asm_residual": 8 * nV + geo + 8 * (3 * nV + nQ),

@@ -94,6 +94,10 @@ typedef struct nsb_matrix {
     const float* vals32;     /* dev [nnz*bs*bs] or NULL: single-precision copy of a BSR matrix's values
                                 (nsb_vec_to_f32).  Read ONLY by the SpMVs inside the Chebyshev
                                 preconditioner; every operator application of the solvers stays FP64 */
+    const float* diag32;     /* dev [nnz] or NULL: block-scalar approximation S (x) I of a BSR matrix, S_ij = mean of
+                                the diagonal of block ij (nsb_bsr_block_scalar_f32).  Read ONLY by the single-
+                                precision Chebyshev polynomial inside the flexible nsb_gmres (nsb_precond.lowp),
+                                in preference to vals32: 8 instead of 40 bytes per block entry */
 } nsb_matrix;
 
 /* preconditioners of nsb_cg / nsb_gmres (K12) */
@@ -317,6 +321,9 @@ int nsb_halo_exchange(nsb_ctx* ctx, int32_t which, int32_t bs, const double* x, 
  * neighbour stopped consuming, 2: a neighbour stopped sending, 3: all-reduce).  All ranks must use
  * the same transport: nsb_p2p_disconnect (after a host barrier) returns to NCCL;
  * nsb_comm_finalize unmaps and frees the blocks (call it after a host barrier). */
+/* out[k] = (float) mean of the diagonal of block k of a BSR value array (nsb_matrix.diag32) */
+int nsb_bsr_block_scalar_f32(nsb_ctx* ctx, int64_t nnz, int32_t bs, const double* vals_dev, float* out_dev, void* stream);
+
 int nsb_p2p_export(nsb_ctx* ctx, int32_t which, uint8_t* handle_out64);
 int nsb_p2p_connect(nsb_ctx* ctx, int32_t which, int32_t npeers, const uint8_t* handles64,
                     const int32_t* peer_n_ghost, const int32_t* peer_off, const int32_t* my_slot);

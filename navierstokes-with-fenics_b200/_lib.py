@@ -29,7 +29,7 @@ class Matrix(C.Structure):
     """struct nsb_matrix"""
     _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
                 ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp), ("tiles", vp),
-                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp)]
+                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp), ("diag32", vp)]
 
 
 class Precond(C.Structure):
@@ -92,6 +92,7 @@ PROTOTYPES = {
     "nsb_comm_init": (C.c_int, [vp, C.c_int32, C.c_int32, vp]),
     "nsb_comm_finalize": (C.c_int, [vp]),
     "nsb_set_halo": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_bsr_block_scalar_f32": (C.c_int, [vp, C.c_int64, C.c_int32, vp, vp, vp]),
     "nsb_p2p_export": (C.c_int, [vp, C.c_int32, vp]),
     "nsb_p2p_connect": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp]),
     "nsb_p2p_status": (C.c_int, [vp, c_i32p]),

@@ -62,12 +62,112 @@ int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* 
 // NSB_PAD32(bs) floats per node.  On a partitioned mesh the padded node is moved as 8-byte words by the
 // ordinary halo exchange (a float4 = 2 doubles, a float2 = 1).
 bool nsb_spmv32_available(const nsb_matrix* A) {
-    return A->kind == NSB_BSR && A->vals32 && A->tiles && A->ntiles > 0 && (A->bs == 3 || A->bs == 2) &&
+    if (A->kind != NSB_BSR || (A->bs != 3 && A->bs != 2)) return false;
+    if (A->diag32) return true;
+    return A->vals32 && A->tiles && A->ntiles > 0 &&
            ((((uintptr_t)A->vals32) | ((uintptr_t)A->col) | ((uintptr_t)A->tiles)) & 15) == 0;
 }
 
+// Block-scalar approximation S (x) I of a BSR matrix, S_ij = mean of the diagonal of block ij, in single
+// precision (nsb_matrix.diag32): y_i = sum_j S_ij x_j on NSB_PAD32(BS)-padded node vectors.  8 bytes per
+// block entry instead of 40: the momentum Jacobian is (mass/dt + diffusion + convection) (x) I plus the
+// lower-order Newton coupling, so as a PRECONDITIONER the scalar part does as well as the full blocks
+// (same GMRES iteration counts, tools/probe_scalar_pc.py).  LANES lanes per row, coalesced value / column
+// streams, one 16-byte gather per entry.
+template <int BS, int LANES, int U>
+__global__ void __launch_bounds__(256)
+k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+              const float* __restrict__ s, const float* __restrict__ x, int32_t nown, const float* __restrict__ xg,
+              float* __restrict__ y) {
+    constexpr int PB = NSB_PAD32(BS);
+    const int lane = threadIdx.x % LANES;
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
+    if (row >= nrows) return;                      // whole lane groups leave together
+    float acc[BS];
+#pragma unroll
+    for (int b = 0; b < BS; ++b) acc[b] = 0.0f;
+    const int32_t end = rowptr[row + 1];
+    // The kernel is latency bound (a row is ~28 entries: row offsets -> columns -> gather is a chain of three
+    // dependent loads and then the warp is done), so every lane keeps U independent gathers in flight.
+    for (int32_t k = rowptr[row] + lane; k < end; k += LANES * U) {
+        int32_t cn[U];
+        float v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int32_t kk = k + u * LANES;
+            const bool ok = kk < end;
+            cn[u] = ok ? col[kk] : (int32_t)row;
+            v[u] = ok ? s[kk] : 0.0f;
+        }
+        if constexpr (BS == 3) {
+            float4 t[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                t[u] = __ldg(reinterpret_cast<const float4*>((cn[u] < nown ? x : xg) + (int64_t)cn[u] * PB));
+#pragma unroll
+            for (int u = 0; u < U; ++u) { acc[0] += v[u] * t[u].x; acc[1] += v[u] * t[u].y; acc[2] += v[u] * t[u].z; }
+        } else {
+            float2 t[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                t[u] = __ldg(reinterpret_cast<const float2*>((cn[u] < nown ? x : xg) + (int64_t)cn[u] * PB));
+#pragma unroll
+            for (int u = 0; u < U; ++u) { acc[0] += v[u] * t[u].x; acc[1] += v[u] * t[u].y; }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < BS; ++b)
+#pragma unroll
+        for (int o = LANES / 2; o > 0; o >>= 1) acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], o, LANES);
+    if (lane == 0) {
+        if constexpr (BS == 3) reinterpret_cast<float4*>(y)[row] = make_float4(acc[0], acc[1], acc[2], 0.0f);
+        else reinterpret_cast<float2*>(y)[row] = make_float2(acc[0], acc[1]);
+    }
+}
+
+template <int BS>
+static int launch_spmv_kron32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, int32_t nown, const float* xg, float* y,
+                              cudaStream_t st) {
+    const double per_row = (double)A->nnz / (double)A->nrows;
+    static int forced = -1;                        // development override: NSB_KRON_LANES = 4 | 8 | 16 | 32
+    if (forced < 0) { const char* e = getenv("NSB_KRON_LANES"); forced = e ? atoi(e) : 0; }
+    const int code = forced ? forced : (per_row <= 40.0 ? 4 : 8);
+    const int lanes = code > 32 ? code / 10 : code;          // 48 = 4 lanes x 8 gathers, 28, 88 likewise
+    const int blocks = nsb_blocks((int64_t)A->nrows * lanes, 256);
+#define NSB_KRON(LANES, U) k_spmv_kron32<BS, LANES, U><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y)
+    if (code == 2) NSB_KRON(2, 4);
+    else if (code == 28) NSB_KRON(2, 8);
+    else if (code == 4) NSB_KRON(4, 4);
+    else if (code == 48) NSB_KRON(4, 8);
+    else if (code == 88) NSB_KRON(8, 8);
+    else if (lanes == 8) NSB_KRON(8, 4);
+    else if (lanes == 16) NSB_KRON(16, 2);
+    else NSB_KRON(32, 2);
+#undef NSB_KRON
+    NSB_LAUNCH_CHECK(ctx, "k_spmv_kron32");
+    return 0;
+}
+
+// out[k] = mean of the diagonal of block k
+__global__ void __launch_bounds__(256)
+k_block_scalar(int64_t nnz, int bs, const double* __restrict__ vals, float* __restrict__ out) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nnz) return;
+    const double* b = vals + k * bs * bs;
+    double sdiag = 0.0;
+    for (int i = 0; i < bs; ++i) sdiag += b[i * (bs + 1)];
+    out[k] = (float)(sdiag / bs);
+}
+extern "C" int nsb_bsr_block_scalar_f32(nsb_ctx* ctx, int64_t nnz, int32_t bs, const double* vals, float* out, void* stream) {
+    NSB_REQUIRE(ctx, ctx && vals && out && nnz >= 0 && bs >= 1 && bs <= 3, "bad arguments");
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
+    k_block_scalar<<<nsb_blocks(nnz, 256), 256, 0, (cudaStream_t)stream>>>(nnz, bs, vals, out);
+    NSB_LAUNCH_CHECK(ctx, "k_block_scalar");
+    return 0;
+}
+
 int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st) {
-    NSB_REQUIRE(ctx, A && nsb_spmv32_available(A), "matrix has no single-precision copy / row tiles");
+    NSB_REQUIRE(ctx, A && nsb_spmv32_available(A), "matrix has no single-precision copy (diag32, or vals32 + row tiles)");
     NSB_REQUIRE(ctx, x && y && x != y, "bad vectors (x must not alias y)");
     const int pb = NSB_PAD32(A->bs);
     int32_t nown = INT32_MAX;
@@ -81,6 +181,7 @@ int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* 
         xg = reinterpret_cast<const float*>(H.ghostbuf) - (int64_t)nown * pb;
     }
     NSB_TIMED(ctx, NSB_T_SPMV_BSR32, st);
+    if (A->diag32) return A->bs == 3 ? launch_spmv_kron32<3>(ctx, A, x, nown, xg, y, st) : launch_spmv_kron32<2>(ctx, A, x, nown, xg, y, st);
     NSB_COUNT(ctx, 1);
     if (A->bs == 3) return launch_spmv_bsr_tma<3, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);
     return launch_spmv_bsr_tma<2, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);

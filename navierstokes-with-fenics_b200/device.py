@@ -301,17 +301,19 @@ class Device:
             self.patterns[name] = pat
         return self.patterns[name]
 
-    def matrix(self, pattern, vals, kind, bs, bc_mask=None, vals32=None):
+    def matrix(self, pattern, vals, kind, bs, bc_mask=None, vals32=None, diag32=None):
         """nsb_matrix descriptor (keeps the tensors alive through attributes).  ``vals32``: float32
-        copy of the BSR values for the SpMVs inside the Chebyshev preconditioner (``to_f32``)."""
+        copy of the BSR values for the SpMVs inside the Chebyshev preconditioner (``to_f32``);
+        ``diag32``: one float per block, its block-scalar approximation (``block_scalar_f32``)."""
         pat = self.patterns[pattern]
         tiles, ntiles = pat.tiles(L.TILE_ENTRIES[(kind, bs)]) if (kind, bs) in L.TILE_ENTRIES else (None, 0)
         m = L.Matrix(kind, bs, pat.nrows, pat.nnz, pat.rowptr.data_ptr(), pat.col.data_ptr(), vals.data_ptr(),
                      bc_mask.data_ptr() if bc_mask is not None else None,
                      tiles.data_ptr() if tiles is not None else None, ntiles,
                      getattr(pat, "halo", 0) if self.partition is not None else 0,
-                     vals32.data_ptr() if vals32 is not None else None)
-        m._keep = (pat, vals, bc_mask, tiles, vals32)
+                     vals32.data_ptr() if vals32 is not None else None,
+                     diag32.data_ptr() if diag32 is not None else None)
+        m._keep = (pat, vals, bc_mask, tiles, vals32, diag32)
         return m
 
     # ---- coefficients -----------------------------------------------------------------------
@@ -447,6 +449,10 @@ class Device:
         sec, n = C.c_double(), C.c_int64()
         self.check(self.lib.nsb_direct_seconds(self.ctx, C.byref(sec), C.byref(n), 1 if reset else 0))
         return sec.value, n.value
+
+    def block_scalar_f32(self, vals, bs, out):
+        """out[k] = float(mean of the diagonal of the bs x bs block k of ``vals``)"""
+        self.check(self.lib.nsb_bsr_block_scalar_f32(self.ctx, out.numel(), bs, _ptr(vals), _ptr(out), self.stream))
 
     def to_f32(self, x, y):
         self.check(self.lib.nsb_vec_to_f32(self.ctx, x.numel(), _ptr(x), _ptr(y), self.stream))

@@ -18,7 +18,7 @@ class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
                  momentum_preconditioner="chebyshev", chebyshev_degree=8, chebyshev_ratio=30.0, partition=None,
-                 preconditioner_precision="f32", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
+                 preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
@@ -56,14 +56,19 @@ class IPCSSolver(SolverBase):
         self._A_mom = dev.empty(p22.nnz * d * d)
         # single-precision copy of the Jacobian values, read only by the SpMVs INSIDE the Chebyshev
         # polynomial; GMRES itself applies the FP64 matrix and tests the FP64 residual.
-        #   "f32"        the whole polynomial in single precision (values, padded vectors, arithmetic)
-        #                inside a flexible GMRES, which keeps z_j = M^-1 v_j and so tolerates the rounding
+        #   "f32-scalar" (default) the polynomial in single precision (padded vectors, arithmetic) inside a
+        #                flexible GMRES, which keeps z_j = M^-1 v_j and so tolerates the rounding; its matrix
+        #                is the block-scalar part S (x) I of J (mean block diagonals, 8 B per block entry)
+        #   "f32"        the same with the full d x d blocks in single precision (40 B per block entry)
         #   "f32-matrix" single-precision values only, FP64 vectors: still a fixed linear preconditioner
         #   "f64"        everything FP64
-        assert preconditioner_precision in ("f32", "f32-matrix", "f64")
-        self._pc_lowp = momentum_preconditioner == "chebyshev" and preconditioner_precision == "f32"
+        assert preconditioner_precision in ("f32-scalar", "f32", "f32-matrix", "f64")
+        cheb = momentum_preconditioner == "chebyshev"
+        self._pc_lowp = cheb and preconditioner_precision in ("f32", "f32-scalar")
         self._A_mom32 = dev.empty(p22.nnz * d * d, dtype=torch.float32) \
-            if (momentum_preconditioner == "chebyshev" and preconditioner_precision != "f64") else None
+            if (cheb and preconditioner_precision in ("f32", "f32-matrix")) else None
+        self._S_mom32 = dev.empty(p22.nnz, dtype=torch.float32) \
+            if (cheb and preconditioner_precision == "f32-scalar") else None
         self._A_mass = dev.empty(p22.nnz)
         self._A_lap = dev.empty(p11.nnz)
         nVo, nQo = self._nV_own, self._nQ_own
@@ -149,7 +154,7 @@ class IPCSSolver(SolverBase):
         dev.assemble_correction(L.MAT, A=self._A_mass)
         self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pressure_dirichlet else None)
         self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
-        self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None, vals32=self._A_mom32)
+        self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None, vals32=self._A_mom32, diag32=self._S_mom32)
         dev.inv_diagonal(self._lap, self._dinvQ)
         if self._p_pc[0] == "chebyshev":
             lmax = 1.1 * dev.lambda_max(self._lap, self._dinvQ, iters=30, work=self._work)
@@ -227,6 +232,8 @@ class IPCSSolver(SolverBase):
             dev.inv_diagonal(self._jac, self._dinvV)
             if self._A_mom32 is not None:
                 dev.to_f32(self._A_mom, self._A_mom32)
+            if self._S_mom32 is not None:
+                dev.block_scalar_f32(self._A_mom, d, self._S_mom32)
             if self._mom_pc == "chebyshev":
                 if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step
                     self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=8, work=self._work)

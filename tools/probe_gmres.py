@@ -45,6 +45,8 @@ ref = None
 lowp = solver._pc_lowp
 if solver._A_mom32 is not None:
     dev.to_f32(solver._A_mom, solver._A_mom32)
+if solver._S_mom32 is not None:
+    dev.block_scalar_f32(solver._A_mom, 3, solver._S_mom32)
 print("single-precision polynomial / flexible GMRES:", lowp)
 for kind, deg, ratio in [("jacobi", 1, 0)] + [("cheb", d, r) for d in (3, 4, 5, 6, 8, 10) for r in (15.0, 30.0, 60.0)]:
     pc = dev.precond(solver._dinvV) if kind == "jacobi" else \
