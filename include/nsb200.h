@@ -232,9 +232,11 @@ int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const dou
               double rtol, double atol, int32_t maxit, int32_t restart, double* work,
               int32_t* iters_out, double* resid_out, void* stream);
 /* largest eigenvalue (modulus) of D^-1 A by `iters` power iterations: upper end of the Chebyshev
- * interval.  work: 2 * nrows*bs doubles. */
-int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, double* work,
-                   double* lambda_out_host, void* stream);
+ * interval.  work: 2 * nrows*bs doubles.  warm_start = 1: work[0 .. nrows*bs) still holds the iterate
+ * the previous call left there (the Jacobian of the previous time step): continue from it, two or
+ * three iterations then track the slowly moving spectrum. */
+int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, int32_t warm_start,
+                   double* work, double* lambda_out_host, void* stream);
 
 /* Function.assign / Vector ops (source/ns_ipcs_solver.py:41-43, source/ns_solver_base.py:1015-1016) */
 int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y, void* stream);

@@ -70,7 +70,7 @@ PROTOTYPES = {
     "nsb_inv_diagonal": (C.c_int, [vp, C.POINTER(Matrix), vp, vp]),
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
-    "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, vp, c_f64p, vp]),
+    "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
     "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                          vp, c_i32p, c_f64p, vp]),
     "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,

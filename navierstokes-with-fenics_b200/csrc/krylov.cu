@@ -323,7 +323,7 @@ k_pi_step(int64_t n, const double* __restrict__ dinv, const double* __restrict__
 }
 
 extern "C" int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters,
-                              double* work, double* lambda_out, void* stream) {
+                              int32_t warm_start, double* work, double* lambda_out, void* stream) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, A && inv_diag && work && lambda_out && iters >= 1, "bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
@@ -331,8 +331,10 @@ extern "C" int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* i
     const int G = krylov_grid(ctx, n);
     double *v = work, *q = work + n;
     double* ds = ctx->d_scalars;
-    k_pi_init<<<G, 256, 0, st>>>(n, v);
-    NSB_LAUNCH_CHECK(ctx, "k_pi_init");
+    if (!warm_start) {        // warm start: work[0..n) still holds the iterate a previous call left there
+        k_pi_init<<<G, 256, 0, st>>>(n, v);
+        NSB_LAUNCH_CHECK(ctx, "k_pi_init");
+    }
     // slots S_H1 / S_H1+1 alternate: ||v_k||^2 with v_k = D^-1 A v_{k-1} / ||v_{k-1}||
     for (int k = 0; k <= iters; ++k) {
         if (nsb_launch_spmv(ctx, A, v, q, nullptr, nullptr, st)) return -1;

@@ -29,6 +29,11 @@ static int launch_spmv_bs(nsb_ctx* ctx, const nsb_matrix* A, const double* x, in
                           double* y, const double* dot_with, double* scalar_out, cudaStream_t st) {
     double per_row = A->nrows > 0 ? (double)A->nnz / (double)A->nrows : 0.0;
     if (KIND == NSB_BSR) per_row *= BS * BS;
+    if (KIND == NSB_CSR) {      // csr_row keeps 4 entries per lane in flight: fewer lanes per row
+        if (per_row <= 40.0) return launch_spmv_t<KIND, BS, 4>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+        if (per_row <= 80.0) return launch_spmv_t<KIND, BS, 8>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+        return launch_spmv_t<KIND, BS, 16>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
+    }
     if (per_row <= 10.0) return launch_spmv_t<KIND, BS, 4>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
     if (per_row <= 24.0) return launch_spmv_t<KIND, BS, 8>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);
     if (per_row <= 64.0) return launch_spmv_t<KIND, BS, 16>(ctx, A, x, nown, xg, y, dot_with, scalar_out, st);

@@ -18,12 +18,30 @@ __device__ __forceinline__ void csr_row(int32_t row, int lane, const int32_t* __
 #pragma unroll
     for (int b = 0; b < BS; ++b) acc[b] = 0.0;
     const int32_t end = rowptr[row + 1];
-    for (int32_t s = rowptr[row] + lane; s < end; s += LANES) {
-        const double v = vals[s];
-        const int32_t cn = col[s];
-        const double* xs = (cn < nown ? x : xg) + (int64_t)cn * BS;
+    // rows are short (15 .. 30 entries): offsets -> columns -> gather is a chain of dependent loads, so a
+    // lane keeps U independent entries in flight (the kernels are latency bound, not bandwidth bound)
+    constexpr int U = 4;
+    for (int32_t s = rowptr[row] + lane; s < end; s += LANES * U) {
+        double v[U];
+        int32_t cn[U];
 #pragma unroll
-        for (int b = 0; b < BS; ++b) acc[b] += v * xs[b];
+        for (int u = 0; u < U; ++u) {
+            const int32_t ss = s + u * LANES;
+            const bool ok = ss < end;
+            v[u] = ok ? vals[ss] : 0.0;
+            cn[u] = ok ? col[ss] : row;
+        }
+        double xv[U][BS];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const double* xs = (cn[u] < nown ? x : xg) + (int64_t)cn[u] * BS;
+#pragma unroll
+            for (int b = 0; b < BS; ++b) xv[u][b] = xs[b];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int b = 0; b < BS; ++b) acc[b] += v[u] * xv[u][b];
     }
 }
 

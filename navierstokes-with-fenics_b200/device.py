@@ -378,13 +378,15 @@ class Device:
     def _pc(self, M):
         return M if isinstance(M, L.Precond) else self.precond(M)
 
-    def lambda_max(self, A, inv_diag, iters=12, work=None):
+    def lambda_max(self, A, inv_diag, iters=12, work=None, warm_start=False):
+        """``warm_start``: ``work`` (kept by the caller between calls) still holds the previous iterate"""
         n = A.nrows * A.bs
         if work is None or work.numel() < 2 * n:
+            assert not warm_start, "a warm start needs the work vector of the previous call"
             work = self.empty(2 * n)
         out = C.c_double()
-        self.check(self.lib.nsb_lambda_max(self.ctx, C.byref(A), _ptr(inv_diag), iters, _ptr(work), C.byref(out),
-                                           self.stream))
+        self.check(self.lib.nsb_lambda_max(self.ctx, C.byref(A), _ptr(inv_diag), iters, 1 if warm_start else 0,
+                                           _ptr(work), C.byref(out), self.stream))
         return out.value
 
     def cg(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=10000, nullspace=False, work=None):

@@ -77,6 +77,7 @@ class IPCSSolver(SolverBase):
         self._bQ, self._dinvQ = dev.empty(nQo), dev.empty(nQo)
         self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nVo, gmres_restart, 1 if self._pc_lowp else 0),
                                    dev.lib.nsb_cg_workspace_doubles(nVo)))
+        self._pi_work = None
         self._have_constant = False
         self._bc_ready = False
         self.newton_iterations, self.krylov_iterations = [], []
@@ -235,8 +236,14 @@ class IPCSSolver(SolverBase):
             if self._S_mom32 is not None:
                 dev.block_scalar_f32(self._A_mom, d, self._S_mom32)
             if self._mom_pc == "chebyshev":
-                if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step
-                    self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=8, work=self._work)
+                if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step,
+                    # and little from step to step: the power iteration continues from the previous
+                    # step's iterate (2 iterations) instead of starting over (8)
+                    warm = self._pi_work is not None
+                    if not warm:
+                        self._pi_work = dev.empty(2 * self._nV_own)
+                    self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=2 if warm else 8,
+                                                      work=self._pi_work, warm_start=warm)
                 pc = dev.precond(self._dinvV, L.PC_CHEBYSHEV, self._cheb_degree, self._lmax / self._cheb_ratio,
                                  self._lmax, lowp=self._pc_lowp)
             else:
