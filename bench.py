@@ -174,7 +174,8 @@ def algorithmic_bytes(solver):
         "spmv_bsr": 8 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,
         # single-precision SpMV of the preconditioner on the block-scalar part of J: one float + one column
         # index per block entry, x and y as one float4 per node, row offsets
-        "spmv_bsr_f32": 4 * nnz22 + 4 * nnz22 + 2 * 16 * nnodes + 4 * nnodes,
+        # + the Chebyshev step fused into its epilogue: r and z read + written, d_new written (float4 each), D^-1
+        "spmv_bsr_f32": 4 * nnz22 + 4 * nnz22 + 4 * nnodes + (16 + 32 + 32 + 16 + 24) * nnodes,
         "spmv_csr": None,                                       # two different matrices share the class
         "asm_jacobian": 8 * 9 * nnz22 + geo + 8 * nV,
         "asm_residual": 8 * nV + geo + 8 * (3 * nV + nQ),

@@ -227,9 +227,11 @@ int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double
            double rtol, double atol, int32_t maxit, int32_t nullspace, double* work,
            int32_t* iters_out, double* resid_out, void* stream);
 /* right-preconditioned restarted GMRES (CGS-2 Arnoldi) for the velocity / mixed Newton systems
- * (source/ns_ipcs_solver.py:138-147, source/ns_bdf_solver.py:91-100) */
+ * (source/ns_ipcs_solver.py:138-147, source/ns_bdf_solver.py:91-100); flexible (keeps M^-1 v_j) when
+ * M->lowp.  x0_is_zero = 1: the caller guarantees x = 0 on entry (Newton updates), which saves the
+ * first residual SpMV (r = b).  work: nsb_gmres_workspace_doubles(n, restart, M->lowp). */
 int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
-              double rtol, double atol, int32_t maxit, int32_t restart, double* work,
+              double rtol, double atol, int32_t maxit, int32_t restart, int32_t x0_is_zero, double* work,
               int32_t* iters_out, double* resid_out, void* stream);
 /* largest eigenvalue (modulus) of D^-1 A by `iters` power iterations: upper end of the Chebyshev
  * interval.  work: 2 * nrows*bs doubles.  warm_start = 1: work[0 .. nrows*bs) still holds the iterate

@@ -74,7 +74,7 @@ PROTOTYPES = {
     "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                          vp, c_i32p, c_f64p, vp]),
     "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
-                            vp, c_i32p, c_f64p, vp]),
+                            C.c_int32, vp, c_i32p, c_f64p, vp]),
     "nsb_vec_copy": (C.c_int, [vp, C.c_int64, vp, vp, vp]),
     "nsb_vec_axpy": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp, vp]),
     "nsb_vec_scale": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp]),

@@ -96,6 +96,16 @@ __device__ __forceinline__ double nsb_wait_line(const uint4* p, unsigned int fla
 }
 #endif
 
+// Chebyshev step fused into the epilogue of the single-precision block-scalar SpMV (linalg.cu
+// k_spmv_kron32, krylov.cu apply_cheb32): with q = S d_old the row computes r -= D^-1 q,
+// d_new = a d_old + b r, z += d_new (zout != null: last step, only zout = z + d_new is written, in FP64)
+struct nsb_cheb32_epi {
+    const double* dinv;
+    float *r, *dnew, *z;
+    double* zout;
+    float a, b;
+};
+
 struct nsb_ctx {
     int device = 0;
     // multi-GPU (comm.cu): one rank per GPU, NCCL communicator created by nsb_comm_init

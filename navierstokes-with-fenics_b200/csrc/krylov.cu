@@ -216,7 +216,8 @@ static int fetch(nsb_ctx* ctx, int slot, int count, cudaStream_t st) {
 // preconditioner application  z = M^-1 v   (scratch: 3 n doubles for Chebyshev)
 // ---------------------------------------------------------------------------------------------
 bool nsb_spmv32_available(const nsb_matrix* A);
-int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st);
+int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st,
+                      const nsb_cheb32_epi* epi = nullptr);
 
 // the single-precision Chebyshev polynomial is not exactly linear in v (FP32 rounding): only the flexible
 // GMRES may use it
@@ -240,9 +241,20 @@ static int apply_cheb32(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M,
         k_cheb32_first<BS><<<G, 256, 0, st>>>(nn, M->inv_diag, v, (float)(1.0 / theta), r, d, z, M->degree == 1 ? zout : nullptr);
         NSB_LAUNCH_CHECK(ctx, "k_cheb32_first");
     }
+    const bool fused = A->diag32 != nullptr;      // block-scalar matrix: the step runs in the SpMV's epilogue
     for (int k = 1; k < M->degree; ++k) {
-        if (nsb_launch_spmv32(ctx, A, d, q, st)) return -1;
         const double rho = 1.0 / (2.0 * sigma1 - rho_old);
+        if (fused) {                              // d and q alternate as old / new direction
+            nsb_cheb32_epi E;
+            E.dinv = M->inv_diag; E.r = r; E.dnew = q; E.z = z;
+            E.zout = k == M->degree - 1 ? zout : nullptr;
+            E.a = (float)(rho * rho_old); E.b = (float)(2.0 * rho / delta);
+            if (nsb_launch_spmv32(ctx, A, d, nullptr, st, &E)) return -1;
+            float* tmp = d; d = q; q = tmp;
+            rho_old = rho;
+            continue;
+        }
+        if (nsb_launch_spmv32(ctx, A, d, q, st)) return -1;
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_cheb32_step<BS><<<G, 256, 0, st>>>(nn, M->inv_diag, q, (float)(rho * rho_old), (float)(2.0 * rho / delta), r, d, z,
                                             k == M->degree - 1 ? zout : nullptr);
@@ -593,7 +605,7 @@ extern "C" int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart, int32
 }
 
 extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
-                         double rtol, double atol, int32_t maxit, int32_t restart, double* work,
+                         double rtol, double atol, int32_t maxit, int32_t restart, int32_t x0_is_zero, double* work,
                          int32_t* iters_out, double* resid_out, void* stream) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, A && b && x && work, "null argument");
@@ -627,22 +639,29 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
     const double tol = fmax(rtol * bnorm, atol);
     int it = 0;
     double rnorm = 0.0;
+    bool first_cycle = true;
     while (true) {
-        // true residual r = b - A x -> w
-        if (nsb_launch_spmv(ctx, A, x, t, nullptr, nullptr, st)) return -1;
-        {
-            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-            k_residual<<<G, 256, 0, st>>>(n, b, t, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+        const bool r_is_b = first_cycle && x0_is_zero;       // x = 0: r = b and ||r|| = ||b||, no SpMV needed
+        first_cycle = false;
+        if (r_is_b) {
+            rnorm = bnorm;
+        } else {
+            // true residual r = b - A x -> w
+            if (nsb_launch_spmv(ctx, A, x, t, nullptr, nullptr, st)) return -1;
+            {
+                NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+                k_residual<<<G, 256, 0, st>>>(n, b, t, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+            }
+            NSB_LAUNCH_CHECK(ctx, "k_residual");
+            if (nsb_allreduce_sum(ctx, ds + S_NRM, 1, st)) return -1;
+            if (fetch(ctx, S_NRM, 1, st)) return -1;
+            rnorm = sqrt(hs[S_NRM]);
         }
-        NSB_LAUNCH_CHECK(ctx, "k_residual");
-        if (nsb_allreduce_sum(ctx, ds + S_NRM, 1, st)) return -1;
-        if (fetch(ctx, S_NRM, 1, st)) return -1;
-        rnorm = sqrt(hs[S_NRM]);
         if (!(rnorm == rnorm)) return nsb_fail(ctx, "GMRES breakdown: residual is NaN%s%s");
         if (rnorm <= tol || it >= maxit) break;
         {
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-            k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_NRM, V);
+            k_normalize<<<G, 256, 0, st>>>(n, r_is_b ? b : w, ds + (r_is_b ? S_OUT : S_NRM), V);
         }
         NSB_LAUNCH_CHECK(ctx, "k_normalize");
         g.assign(m + 1, 0.0);

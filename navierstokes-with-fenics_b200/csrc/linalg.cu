@@ -79,11 +79,11 @@ bool nsb_spmv32_available(const nsb_matrix* A) {
 // lower-order Newton coupling, so as a PRECONDITIONER the scalar part does as well as the full blocks
 // (same GMRES iteration counts, tools/probe_scalar_pc.py).  LANES lanes per row, coalesced value / column
 // streams, one 16-byte gather per entry.
-template <int BS, int LANES, int U>
+template <int BS, int LANES, int U, bool CHEB>
 __global__ void __launch_bounds__(256)
 k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
               const float* __restrict__ s, const float* __restrict__ x, int32_t nown, const float* __restrict__ xg,
-              float* __restrict__ y) {
+              float* __restrict__ y, nsb_cheb32_epi E) {
     constexpr int PB = NSB_PAD32(BS);
     const int lane = threadIdx.x % LANES;
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
@@ -125,21 +125,58 @@ k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* 
 #pragma unroll
         for (int o = LANES / 2; o > 0; o >>= 1) acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], o, LANES);
     if (lane == 0) {
-        if constexpr (BS == 3) reinterpret_cast<float4*>(y)[row] = make_float4(acc[0], acc[1], acc[2], 0.0f);
-        else reinterpret_cast<float2*>(y)[row] = make_float2(acc[0], acc[1]);
+        if constexpr (CHEB) {
+            float ri[BS], dold[BS], zi[BS];
+            if constexpr (BS == 3) {
+                const float4 a4 = reinterpret_cast<const float4*>(E.r)[row], b4 = reinterpret_cast<const float4*>(x)[row],
+                             c4 = reinterpret_cast<const float4*>(E.z)[row];
+                ri[0] = a4.x; ri[1] = a4.y; ri[2] = a4.z; dold[0] = b4.x; dold[1] = b4.y; dold[2] = b4.z;
+                zi[0] = c4.x; zi[1] = c4.y; zi[2] = c4.z;
+            } else {
+                const float2 a2 = reinterpret_cast<const float2*>(E.r)[row], b2 = reinterpret_cast<const float2*>(x)[row],
+                             c2 = reinterpret_cast<const float2*>(E.z)[row];
+                ri[0] = a2.x; ri[1] = a2.y; dold[0] = b2.x; dold[1] = b2.y; zi[0] = c2.x; zi[1] = c2.y;
+            }
+#pragma unroll
+            for (int c = 0; c < BS; ++c) {
+                ri[c] -= (float)E.dinv[row * BS + c] * acc[c];
+                acc[c] = E.a * dold[c] + E.b * ri[c];          // d_new
+                zi[c] += acc[c];
+            }
+            if (E.zout) {
+#pragma unroll
+                for (int c = 0; c < BS; ++c) E.zout[row * BS + c] = (double)zi[c];
+            } else if constexpr (BS == 3) {
+                reinterpret_cast<float4*>(E.r)[row] = make_float4(ri[0], ri[1], ri[2], 0.0f);
+                reinterpret_cast<float4*>(E.dnew)[row] = make_float4(acc[0], acc[1], acc[2], 0.0f);
+                reinterpret_cast<float4*>(E.z)[row] = make_float4(zi[0], zi[1], zi[2], 0.0f);
+            } else {
+                reinterpret_cast<float2*>(E.r)[row] = make_float2(ri[0], ri[1]);
+                reinterpret_cast<float2*>(E.dnew)[row] = make_float2(acc[0], acc[1]);
+                reinterpret_cast<float2*>(E.z)[row] = make_float2(zi[0], zi[1]);
+            }
+        } else {
+            if constexpr (BS == 3) reinterpret_cast<float4*>(y)[row] = make_float4(acc[0], acc[1], acc[2], 0.0f);
+            else reinterpret_cast<float2*>(y)[row] = make_float2(acc[0], acc[1]);
+        }
     }
 }
 
 template <int BS>
 static int launch_spmv_kron32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, int32_t nown, const float* xg, float* y,
-                              cudaStream_t st) {
+                              const nsb_cheb32_epi* epi, cudaStream_t st) {
     const double per_row = (double)A->nnz / (double)A->nrows;
     static int forced = -1;                        // development override: NSB_KRON_LANES = 4 | 8 | 16 | 32
     if (forced < 0) { const char* e = getenv("NSB_KRON_LANES"); forced = e ? atoi(e) : 0; }
     const int code = forced ? forced : (per_row <= 40.0 ? 4 : 8);
     const int lanes = code > 32 ? code / 10 : code;          // 48 = 4 lanes x 8 gathers, 28, 88 likewise
     const int blocks = nsb_blocks((int64_t)A->nrows * lanes, 256);
-#define NSB_KRON(LANES, U) k_spmv_kron32<BS, LANES, U><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y)
+    const nsb_cheb32_epi E = epi ? *epi : nsb_cheb32_epi{};
+#define NSB_KRON(LANES, U)                                                                                                  \
+    do {                                                                                                                    \
+        if (epi) k_spmv_kron32<BS, LANES, U, true><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E);  \
+        else k_spmv_kron32<BS, LANES, U, false><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E); \
+    } while (0)
     if (code == 2) NSB_KRON(2, 4);
     else if (code == 28) NSB_KRON(2, 8);
     else if (code == 4) NSB_KRON(4, 4);
@@ -171,9 +208,12 @@ extern "C" int nsb_bsr_block_scalar_f32(nsb_ctx* ctx, int64_t nnz, int32_t bs, c
     return 0;
 }
 
-int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st) {
+int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st,
+                      const nsb_cheb32_epi* epi) {
     NSB_REQUIRE(ctx, A && nsb_spmv32_available(A), "matrix has no single-precision copy (diag32, or vals32 + row tiles)");
-    NSB_REQUIRE(ctx, x && y && x != y, "bad vectors (x must not alias y)");
+    NSB_REQUIRE(ctx, x && (epi || y) && x != y, "bad vectors (x must not alias y)");
+    NSB_REQUIRE(ctx, !epi || (A->diag32 && epi->dinv && epi->r && epi->z && (epi->zout || epi->dnew) && epi->dnew != x),
+                "fused Chebyshev step needs the block-scalar matrix and a second direction buffer");
     const int pb = NSB_PAD32(A->bs);
     int32_t nown = INT32_MAX;
     const float* xg = x;
@@ -186,7 +226,7 @@ int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* 
         xg = reinterpret_cast<const float*>(H.ghostbuf) - (int64_t)nown * pb;
     }
     NSB_TIMED(ctx, NSB_T_SPMV_BSR32, st);
-    if (A->diag32) return A->bs == 3 ? launch_spmv_kron32<3>(ctx, A, x, nown, xg, y, st) : launch_spmv_kron32<2>(ctx, A, x, nown, xg, y, st);
+    if (A->diag32) return A->bs == 3 ? launch_spmv_kron32<3>(ctx, A, x, nown, xg, y, epi, st) : launch_spmv_kron32<2>(ctx, A, x, nown, xg, y, epi, st);
     NSB_COUNT(ctx, 1);
     if (A->bs == 3) return launch_spmv_bsr_tma<3, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);
     return launch_spmv_bsr_tma<2, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);

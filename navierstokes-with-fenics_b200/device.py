@@ -401,7 +401,7 @@ class Device:
         self.check(st)
         return it.value, res.value
 
-    def gmres(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None):
+    def gmres(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None, x0_is_zero=False):
         n = A.nrows * A.bs
         M = self._pc(M)
         need = self.lib.nsb_gmres_workspace_doubles(n, restart, M.lowp)
@@ -409,7 +409,7 @@ class Device:
             work = self.empty(need)
         it, res = C.c_int32(), C.c_double()
         st = self.lib.nsb_gmres(self.ctx, C.byref(A), C.byref(M), _ptr(b), _ptr(x), rtol, atol, maxit, restart,
-                                _ptr(work), C.byref(it), C.byref(res), self.stream)
+                                1 if x0_is_zero else 0, _ptr(work), C.byref(it), C.byref(res), self.stream)
         self.check(st)
         return it.value, res.value
 

@@ -257,7 +257,7 @@ class IPCSSolver(SolverBase):
                 # strongly non-normal Jacobians (coarse meshes, sharp inflow transients) stall it.  Give it
                 # three restart cycles, then finish from the current iterate with plain Jacobi.
                 try:
-                    n_it, _ = dev.gmres(self._jac, pc, self._bV, self._dxV, maxit=3 * self._restart, **kw)
+                    n_it, _ = dev.gmres(self._jac, pc, self._bV, self._dxV, maxit=3 * self._restart, x0_is_zero=True, **kw)
                 except RuntimeError as err:
                     if "did not converge" not in str(err):
                         raise
@@ -265,7 +265,7 @@ class IPCSSolver(SolverBase):
                     n_j, _ = dev.gmres(self._jac, dev.precond(self._dinvV), self._bV, self._dxV, **kw)
                     n_it = 3 * self._restart + n_j
             else:
-                n_it, _ = dev.gmres(self._jac, pc, self._bV, self._dxV, **kw)
+                n_it, _ = dev.gmres(self._jac, pc, self._bV, self._dxV, x0_is_zero=True, **kw)
             kry.append(n_it)
             dev.axpy(-1.0, self._dxV, ustar)
             dev.halo_exchange(L.HALO_NODES, d, ustar)
