@@ -250,11 +250,14 @@ def run_nsb200(args):
     sampler.start()
     l0 = dev.launch_count()
     dev.timer_enable(True)
+    state = solver.get_state()              # both legs advance the SAME K time steps
     ms, _, _ = timed(args.steps, False)
     classes = dev.timer_report()
     dev.timer_enable(False)
     launches = dev.launch_count() - l0
     clocks = sampler.result()
+    solver.set_state(state)
+    del state
     ms_e2e, h2d, d2h = timed(args.steps, True)
     if world > 1:
         # collective tear-down BEFORE rank 0 goes off to format the result: every rank leaves together

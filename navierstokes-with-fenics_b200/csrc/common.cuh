@@ -106,8 +106,16 @@ struct nsb_cheb32_epi {
     float a, b;
 };
 
+// the same step in FP64 in the epilogue of the CSR SpMV kernels (pressure Chebyshev-CG): z += d_new in place
+struct nsb_cheb64_epi {
+    const double* dinv;
+    double *r, *dnew, *z;
+    double a, b;
+};
+
 struct nsb_ctx {
     int device = 0;
+    const nsb_cheb64_epi* spmv_epi = nullptr;   // set by apply_pc for the very next CSR SpMV, consumed by its launcher
     // multi-GPU (comm.cu): one rank per GPU, NCCL communicator created by nsb_comm_init
     int rank = 0, nranks = 1;
     void* nccl_comm = nullptr;

@@ -289,9 +289,20 @@ static int apply_pc(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, con
         k_cheb_first<<<G, 256, 0, st>>>(n, M->inv_diag, v, 1.0 / theta, r, d, z);
         NSB_LAUNCH_CHECK(ctx, "k_cheb_first");
     }
+    const bool fused = A->kind == NSB_CSR;        // CSR kernels carry the step in their epilogue (d, q alternate)
     for (int k = 1; k < M->degree; ++k) {
-        if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st, /*lowp=*/true)) return -1;
         const double rho = 1.0 / (2.0 * sigma1 - rho_old);
+        if (fused) {
+            nsb_cheb64_epi E;
+            E.dinv = M->inv_diag; E.r = r; E.dnew = q; E.z = z;
+            E.a = rho * rho_old; E.b = 2.0 * rho / delta;
+            ctx->spmv_epi = &E;
+            if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st)) return -1;
+            double* tmp = d; d = q; q = tmp;
+            rho_old = rho;
+            continue;
+        }
+        if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st, /*lowp=*/true)) return -1;
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_cheb_step<<<G, 256, 0, st>>>(n, M->inv_diag, q, rho * rho_old, 2.0 * rho / delta, r, d, z);
         NSB_LAUNCH_CHECK(ctx, "k_cheb_step");

@@ -16,6 +16,11 @@ static int launch_spmv_t(nsb_ctx* ctx, const nsb_matrix* A, const double* x, int
         k_spmv<KIND, BS, LANES, true><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
             A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, nown, xg, y, dot_with, ctx->d_partials,
             ctx->d_counter, scalar_out);
+    } else if (KIND == NSB_CSR && ctx->spmv_epi) {
+        const nsb_cheb64_epi E = *ctx->spmv_epi;
+        ctx->spmv_epi = nullptr;
+        k_spmv<KIND, BS, LANES, false, true><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
+            A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, nown, xg, y, nullptr, nullptr, nullptr, nullptr, E);
     } else {
         k_spmv<KIND, BS, LANES, false><<<(int)blocks, NSB_SPMV_THREADS, 0, st>>>(
             A->nrows, A->rowptr, A->col, A->vals, A->bc_mask, x, nown, xg, y, nullptr, nullptr, nullptr, nullptr);
@@ -59,6 +64,10 @@ int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* 
         xg = H.ghostbuf - (int64_t)nown * A->bs;
     }
     if (spmv_dispatch(ctx, A, x, nown, xg, y, dot_with, scalar_out, st, lowp)) return -1;
+    if (ctx->spmv_epi) {
+        ctx->spmv_epi = nullptr;
+        return nsb_fail(ctx, "internal: fused Chebyshev epilogue requested for a SpMV kernel that has none%s%s");
+    }
     if (dot_with && nsb_allreduce_sum(ctx, scalar_out, 1, st)) return -1;
     return 0;
 }

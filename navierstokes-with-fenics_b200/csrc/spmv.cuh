@@ -67,13 +67,15 @@ __device__ __forceinline__ void bsr_row(int32_t row, int lane, const int32_t* __
 }
 
 // y = A x ; if DOT: scalars_out[0] = sum_i d[i] * y[i]  (d = dot_with)
-template <int KIND, int BS, int LANES, bool DOT>
+// CHEB: instead of storing y = A x the row applies the Chebyshev step of krylov.cu to it (x = d_old):
+// r -= D^-1 y ; d_new = a d_old + b r ; z += d_new
+template <int KIND, int BS, int LANES, bool DOT, bool CHEB = false>
 __global__ void __launch_bounds__(NSB_SPMV_THREADS)
 k_spmv(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
        const double* __restrict__ vals, const uint8_t* __restrict__ mask, const double* __restrict__ x,
        int32_t nown, const double* __restrict__ xg,
        double* __restrict__ y, const double* __restrict__ dot_with, double* partials,
-       unsigned int* counter, double* scalar_out) {
+       unsigned int* counter, double* scalar_out, nsb_cheb64_epi E = nsb_cheb64_epi{}) {
     constexpr int ROWS_PER_BLOCK = NSB_SPMV_THREADS / LANES;
     const int lane = threadIdx.x % LANES;
     double dsum[1] = {0.0};
@@ -97,7 +99,13 @@ k_spmv(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restr
                 const int64_t d = row * BS + b;
                 double v = acc[b];
                 if (mask != nullptr && mask[d]) v = x[d];
-                y[d] = v;
+                if (CHEB) {
+                    const double ri = E.r[d] - E.dinv[d] * v;
+                    const double dn = E.a * x[d] + E.b * ri;
+                    E.r[d] = ri; E.dnew[d] = dn; E.z[d] += dn;
+                } else {
+                    y[d] = v;
+                }
                 if (DOT) dsum[0] += dot_with[d] * v;
             }
         }

@@ -136,6 +136,24 @@ class IPCSSolver(SolverBase):
             nbytes += self._pbc_host.numel() * 8
         return nbytes
 
+    # ---- checkpoint / resume of the time loop (source/ns_problem.py:601-653 writes the solution and the
+    # time-stepping state; here both stay on the device) -------------------------------------------
+    def get_state(self):
+        """device copies of the BDF history, pressures and the time-stepping object's state"""
+        import copy
+        return dict(velocities=[v.clone() for v in self._velocities], ustar=self._intermediate_velocity.clone(),
+                    pressure=self._pressure.clone(), old_pressure=self._old_pressure.clone(),
+                    time_stepping=copy.deepcopy(self._time_stepping.__dict__))
+
+    def set_state(self, state):
+        import copy
+        for v, s in zip(self._velocities, state["velocities"]):
+            v.copy_(s)
+        self._intermediate_velocity.copy_(state["ustar"])
+        self._pressure.copy_(state["pressure"])
+        self._old_pressure.copy_(state["old_pressure"])
+        self._time_stepping.__dict__.update(copy.deepcopy(state["time_stepping"]))
+
     def fetch_solution(self, out=None):
         """Device -> pinned host copy of the mixed solution vector (what the reference hands to
         its XDMF writer, source/ns_problem.py:733-735).  Returns (host tensor, bytes)."""
