@@ -256,6 +256,10 @@ k_p2p_exchange(int bs, unsigned long long epoch, long long cap, p2p_args P,
             dst[e] = nsb_wait_line(src + e, flag, err, 2);
         __syncthreads();                                      // every line of this block has been read
         if (threadIdx.x == 0) st_volatile_u64(P.peer_ack[i] + P.my_slot[i] * P2P_MAXB + blockIdx.x, epoch);
+        // exchanges of this plan differ in width (3 doubles per node, 2 for a padded float4), hence in blocks
+        // per pair: the blocks this exchange does not use have nothing to consume -- acknowledge for them too
+        if (blockIdx.x == 0 && (int)threadIdx.x >= nb && threadIdx.x < P2P_MAXB)
+            st_volatile_u64(P.peer_ack[i] + P.my_slot[i] * P2P_MAXB + threadIdx.x, epoch);
     }
 }
 
