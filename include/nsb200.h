@@ -336,7 +336,9 @@ int nsb_p2p_disconnect(nsb_ctx* ctx);   /* back to NCCL send/recv (all ranks, af
 
 /* ---------------------------------------------------------------- instrumentation ------- */
 /* Per-kernel-class CUDA-event timing on the launching stream (SURVEY.md 8b nsb_timer_*).
- * enable != 0 starts recording an event pair around every launch group of every class;
+ * enable = 1 starts recording an event pair around every launch group of every class; enable =
+ * (mask << 1) with bit c of mask set times class c only (the event pairs cost about a microsecond per
+ * launch group: bench.py times only the large kernels inside its headline region); 0 stops;
  * nsb_timer_report synchronises the device, writes accumulated milliseconds and the number of
  * timed regions per class (arrays of NSB_T_NCLASS; either may be NULL) and resets both. */
 int nsb_timer_enable(nsb_ctx* ctx, int32_t enable);

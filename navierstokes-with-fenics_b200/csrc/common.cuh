@@ -159,6 +159,7 @@ struct nsb_ctx {
     // instrumentation
     int64_t launch_count = 0;         // kernels launched by this context (all classes)
     bool timing = false;
+    uint32_t timing_mask = 0xffffffffu;   // bit c: class c is timed (nsb_timer_enable)
     nsb_timer_class timers[NSB_T_NCLASS];
 };
 
@@ -175,7 +176,7 @@ int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass
 // RAII region: records a start/stop event pair on `st` around the launches of one kernel class
 struct nsb_timed_region {
     nsb_ctx* ctx; int cls; cudaStream_t st; bool on;
-    nsb_timed_region(nsb_ctx* c, int k, cudaStream_t s) : ctx(c), cls(k), st(s), on(c && c->timing) {
+    nsb_timed_region(nsb_ctx* c, int k, cudaStream_t s) : ctx(c), cls(k), st(s), on(c && c->timing && ((c->timing_mask >> k) & 1u)) {
         if (!on) return;
         nsb_timer_class& t = ctx->timers[cls];
         if (t.used + 2 > t.ev.size()) {

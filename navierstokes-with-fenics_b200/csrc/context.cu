@@ -237,6 +237,7 @@ extern "C" int nsb_timer_enable(nsb_ctx* ctx, int32_t enable) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     if (nsb_timer_flush(ctx)) return nsb_fail(ctx, "timer flush failed%s%s");
     ctx->timing = enable != 0;
+    ctx->timing_mask = enable == 1 ? 0xffffffffu : ((uint32_t)enable >> 1);   // 1: every class; else bit (c+1) selects class c
     return 0;
 }
 

@@ -496,8 +496,12 @@ class Device:
         return self.launch_count()
 
     # ---- instrumentation --------------------------------------------------------------------
-    def timer_enable(self, on=True):
-        self.check(self.lib.nsb_timer_enable(self.ctx, 1 if on else 0))
+    def timer_enable(self, on=True, classes=None):
+        """``classes``: names out of ``_lib.TIMER_CLASSES`` to time (default: all)"""
+        code = 1 if on else 0
+        if on and classes is not None:
+            code = sum(1 << L.TIMER_CLASSES.index(c) for c in classes) << 1
+        self.check(self.lib.nsb_timer_enable(self.ctx, code))
 
     def timer_report(self):
         """{class: (milliseconds, timed regions)} since the last report (synchronises)."""
