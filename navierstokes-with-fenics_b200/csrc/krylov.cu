@@ -778,6 +778,10 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
         }
         NSB_LAUNCH_CHECK(ctx, "k_add");
         NSB_CUDA(ctx, cudaStreamSynchronize(st));   // hs[S_Y..] is reused next cycle
+        // Converged by the Arnoldi residual norm |g_{j+1}|: done, as PETSc's KSPGMRES (the reference's Krylov
+        // library) does -- with CGS-2 the recurrence tracks ||b - A x|| to round-off, and in the flexible variant
+        // w = A z_j makes it exact by construction.  Only a restart recomputes the true residual.
+        if (rnorm <= tol) break;
     }
     if (iters_out) *iters_out = it;
     if (resid_out) *resid_out = rnorm;

@@ -256,11 +256,11 @@ class IPCSSolver(SolverBase):
             if self._mom_pc == "chebyshev":
                 if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step,
                     # and little from step to step: the power iteration continues from the previous
-                    # step's iterate (2 iterations) instead of starting over (8)
+                    # step's iterate (1 iteration = 2 SpMVs) instead of starting over (8)
                     warm = self._pi_work is not None
                     if not warm:
                         self._pi_work = dev.empty(2 * self._nV_own)
-                    self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=2 if warm else 8,
+                    self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=1 if warm else 8,
                                                       work=self._pi_work, warm_start=warm)
                 pc = dev.precond(self._dinvV, L.PC_CHEBYSHEV, self._cheb_degree, self._lmax / self._cheb_ratio,
                                  self._lmax, lowp=self._pc_lowp)
