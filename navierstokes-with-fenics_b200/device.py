@@ -176,8 +176,7 @@ class Device:
             for which, pl in ((L.HALO_NODES, part.nodes), (L.HALO_VERTS, part.verts)):
                 buf = (C.c_uint8 * 64)()
                 self.check(self.lib.nsb_p2p_export(self.ctx, which, buf))
-                mine[which] = dict(handle=bytes(buf), peers=[int(r) for r in pl.peers],
-                                   recv_ptr=[int(v) for v in pl.recv_ptr], n_ghost=int(pl.n_ghost))
+                mine[which] = dict(handle=bytes(buf), **pl.peer_memory_layout())
             if part.nranks <= 8:                          # all-reduce block of the Krylov scalars
                 buf = (C.c_uint8 * 64)()
                 self.check(self.lib.nsb_p2p_export(self.ctx, L.HALO_NONE, buf))
@@ -190,16 +189,9 @@ class Device:
         if ok:
             try:
                 for which, pl in ((L.HALO_NODES, part.nodes), (L.HALO_VERTS, part.verts)):
-                    handles, nghost, off, slot = b"", [], [], []
-                    for r in pl.peers:
-                        theirs = everyone[int(r)][1][which]
-                        s = theirs["peers"].index(part.rank)
-                        handles += theirs["handle"]
-                        nghost.append(theirs["n_ghost"])
-                        off.append(theirs["recv_ptr"][s])
-                        slot.append(s)
+                    ng, of, sl = pl.peer_memory_tables(part.rank, [e[1].get(which) for e in everyone])
+                    handles = b"".join(everyone[int(r)][1][which]["handle"] for r in pl.peers)
                     hb = (C.c_uint8 * max(len(handles), 1)).from_buffer_copy(handles or b"\0")
-                    ng, of, sl = (np.asarray(a, dtype=np.int32) for a in (nghost, off, slot))
                     self.check(self.lib.nsb_p2p_connect(self.ctx, which, len(pl.peers), hb, ng.ctypes.data,
                                                         of.ctypes.data, sl.ctypes.data))
                 if part.nranks <= 8:

@@ -61,6 +61,33 @@ class HaloPlan:
         return self
 
 
+    # ---- NVLink peer-memory transport (csrc/comm.cu nsb_p2p_*): what a rank publishes / derives ------------
+    def peer_memory_layout(self):
+        """what the neighbours need to know to PUSH into this rank's ring: (peers, recv_ptr, n_ghost)"""
+        return dict(peers=[int(r) for r in self.peers], recv_ptr=[int(v) for v in self.recv_ptr], n_ghost=int(self.n_ghost))
+
+    def peer_memory_tables(self, rank, layouts):
+        """Per neighbour of this rank, in plan order: (its ghost count, the offset of this rank's part inside
+        its ghost block, this rank's index in its peer list) -- the arguments of ``nsb_p2p_connect``.
+        ``layouts[r]`` is rank r's ``peer_memory_layout()``.  Checks the pairing the push kernel relies on: the
+        neighbour expects exactly as many entries from this rank as this rank sends (both ends size the
+        exchange's grid from that count)."""
+        nghost, off, slot = [], [], []
+        for i, r in enumerate(self.peers):
+            theirs = layouts[int(r)]
+            if rank not in theirs["peers"]:
+                raise ValueError("rank %d lists rank %d as a neighbour but not the other way round" % (rank, int(r)))
+            s = theirs["peers"].index(rank)
+            expects = theirs["recv_ptr"][s + 1] - theirs["recv_ptr"][s]
+            sends = int(self.send_ptr[i + 1] - self.send_ptr[i])
+            if expects != sends:
+                raise ValueError("rank %d sends %d entries to rank %d, which expects %d" % (rank, sends, int(r), expects))
+            nghost.append(theirs["n_ghost"])
+            off.append(theirs["recv_ptr"][s])
+            slot.append(s)
+        return (np.asarray(nghost, dtype=np.int32), np.asarray(off, dtype=np.int32), np.asarray(slot, dtype=np.int32))
+
+
 class Partition:
     """Local view of rank ``rank`` of ``nranks``: ``mesh`` (SimplexMesh with the global boundary
     markers carried over), ``node_perm`` (natural local P2 numbering -> owned-first numbering),

@@ -66,6 +66,38 @@ def test_partition_invariants(dim, n, nranks, axis):
         assert np.array_equal(lg[order], gd[sel]) and np.allclose(lv[keep][order], gv[sel])
 
 
+@pytest.mark.parametrize("dim,n,nranks,axis", CASES + [(3, (3, 3, 16), 8, None)])
+def test_peer_memory_tables_emulated_push(dim, n, nranks, axis):
+    """The tables handed to nsb_p2p_connect, checked by emulating the push kernel on the host: every rank
+    stores its boundary values into its neighbours' ring slots at (offset, count) and every rank then finds
+    exactly its ghosts there -- for interleaved widths 3 and 2 (velocity nodes / float4-padded nodes)."""
+    from nsb200 import partition as P
+    mesh = _mesh(dim, n)
+    parts = P.connect([P.build_partition(mesh, r, nranks, axis=axis) for r in range(nranks)])
+    for name in ("nodes", "verts"):
+        plans = [getattr(p, name) for p in parts]
+        layouts = [pl.peer_memory_layout() for pl in plans]
+        for bs in (3, 2, 1):
+            rings = [np.full(max(pl.n_ghost, 1) * 3, np.nan) for pl in plans]         # one ring slot per rank
+            for p, pl in zip(parts, plans):
+                assert len(pl.peers) <= 8
+                nghost, off, slot = pl.peer_memory_tables(p.rank, layouts)
+                x = np.stack([_field(pl.owned_gid) + c for c in range(bs)], axis=1).reshape(-1)
+                for i, r in enumerate(pl.peers):
+                    idx = pl.send_idx[pl.send_ptr[i]:pl.send_ptr[i + 1]]
+                    assert off[i] + len(idx) <= nghost[i] == plans[r].n_ghost and plans[r].peers[slot[i]] == p.rank
+                    vals = x.reshape(-1, bs)[idx].reshape(-1)
+                    rings[r][off[i] * bs: off[i] * bs + len(vals)] = vals
+            for pl, ring in zip(plans, rings):
+                want = np.stack([_field(pl.ghost_gid) + c for c in range(bs)], axis=1).reshape(-1)
+                assert np.array_equal(ring[:pl.n_ghost * bs], want)
+    # a broken pairing is refused
+    bad = [dict(l) for l in [pl.peer_memory_layout() for pl in (p.nodes for p in parts)]]
+    bad[int(parts[0].nodes.peers[0])]["recv_ptr"] = [v + (1 if k else 0) for k, v in enumerate(bad[int(parts[0].nodes.peers[0])]["recv_ptr"])]
+    with pytest.raises(ValueError):
+        parts[0].nodes.peer_memory_tables(0, bad)
+
+
 def test_partition_rejects_too_many_ranks():
     from nsb200 import partition as P
     with pytest.raises(ValueError):
