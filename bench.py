@@ -15,9 +15,15 @@ Prints ONE JSON line (rank 0).  `value` = time steps per second with every input
 host memory and the mixed solution vector copied back to the host inside the timed region.
 `roofline` is for the kernel class with the largest share of the step, from CUDA-event pairs
 recorded by libnsb200 around every launch on the launching stream (nsb_timer_*).
-`cpu_baseline` / `--impl reference`: the CPU oracle (oracle/, plain C assembly + numpy Krylov,
-the "port" of the reference path -- FEniCS itself is unavailable on this box) on a bounded
-sample of the same workload, scaled to the metric's unit by the DOF ratio.
+`cpu_baseline` / `--impl reference`: the CPU oracle (oracle/, plain C/OpenMP assembly and
+Jacobi-GMRES/CG on all host threads, the "port" of the reference path -- FEniCS itself is
+unavailable on this box) on a bounded sample of the same workload: the same cavity problem on a
+16^3 mesh (112 724 DOF).  Its line reports the steps/s it MEASURED at that size under the size it
+ran (`config.cells_per_edge`); the DOF-ratio extrapolation to the 73^3 workload is a separate,
+clearly named field (`extrapolated_to_c5`), never the value.  The GPU line carries `same_size`:
+both arms on the same 16^3 mesh, their ratio, and the relative error of the GPU fields against the
+oracle's after the same steps (`parity_rel_err`); `checksums` (||u||_2, ||p - mean p||_2 after the K
+timed steps, all-reduced over owned dofs) must agree across N = 1, 2, 4, 8.
 """
 import argparse
 import json
@@ -44,6 +50,8 @@ def parse():
     ap.add_argument("--impl", default="nsb200", choices=["nsb200", "reference"])
     ap.add_argument("--n", "--cells", dest="n", type=int, default=73, help="cells per edge of the unit cube (73 -> 9.93 M DOF)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-n", type=int, default=CPU_SAMPLE_N,
+                    help="cells per edge of the bounded sample the CPU arm runs (and of the same-size GPU leg)")
     return ap.parse_args()
 
 
@@ -55,14 +63,25 @@ def mixed_dofs(n):
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the oracle on a bounded sample
 # ---------------------------------------------------------------------------------------------
-def cpu_oracle_steps(n, steps, warmup):
-    """Time `steps` IPCS steps of the CPU oracle (C assembly with all host threads, Jacobi
-    GMRES/CG in numpy) on the n^3 cavity.  Returns (seconds per step, threads)."""
+def host_threads():
+    """threads the CPU arm uses: every core this process may run on, set explicitly (torchrun exports
+    OMP_NUM_THREADS=1, which would silently turn the all-core baseline into a single-thread one)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_oracle_steps(n, steps, warmup, keep_fields=False):
+    """Time `steps` IPCS steps (after `warmup` untimed ones) of the CPU oracle on the n^3 cavity: C/OpenMP
+    assembly + C/OpenMP Jacobi-GMRES(40)/CG at rtol 1e-12 (oracle/c/nsoracle.c) on all host threads.
+    Returns (seconds per step, threads, oracle)."""
     import oracle
+    threads = host_threads()
     om = oracle.mesh.hyper_rectangle((0.0, 0.0, 0.0), (1.0, 1.0, 1.0), (n, n, n))
     vel = [(w, None, (0.0, 0.0, 0.0)) for w in (1, 2, 3, 5, 6)] + [(4, None, (1.0, 0.0, 0.0))]
-    orc = oracle.solvers.IPCSOracle(om, RE, vel, [], assembler="c")
-    orc.linear_solver = "krylov"
+    orc = oracle.solvers.IPCSOracle(om, RE, vel, [], assembler="c", threads=threads)
+    orc.linear_solver = "krylov-c"
     t, times = 0.0, []
     for s in range(warmup + steps):
         alpha = (1.0, -1.0, 0.0) if s == 0 else (1.5, -2.0, 0.5)
@@ -73,30 +92,47 @@ def cpu_oracle_steps(n, steps, warmup):
         el = time.perf_counter() - t0
         if s >= warmup:
             times.append(el)
-    return sum(times) / len(times), orc.asm.threads
+    return sum(times) / len(times), orc.asm.threads, orc
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sec, threads = cpu_oracle_steps(CPU_SAMPLE_N, args.steps, min(args.warmup, 1))
-    scale = mixed_dofs(CPU_SAMPLE_N) / mixed_dofs(args.n)
-    value = scale / sec
-    sample = ("IPCS step on the %d^3 x 6 cavity (%d DOF), C assembly on %d OpenMP threads + numpy Jacobi-GMRES/CG "
-              "(rtol 1e-12); steps/s scaled by the DOF ratio %.4g to the %d^3 workload (linear-cost assumption, "
-              "favours the CPU)" % (CPU_SAMPLE_N, mixed_dofs(CPU_SAMPLE_N), threads, scale, args.n))
+    n = args.ref_n
+    sec, threads, orc = cpu_oracle_steps(n, args.steps, args.warmup)
+    value = 1.0 / sec                      # steps/s MEASURED on the n^3 sample -- nothing is scaled
+    scale = mixed_dofs(n) / mixed_dofs(args.n)
+    sample = ("%d timed IPCS steps (after %d warm-up steps) of the same cavity problem on the %d^3 x 6 mesh (%d DOF): "
+              "C/OpenMP assembly + C/OpenMP Jacobi-GMRES(40)/CG rtol 1e-12 on %d threads, %.3f s/step; value is the "
+              "rate measured at THIS size" % (args.steps, args.warmup, n, mixed_dofs(n), threads, sec))
+    cfg = workload_config(n, 1)
+    cfg["parallelism"] = "%d host threads (OpenMP), no GPU" % threads
+    cfg["l2_policy"] = "n/a (CPU)"
+    cfg["linear_solvers"] = "Jacobi-preconditioned GMRES(40) / CG, rtol 1e-12 (oracle/c/nsoracle.c nso_gmres, nso_pcg)"
+    cfg["bounded_sample_of"] = workload_config(args.n, 1)["workload"]
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 / value,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.n, args.gpus),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": cfg,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "extrapolated_to_c5": {"value": value * scale, "unit": UNIT, "dof_ratio": scale,
+                               "assumption": "cost linear in DOF (favours the CPU: Krylov iteration counts grow with n); "
+                                             "an estimate, not a measurement"},
+        "newton_iterations": orc.newton_iterations[-args.steps:], "krylov_iterations": orc.krylov_iterations[-1],
+        "checksums": oracle_checksums(orc),
         "note": "FEniCS/PETSc (the reference's own CPU path) is not installable on this box; kind=port is the "
-                "CPU oracle restating it (oracle/c/nsoracle.c + oracle/krylov.py)",
+                "CPU oracle restating it (oracle/c/nsoracle.c)",
     }
     print(json.dumps(line), flush=True)
+
+
+def oracle_checksums(orc):
+    import numpy as np
+    u, p = orc.velocities[1], orc.old_pressure
+    return {"u_l2": float(np.linalg.norm(u)), "p_minus_mean_l2": float(np.linalg.norm(p - p.mean()))}
 
 
 def workload_config(n, gpus):
@@ -185,6 +221,62 @@ def algorithmic_bytes(solver):
     }, dict(nV=nV, nQ=nQ, nnz22=nnz22, nnz11=nnz11)
 
 
+def make_cavity_solver(n, rank=0, world=1, local=0):
+    """the C5 problem on the n^3 x 6 unit cube: lid (1,0,0) on y = 1, no-slip elsewhere, from rest"""
+    import nsb200
+    V = nsb200.VelocityBCType
+    mesh, markers = nsb200.hyper_cube(3, n)
+    part = None
+    if world > 1:
+        # mesh-partitioned run (SURVEY.md 8e): z-slabs, one rank per GPU, halos + all-reduces in libnsb200
+        from nsb200 import partition as npart
+        part = npart.connect_distributed(npart.build_partition(mesh, rank, world))
+    ts = nsb200.BDFTimeStepping(0.0, 1.0e6, order=2, desired_start_time_step=DT)
+    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=local, partition=part)
+    solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / RE))
+    solver.set_boundary_conditions([(V.no_slip, w, None) for w in (1, 2, 3, 5, 6)] + [(V.constant, 4, (1.0, 0.0, 0.0))])
+    return solver, ts
+
+
+def same_size_leg(n_ref, steps, local):
+    """Both arms on the SAME n_ref^3 mesh for the same `steps` time steps from rest: measured steps/s of each
+    (the GPU's through the public API incl. the per-step solution copy to the host), their ratio, and the
+    relative max-norm error of the GPU fields against the oracle's (pressure up to its mean: the all-Neumann
+    problem fixes p only up to a constant)."""
+    import numpy as np
+    import torch
+    solver, ts = make_cavity_solver(n_ref, local=local)
+
+    def run(k):
+        for _ in range(k):
+            ts.update_coefficients()
+            solver.solve(upload_bcs=True)
+            solver.fetch_solution()
+            ts.advance_time()
+            solver.advance_time()
+    state = solver.get_state()
+    run(steps)                                  # untimed pass: one-time setup (constant operators, pinned buffers)
+    solver.set_state(state)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    run(steps)
+    torch.cuda.synchronize()
+    gpu_sec = (time.perf_counter() - t0) / steps
+    u = solver._velocities[1].cpu().numpy()
+    p = solver._old_pressure.cpu().numpy()
+    cpu_sec, threads, orc = cpu_oracle_steps(n_ref, steps, 0)
+    ou, op = orc.velocities[1], orc.old_pressure
+    err = {"velocity": float(np.abs(u - ou).max() / np.abs(ou).max()),
+           "pressure_minus_mean": float(np.abs((p - p.mean()) - (op - op.mean())).max() / np.abs(op - op.mean()).max())}
+    out = {"cells_per_edge": n_ref, "mixed_dofs": mixed_dofs(n_ref), "steps": steps,
+           "gpu_steps_per_s_e2e": 1.0 / gpu_sec, "cpu_steps_per_s": 1.0 / cpu_sec, "cpu_threads": threads,
+           "ratio": cpu_sec / gpu_sec, "parity_rel_err": err,
+           "newton_iterations": {"gpu": solver.newton_iterations[-steps:], "cpu": orc.newton_iterations[-steps:]},
+           "checksums": {"gpu": solver.checksums(lagged=True), "cpu": oracle_checksums(orc)}}
+    solver.dev.close()
+    return out, cpu_sec, threads
+
+
 def run_nsb200(args):
     import torch
     import __graft_entry__
@@ -202,18 +294,8 @@ def run_nsb200(args):
     if world > 1:
         dist.barrier()
     import nsb200
-    V = nsb200.VelocityBCType
     n = args.n
-    mesh, markers = nsb200.hyper_cube(3, n)
-    part = None
-    if world > 1:
-        # mesh-partitioned run: z-slabs, one rank per GPU, halos + all-reduces in libnsb200
-        from nsb200 import partition as npart
-        part = npart.connect_distributed(npart.build_partition(mesh, rank, world))
-    ts = nsb200.BDFTimeStepping(0.0, 1.0e6, order=2, desired_start_time_step=DT)
-    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=local, partition=part)
-    solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / RE))
-    solver.set_boundary_conditions([(V.no_slip, w, None) for w in (1, 2, 3, 5, 6)] + [(V.constant, 4, (1.0, 0.0, 0.0))])
+    solver, ts = make_cavity_solver(n, rank, world, local)
     dev = solver.dev
 
     def step(e2e=False):
@@ -273,6 +355,7 @@ def run_nsb200(args):
     solver.set_state(state)
     del state
     ms_e2e, h2d, d2h = timed(args.steps, True)
+    checksums = solver.checksums(lagged=True)      # collective on a partitioned run: before the tear-down
     if world > 1:
         # collective tear-down BEFORE rank 0 goes off to format the result: every rank leaves together
         per_rank = [None] * world
@@ -322,7 +405,7 @@ def run_nsb200(args):
             breakdown[k]["frac_of_hbm_peak"] = breakdown[k]["GB/s"] / hbm_peak
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
-        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak" if world == 1 else "strong", "vs_baseline": None,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": workload_config(n, world), "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches, "roofline": roofline, "breakdown": breakdown,
@@ -331,17 +414,20 @@ def run_nsb200(args):
                           % (K, ms_instrumented / K),
         "newton_iterations": solver.newton_iterations[-K:], "krylov_iterations": solver.krylov_iterations[-1],
         "chebyshev_fallbacks": solver.chebyshev_fallbacks,
+        "checksums": checksums,
         "assembly_gdof_per_s": {k: sizes["nV"] / (big[k][0] / big[k][1] * 1e-3) / 1e9
                                 for k in ("asm_jacobian", "asm_residual") if big[k][1]},
     }
     if world == 1 and not args.no_cpu_baseline:
-        sec, threads = cpu_oracle_steps(CPU_SAMPLE_N, 2, 1)
-        scale = mixed_dofs(CPU_SAMPLE_N) / mixed_dofs(n)
+        ss, sec, threads = same_size_leg(args.ref_n, 2, local)
+        scale = mixed_dofs(args.ref_n) / mixed_dofs(n)
         line["cpu_baseline"] = {
-            "value": scale / sec, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": "2 IPCS steps of the CPU oracle (C assembly, %d OpenMP threads; numpy Jacobi-GMRES/CG rtol 1e-12) "
-                      "on the %d^3 x 6 cavity (%d DOF, %.3f s/step), scaled by the DOF ratio %.4g"
-                      % (threads, CPU_SAMPLE_N, mixed_dofs(CPU_SAMPLE_N), sec, scale)}
+            "value": 1.0 / sec, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "2 IPCS steps from rest of the same cavity problem on the %d^3 x 6 mesh (%d DOF): C/OpenMP assembly + "
+                      "C/OpenMP Jacobi-GMRES(40)/CG rtol 1e-12 on %d threads, %.3f s/step; value is the rate MEASURED at "
+                      "that size (DOF-ratio estimate for the %d^3 workload: %.3g steps/s, not a measurement)"
+                      % (args.ref_n, mixed_dofs(args.ref_n), threads, sec, n, scale / sec)}
+        line["same_size"] = ss
     if per_rank is not None:
         line["partition"] = per_rank
         line["halo_transport"] = solver.dev.halo_transport

@@ -90,10 +90,13 @@ class Pattern:
 class Device:
     """One GPU, one mesh.  Raises if CUDA or libnsb200.so is unavailable (no CPU fallback)."""
 
-    def __init__(self, mesh, device_index=0, mixed=False, partition=None):
+    def __init__(self, mesh, device_index=0, mixed=False, partition=None, node_perm=None):
         """``partition`` (partition.Partition with finalized halo plans): this rank's share of a
         mesh-partitioned run; ``mesh`` is then ignored in favour of the partition's local mesh and
-        torch.distributed must be initialised (it carries the NCCL id to the other ranks)."""
+        torch.distributed must be initialised (it carries the NCCL id to the other ranks).
+        ``node_perm`` (ingest mode): natural P2 node number (vertex v / N0 + e) -> the node
+        number to use on the device, e.g. the one a real dolfin's re-ordered dofmap assigns; every map,
+        pattern and kernel then works in that numbering."""
         if not torch.cuda.is_available():
             raise RuntimeError("nsb200 needs a CUDA device: there is no CPU fallback")
         self.lib = L.load()
@@ -106,7 +109,8 @@ class Device:
             assert not mixed, "the monolithic solvers run on one GPU (SURVEY.md 8e: replicas only)"
             mesh = partition.mesh
         self.mesh = mesh
-        self.spaces = sp = TaylorHoodSpaces(mesh, None if partition is None else partition.node_perm)
+        assert partition is None or node_perm is None
+        self.spaces = sp = TaylorHoodSpaces(mesh, node_perm if partition is None else partition.node_perm)
         self.dim = sp.dim
         self.n_owned_nodes = sp.n_nodes if partition is None else partition.nodes.n_owned
         self.n_owned_verts = sp.n_vertices if partition is None else partition.verts.n_owned

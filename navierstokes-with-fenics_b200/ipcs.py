@@ -346,6 +346,17 @@ class IPCSSolver(SolverBase):
             self._w[sp.dim * sp.n_nodes:] -= shift
         return self._w
 
+    def checksums(self, lagged=False):
+        """{||u||_2, ||p - mean p||_2} over the owned dofs of all ranks (all-reduced): what bench.py prints so
+        that runs on 1, 2, 4 and 8 GPUs can be compared.  ``lagged``: the fields after ``advance_time``
+        (velocities[1], old_pressure) instead of the current ones."""
+        dev = self.dev
+        u = (self._velocities[1] if lagged else self._velocities[0])[:self._nV_own]
+        p = (self._old_pressure if lagged else self._pressure)[:self._nQ_own]
+        nq = float(dev.partition.verts.n_global) if dev.partition is not None else float(self._nQ_own)
+        pp, ps = dev.dot(p, p), dev.sum(p)
+        return {"u_l2": float(np.sqrt(dev.dot(u, u))), "p_minus_mean_l2": float(np.sqrt(max(pp - ps * ps / nq, 0.0)))}
+
     def mean_pressure(self):
         dev = self.dev
         if not hasattr(self, "_p1_weights"):

@@ -400,3 +400,165 @@ void nso_spmv(int64_t n, const int64_t* rowptr, const int32_t* col, const double
         y[i] = s;
     }
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Krylov solvers in C/OpenMP: the algorithm-matched CPU arm of bench.py (SURVEY.md 8d variant (b)) --
+ * the same Jacobi-preconditioned CG / right-Jacobi restarted GMRES with CGS-2 as oracle/krylov.py
+ * (which stays the readable statement, and the two are compared in tests/test_oracle.py), without the
+ * numpy temporaries, so that the CPU baseline is bound by the host's memory bandwidth and not by the
+ * interpreter.  Stopping rule of include/nsb200.h: ||r|| <= max(rtol ||b||, atol).
+ * ------------------------------------------------------------------------------------------- */
+static double par_dot(int64_t n, const double* x, const double* y) {
+    double s = 0.0;
+#pragma omp parallel for reduction(+ : s) schedule(static)
+    for (int64_t i = 0; i < n; ++i) s += x[i] * y[i];
+    return s;
+}
+
+static double par_sum(int64_t n, const double* x) {
+    double s = 0.0;
+#pragma omp parallel for reduction(+ : s) schedule(static)
+    for (int64_t i = 0; i < n; ++i) s += x[i];
+    return s;
+}
+
+/* Jacobi-PCG.  nullspace != 0: constant null space, rhs and solution projected to zero mean.
+ * Returns the iteration count (negative: not converged); *resid = final ||r||. */
+int nso_pcg(int64_t n, const int64_t* rowptr, const int32_t* col, const double* vals, const double* b_in, double* x,
+            double rtol, double atol, int maxit, int nullspace, double* resid) {
+    double* w = (double*)malloc(sizeof(double) * 6 * (size_t)n);
+    if (!w) return -1000000;
+    double *b = w, *r = w + n, *z = w + 2 * n, *p = w + 3 * n, *q = w + 4 * n, *dinv = w + 5 * n;
+    const double shift = nullspace ? par_sum(n, b_in) / (double)n : 0.0;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        double d = 1.0;
+        for (int64_t k = rowptr[i]; k < rowptr[i + 1]; ++k)
+            if (col[k] == i) d = vals[k];
+        dinv[i] = 1.0 / d;
+        b[i] = b_in[i] - shift;
+    }
+    nso_spmv(n, rowptr, col, vals, x, q);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        r[i] = b[i] - q[i];
+        z[i] = dinv[i] * r[i];
+        p[i] = z[i];
+    }
+    double rz = par_dot(n, r, z), rr = par_dot(n, r, r);
+    const double bn = sqrt(par_dot(n, b, b));
+    const double tol = fmax(rtol * bn, atol);
+    int it = 0;
+    while (sqrt(rr) > tol && it < maxit) {
+        nso_spmv(n, rowptr, col, vals, p, q);
+        const double alpha = rz / par_dot(n, p, q);
+        double rz_new = 0.0, rr_new = 0.0;
+#pragma omp parallel for reduction(+ : rz_new, rr_new) schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+            x[i] += alpha * p[i];
+            const double ri = r[i] - alpha * q[i];
+            r[i] = ri;
+            const double zi = dinv[i] * ri;
+            z[i] = zi;
+            rz_new += ri * zi;
+            rr_new += ri * ri;
+        }
+        const double beta = rz_new / rz;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
+        rz = rz_new;
+        rr = rr_new;
+        ++it;
+    }
+    if (nullspace) {
+        const double m = par_sum(n, x) / (double)n;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) x[i] -= m;
+    }
+    if (resid) *resid = sqrt(rr);
+    free(w);
+    return sqrt(rr) <= tol ? it : -it - 1;
+}
+
+/* right-Jacobi-preconditioned GMRES(restart), CGS-2 Arnoldi.  Returns iterations (negative: not converged). */
+int nso_gmres(int64_t n, const int64_t* rowptr, const int32_t* col, const double* vals, const double* b, double* x,
+              double rtol, double atol, int maxit, int restart, double* resid) {
+    const int m = restart;
+    double* V = (double*)malloc(sizeof(double) * (size_t)(m + 4) * (size_t)n);
+    double* H = (double*)calloc((size_t)(m + 1) * m, sizeof(double));
+    double* sm = (double*)malloc(sizeof(double) * (size_t)(5 * m + 8));
+    if (!V || !H || !sm) { free(V); free(H); free(sm); return -1000000; }
+    double *w = V + (size_t)(m + 1) * n, *t = w + n, *dinv = t + n;
+    double *cs = sm, *sn = sm + m, *g = sm + 2 * m, *y = sm + 3 * m + 1, *h = sm + 4 * m + 1;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        double d = 1.0;
+        for (int64_t k = rowptr[i]; k < rowptr[i + 1]; ++k)
+            if (col[k] == i) d = vals[k];
+        dinv[i] = 1.0 / d;
+    }
+    const double tol = fmax(rtol * sqrt(par_dot(n, b, b)), atol);
+    int it = 0;
+    double rn = 0.0;
+    for (;;) {
+        nso_spmv(n, rowptr, col, vals, x, t);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) w[i] = b[i] - t[i];
+        rn = sqrt(par_dot(n, w, w));
+        if (rn <= tol || it >= maxit) break;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) V[i] = w[i] / rn;
+        memset(g, 0, sizeof(double) * (m + 1));
+        g[0] = rn;
+        int j = 0;
+        while (j < m && it < maxit) {
+            const double* vj = V + (size_t)j * n;
+#pragma omp parallel for schedule(static)
+            for (int64_t i = 0; i < n; ++i) t[i] = dinv[i] * vj[i];
+            nso_spmv(n, rowptr, col, vals, t, w);
+            double* Hj = H + (size_t)j * (m + 1);
+            for (int k = 0; k <= j; ++k) Hj[k] = 0.0;
+            for (int pass = 0; pass < 2; ++pass) {
+                for (int k = 0; k <= j; ++k) h[k] = par_dot(n, V + (size_t)k * n, w);
+#pragma omp parallel for schedule(static)
+                for (int64_t i = 0; i < n; ++i) {
+                    double wi = w[i];
+                    for (int k = 0; k <= j; ++k) wi -= h[k] * V[(size_t)k * n + i];
+                    w[i] = wi;
+                }
+                for (int k = 0; k <= j; ++k) Hj[k] += h[k];
+            }
+            const double wn = sqrt(par_dot(n, w, w));
+            Hj[j + 1] = wn;
+            double* vn = V + (size_t)(j + 1) * n;
+#pragma omp parallel for schedule(static)
+            for (int64_t i = 0; i < n; ++i) vn[i] = w[i] / wn;
+            for (int k = 0; k < j; ++k) {
+                const double a = cs[k] * Hj[k] + sn[k] * Hj[k + 1];
+                Hj[k + 1] = -sn[k] * Hj[k] + cs[k] * Hj[k + 1];
+                Hj[k] = a;
+            }
+            const double dd = hypot(Hj[j], Hj[j + 1]);
+            cs[j] = Hj[j] / dd; sn[j] = Hj[j + 1] / dd;
+            Hj[j] = dd; Hj[j + 1] = 0.0;
+            g[j + 1] = -sn[j] * g[j];
+            g[j] = cs[j] * g[j];
+            ++it; ++j;
+            if (fabs(g[j]) <= tol) break;
+        }
+        for (int i = j - 1; i >= 0; --i) {
+            double s = g[i];
+            for (int k = i + 1; k < j; ++k) s -= H[(size_t)k * (m + 1) + i] * y[k];
+            y[i] = s / H[(size_t)i * (m + 1) + i];
+        }
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+            double s = 0.0;
+            for (int k = 0; k < j; ++k) s += y[k] * V[(size_t)k * n + i];
+            x[i] += dinv[i] * s;
+        }
+    }
+    if (resid) *resid = rn;
+    free(V); free(H); free(sm);
+    return rn <= tol ? it : -it - 1;
+}

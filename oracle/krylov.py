@@ -105,3 +105,31 @@ def gmres(A, b, x0=None, rtol=1e-12, atol=0.0, maxit=2000, restart=40):
         y = np.linalg.solve(np.triu(H[:j, :j]), g[:j])
         x += dinv * (y @ V[:j])
     return x, it
+
+
+# ---- the same two solvers in C/OpenMP (oracle/c/nsoracle.c nso_pcg / nso_gmres): the timed CPU arm ----
+def _csr_args(A):
+    op = A if isinstance(A, Operator) else Operator(A)
+    return op, (C.c_int64(op.n), op.rowptr.ctypes.data, op.col.ctypes.data, op.vals.ctypes.data)
+
+
+def pcg_c(A, b, x0=None, rtol=1e-12, atol=0.0, maxit=10000, nullspace=False):
+    op, args = _csr_args(A)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    x = np.zeros_like(b) if x0 is None else np.array(x0, dtype=np.float64)
+    res = C.c_double()
+    it = op.lib.nso_pcg(*args, b.ctypes.data, x.ctypes.data, rtol, atol, maxit, 1 if nullspace else 0, C.byref(res))
+    if it < 0:
+        raise RuntimeError("nso_pcg did not converge (%d iterations, residual %g)" % (-it - 1, res.value))
+    return x, it
+
+
+def gmres_c(A, b, x0=None, rtol=1e-12, atol=0.0, maxit=2000, restart=40):
+    op, args = _csr_args(A)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    x = np.zeros_like(b) if x0 is None else np.array(x0, dtype=np.float64)
+    res = C.c_double()
+    it = op.lib.nso_gmres(*args, b.ctypes.data, x.ctypes.data, rtol, atol, maxit, restart, C.byref(res))
+    if it < 0:
+        raise RuntimeError("nso_gmres did not converge (%d iterations, residual %g)" % (-it - 1, res.value))
+    return x, it

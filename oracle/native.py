@@ -71,6 +71,10 @@ def load():
         lib.nso_correction_rhs.argtypes = [C.POINTER(_Mesh), vp, vp, vp, vp, vp, C.c_double, vp]
         lib.nso_spmv.restype = None
         lib.nso_spmv.argtypes = [C.c_int64, vp, vp, vp, vp, vp]
+        lib.nso_pcg.restype = C.c_int
+        lib.nso_pcg.argtypes = [C.c_int64, vp, vp, vp, vp, vp, C.c_double, C.c_double, C.c_int, C.c_int, vp]
+        lib.nso_gmres.restype = C.c_int
+        lib.nso_gmres.argtypes = [C.c_int64, vp, vp, vp, vp, vp, C.c_double, C.c_double, C.c_int, C.c_int, vp]
         _lib = lib
     return _lib
 

@@ -115,7 +115,8 @@ class IPCSOracle(_Base):
         self.pressure_bcs = list(pressure_bcs)        # [(marker, value)]
         self.tol, self.max_iter = tol, max_iter
         self.alpha, self.k = (1.0, -1.0, 0.0), None
-        self.linear_solver = "lu"          # "lu" (reference-faithful) | "krylov" (algorithm-matched)
+        self.linear_solver = "lu"          # "lu" (reference-faithful) | "krylov" / "krylov-c" (algorithm-matched)
+        self.krylov_rtol = 1e-12
         self.krylov_iterations = []
 
     def _bcs_at(self, t):
@@ -150,13 +151,17 @@ class IPCSOracle(_Base):
         def J(x):
             return obc.apply_ident(asm.ipcs_momentum_jacobian(x, a0, k, self.c_conv, self.c_visc), vd)
 
-        krylov = self.linear_solver == "krylov"
+        krylov = self.linear_solver in ("krylov", "krylov-c")
         kit = dict(momentum=[], pressure=0, correction=0)
         if krylov:
-            from . import krylov as okr
+            from . import krylov as _okr
+
+            class okr:                      # "krylov": numpy statement; "krylov-c": the same in C/OpenMP
+                gmres = staticmethod(_okr.gmres_c if self.linear_solver == "krylov-c" else _okr.gmres)
+                pcg = staticmethod(_okr.pcg_c if self.linear_solver == "krylov-c" else _okr.pcg)
 
             def lin(A, b):
-                x, n_it = okr.gmres(A, b, rtol=1e-12)
+                x, n_it = okr.gmres(A, b, rtol=self.krylov_rtol)
                 kit["momentum"].append(n_it)
                 return x
         else:
@@ -173,9 +178,9 @@ class IPCSOracle(_Base):
                 x0 = self.pressure.copy()
                 x0[pd] = pv
                 self.pressure[:], kit["pressure"] = okr.pcg(obc.apply_ident(A, pd), obc.apply_rhs_linear(b, pd, pv),
-                                                            x0=x0, rtol=1e-12)
+                                                            x0=x0, rtol=self.krylov_rtol)
             else:
-                self.pressure[:], kit["pressure"] = okr.pcg(A, b, x0=self.pressure, rtol=1e-12, nullspace=True)
+                self.pressure[:], kit["pressure"] = okr.pcg(A, b, x0=self.pressure, rtol=self.krylov_rtol, nullspace=True)
         elif len(pd):
             self.pressure[:] = lu_solve(obc.apply_ident(A, pd), obc.apply_rhs_linear(b, pd, pv))
         else:
@@ -187,7 +192,7 @@ class IPCSOracle(_Base):
             x0 = self.intermediate_velocity.copy()
             x0[vd] = vv
             self.velocities[0][:], kit["correction"] = okr.pcg(obc.apply_ident(M, vd),
-                                                               obc.apply_rhs_linear(b, vd, vv), x0=x0, rtol=1e-12)
+                                                               obc.apply_rhs_linear(b, vd, vv), x0=x0, rtol=self.krylov_rtol)
         else:
             self.velocities[0][:] = lu_solve(obc.apply_ident(M, vd), obc.apply_rhs_linear(b, vd, vv))
         self.krylov_iterations.append(kit)
