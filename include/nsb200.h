@@ -264,6 +264,33 @@ int nsb_boundary_force(nsb_ctx* ctx, int32_t nfacets, const int32_t* facet_cell_
                        const uint8_t* facet_opp_dev, const double* u, const double* p, double c_visc,
                        double* force_out_host3, void* stream);
 
+/* ---------------------------------------------------------------- projection / diagnostics */
+/* Right-hand side of dolfin.project(expr, V|Q) (source/ns_solver_base.py:1151,1168; the mean-pressure
+ * re-projection :1201; demo/taylor_green_vortex.py:61-69): the host interpolates the Expression into P_k on
+ * every cell (cell_vals_dev [ncells][nk][ncomp], values at the cell's P_k lattice nodes) and hands over the
+ * exact reference tensor table_dev [nloc_row][nk] = int phi_I psi^k_J; b[row*ncomp+c] = sum over incident
+ * cells of detJ sum_J table[I][J] vals[cell][J][c].  which = NSB_PAT_P2P2 (rows = P2 nodes) | NSB_PAT_P1P1
+ * (rows = vertices).  The mass solve that follows is nsb_cg on the P2 / P1 mass matrix. */
+int nsb_assemble_cell_rhs(nsb_ctx* ctx, int32_t which, int32_t nk, int32_t ncomp, const double* table_dev,
+                          const double* cell_vals_dev, double* b_out, void* stream);
+/* dolfin.errornorm(u_exact, u_h) ** 2 (convergence_test/taylor_green_vortex.py:101-119): both functions interpolated
+ * into P_{k+3} on every cell, the difference integrated exactly.  cell_vals_dev [ncells][nk][ncomp]: the exact
+ * solution at the cell's lattice nodes; E_dev [nk][nloc]: the space's basis at those nodes; Psi_dev [nq][nk], wq_dev
+ * [nq]: the P_{k+3} basis at the points of a quadrature rule exact for degree 2(k+3), and its weights (reference
+ * cell, sum = 1/d!); work_dev [ncells*nk*ncomp] scratch.  space as `which` above; uh interleaved (ncomp per node). */
+int nsb_cell_error_norm2(nsb_ctx* ctx, int32_t space, int32_t ncomp, const double* uh, int32_t nk,
+                         const double* E_dev, int32_t nq, const double* Psi_dev, const double* wq_dev,
+                         const double* cell_vals_dev, double* work_dev, double* out_host, void* stream);
+/* CFL diagnostic of source/ns_problem.py:554-587 (runs every step, :714): max-norm of the DG-k LocalSolver
+ * projection of  k |u| dt / h_T  (quadrature degree 2k; h_T = UFL CellDiameter = longest edge).  scale = k * dt;
+ * B_dev [nq][NL2]: P2 basis at the quadrature points; P_dev [NL2][nq]: nodes x points matrix of the local
+ * projection  Phi (B^T W B)^-1 B^T W.  u in V numbering.  Max over all ranks on a partitioned mesh. */
+int nsb_cfl_max(nsb_ctx* ctx, const double* u, double scale, int32_t nq, const double* B_dev,
+                const double* P_dev, double* out_host, void* stream);
+/* x -= s: the mean-pressure shift of source/ns_solver_base.py:1190-1203 (subtracting a constant from a P1
+ * function IS its L2 projection) */
+int nsb_vec_shift(nsb_ctx* ctx, int64_t n, double s, double* x, void* stream);
+
 /* ---------------------------------------------------------------- direct solve (K16) ----- */
 /* x = A^-1 b for the indefinite mixed Newton system, which the reference hands to PETSc's sparse LU
  * (source/ns_bdf_solver.py:91-100,106; source/ns_solver_base.py:938-949,974-983).  LIBRARY leg, not

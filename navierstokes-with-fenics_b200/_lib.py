@@ -75,6 +75,10 @@ PROTOTYPES = {
                          vp, c_i32p, c_f64p, vp]),
     "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                             C.c_int32, vp, c_i32p, c_f64p, vp]),
+    "nsb_assemble_cell_rhs": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp]),
+    "nsb_cell_error_norm2": (C.c_int, [vp, C.c_int32, C.c_int32, vp, C.c_int32, vp, C.c_int32, vp, vp, vp, vp, c_f64p, vp]),
+    "nsb_cfl_max": (C.c_int, [vp, vp, C.c_double, C.c_int32, vp, vp, c_f64p, vp]),
+    "nsb_vec_shift": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp]),
     "nsb_vec_copy": (C.c_int, [vp, C.c_int64, vp, vp, vp]),
     "nsb_vec_axpy": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp, vp]),
     "nsb_vec_scale": (C.c_int, [vp, C.c_int64, C.c_double, vp, vp]),

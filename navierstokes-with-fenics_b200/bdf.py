@@ -7,8 +7,6 @@ the GPU.  Same constructor arguments and public methods as the reference class
 The Newton update is the K16 library leg (cuSOLVER sparse QR, ``monolithic.py``), whose time is
 reported apart (``direct_solve_seconds``), as BASELINE.json's north star asks.
 """
-import numpy as np
-
 from . import _lib as L
 from .monolithic import MixedSolverBase
 
@@ -36,23 +34,17 @@ class ImplicitBDFSolver(MixedSolverBase):
                                   co["viscous_term"])
 
     def set_initial_conditions(self, initial_conditions):
-        """source/ns_solver_base.py:1123-1171: nodal data of degree <= 2 / 1, for which dolfin's
-        projection is the identity; written to solutions[0] and [1]."""
+        """source/ns_solver_base.py:1123-1171: ``dolfin.project`` of the initial data (``ipcs.initial_fields``),
+        written to solutions[0] and [1]."""
+        from .ipcs import initial_fields
         assert isinstance(initial_conditions, dict) and "velocity" in initial_conditions
-        sp, dev = self.dev.spaces, self.dev
-        d, nn = sp.dim, sp.n_nodes
-        w = np.zeros(self._nW)
-        v = initial_conditions["velocity"]
-        x = sp.node_coordinates()
-        u0 = np.asarray(v(x), dtype=np.float64).reshape(nn, d) if callable(v) else \
-            np.broadcast_to(np.asarray(v, dtype=np.float64), (nn, d))
-        for c in range(d):
-            w[c * nn:(c + 1) * nn] = u0[:, c]
-        if "pressure" in initial_conditions:
-            p = initial_conditions["pressure"]
-            xv = sp.mesh.coords
-            w[d * nn:] = np.asarray(p(xv), dtype=np.float64).reshape(-1) if callable(p) else float(p)
-        w = dev.upload(w)
+        dev = self.dev
+        u0, p0 = initial_fields(dev, initial_conditions)
+        v2w, q2w = self._maps()
+        w = dev.zeros(self._nW)
+        dev.scatter(v2w, u0, w)
+        if p0 is not None:
+            dev.scatter(q2w, p0, w)
         self._solutions[0].copy_(w)
         self._solutions[1].copy_(w)
 
@@ -64,6 +56,20 @@ class ImplicitBDFSolver(MixedSolverBase):
         self._update_bc_values()
         self._update_time_stepping_coefficients()
         self._solve_time_step()
+        if hasattr(self, "_mean_pressure_value"):
+            self._shift_mean_pressure()
+
+    def _shift_mean_pressure(self):
+        """source/ns_solver_base.py:1190-1203: p <- p - (int p / int 1 - target), in place on solutions[0]"""
+        dev, sp = self.dev, self.dev.spaces
+        p = self._solutions[0][sp.dim * sp.n_nodes:]          # the pressure block of W is in Q numbering
+        integral, volume = dev.p1_integral(p)
+        dev.shift(p, integral / volume - self._mean_pressure_value)
+
+    def cfl_number(self, step_size=None):
+        """``InstationaryProblem._compute_cfl_number`` (source/ns_problem.py:554-587)"""
+        k = self._time_stepping.get_next_step_size() if step_size is None else step_size
+        return self.dev.cfl(self.velocity, k)
 
     def _residual(self):
         dev, w = self.dev, self._solutions

@@ -448,6 +448,106 @@ class Device:
         self.check(self.lib.nsb_direct_seconds(self.ctx, C.byref(sec), C.byref(n), 1 if reset else 0))
         return sec.value, n.value
 
+    # ---- L2 projection, error norms, CFL (csrc/project.cu) ----------------------
+    def _cell_lattice_values(self, fn, k, ncomp):
+        """values of ``fn(x[n,d]) -> [n,ncomp]`` at the P_k lattice nodes of every cell (dolfin's per-cell
+        interpolation of an Expression of degree k), device tensor [ncells, nk, ncomp]"""
+        from . import lagrange
+        m, d = self.mesh, self.dim
+        lam = lagrange._bary(lagrange.lattice_points(d, k))                # [nk, d+1]
+        X = np.einsum("km,cmi->cki", lam, m.coords[m.cells])               # [ncells, nk, d]
+        F = np.asarray(fn(X.reshape(-1, d)), dtype=np.float64).reshape(m.num_cells, lam.shape[0], ncomp)
+        return self.upload(F), lam.shape[0]
+
+    def mass_operator(self, space):
+        """(nsb_matrix, inverse diagonal) of the P2 (x I_d) / P1 mass matrix without Dirichlet rows, cached"""
+        if not hasattr(self, "_mass_ops"):
+            self._mass_ops = {}
+        if space not in self._mass_ops:
+            if space == "V":
+                pat = self.pattern("P2P2")
+                A = self.empty(pat.nnz)
+                self.assemble_correction(L.MAT, A=A)
+                M = self.matrix("P2P2", A, L.CSR, self.dim)
+            else:
+                pat = self.pattern("P1P1")
+                A = self.empty(pat.nnz)
+                self.assemble_p1_mass(L.MAT, A=A)
+                M = self.matrix("P1P1", A, L.CSR, 1)
+            dinv = self.empty(M.nrows * M.bs)
+            self.inv_diagonal(M, dinv)
+            self._mass_ops[space] = (M, dinv)
+        return self._mass_ops[space]
+
+    def project(self, fn, space, degree, out=None, rtol=1e-14):
+        """``dolfin.project(Expression(degree=degree), V|Q)`` (source/ns_solver_base.py:1151,1168): cell-wise P_k
+        interpolant of ``fn``, exact right-hand side on the device, mass solve by Jacobi-CG (LU in the
+        reference).  Returns the [owned | ghost] dof vector (V interleaved / Q)."""
+        from . import lagrange
+        assert space in ("V", "Q") and degree >= 1
+        d = self.dim
+        ncomp = d if space == "V" else 1
+        which, pname, halo = (L.PAT_P2P2, "P2P2", L.HALO_NODES) if space == "V" else (L.PAT_P1P1, "P1P1", L.HALO_VERTS)
+        self.pattern(pname)
+        F, nk = self._cell_lattice_values(fn, degree, ncomp)
+        R = self.upload(lagrange.cross_mass(d, "P2" if space == "V" else "P1", degree))
+        M, dinv = self.mass_operator(space)
+        n_own = M.nrows * M.bs
+        b = self.empty(n_own)
+        self.check(self.lib.nsb_assemble_cell_rhs(self.ctx, which, nk, ncomp, _ptr(R), _ptr(F), _ptr(b), self.stream))
+        n_all = (self.spaces.n_nodes * d) if space == "V" else self.spaces.n_vertices
+        x = self.zeros(n_all) if out is None else out
+        x[:n_own].zero_()
+        self.cg(M, dinv, b, x, rtol=rtol)
+        self.halo_exchange(halo, ncomp, x)
+        return x
+
+    def errornorm(self, exact_fn, uh, space, degree_rise=3):
+        """``dolfin.errornorm(u_exact, u_h)`` (L2, default degree_rise = 3; App. A.7): both interpolated into
+        P_{k+3} on every cell, || difference ||_L2"""
+        from . import lagrange
+        assert self.partition is None, "errornorm runs on one GPU"
+        d = self.dim
+        ncomp, k0, which = (d, 2, L.PAT_P2P2) if space == "V" else (1, 1, L.PAT_P1P1)
+        k = k0 + degree_rise
+        F, nk = self._cell_lattice_values(exact_fn, k, ncomp)
+        pts = lagrange.lattice_points(d, k)
+        E = lagrange.eval_p2(d, pts) if space == "V" else lagrange.eval_p1(d, pts)
+        Xq, Wq = lagrange.simplex_rule(d, 2 * k)
+        Psi = lagrange.eval_lagrange(d, k, Xq)
+        work = self.empty(F.numel())
+        out = C.c_double()
+        self.check(self.lib.nsb_cell_error_norm2(self.ctx, which, ncomp, _ptr(uh), nk, _ptr(self.upload(E)), len(Wq),
+                                                 _ptr(self.upload(Psi)), _ptr(self.upload(Wq)), _ptr(F), _ptr(work),
+                                                 C.byref(out), self.stream))
+        return float(np.sqrt(max(out.value, 0.0)))
+
+    def cfl(self, u, step_size, degree=2):
+        """max local CFL number of source/ns_problem.py:554-587 for the P2 velocity ``u`` (V numbering)"""
+        from . import lagrange
+        if not hasattr(self, "_cfl_tabs"):
+            B, P = lagrange.cfl_tables(self.dim)
+            self._cfl_tabs = (self.upload(B), self.upload(P), B.shape[0])
+        B, P, nq = self._cfl_tabs
+        out = C.c_double()
+        self.check(self.lib.nsb_cfl_max(self.ctx, _ptr(u), float(degree) * float(step_size), nq, _ptr(B), _ptr(P),
+                                        C.byref(out), self.stream))
+        return out.value
+
+    def shift(self, x, s):
+        """x -= s"""
+        self.check(self.lib.nsb_vec_shift(self.ctx, x.numel(), float(s), _ptr(x), self.stream))
+
+    def p1_integral(self, p):
+        """(int p dx, int 1 dx) for a P1 function in Q numbering (source/ns_solver_base.py:1194)"""
+        n_own = self.n_owned_verts
+        if not hasattr(self, "_p1_weights"):
+            self.pattern("P1P1")
+            self._p1_weights = self.empty(n_own)
+            self.assemble_p1_mass(L.VEC, w=self._p1_weights)
+            self._volume = self.sum(self._p1_weights)
+        return self.dot(self._p1_weights, p[:n_own]), self._volume
+
     def block_scalar_f32(self, vals, bs, out):
         """out[k] = float(mean of the diagonal of the bs x bs block k of ``vals``)"""
         self.check(self.lib.nsb_bsr_block_scalar_f32(self.ctx, out.numel(), bs, _ptr(vals), _ptr(out), self.stream))

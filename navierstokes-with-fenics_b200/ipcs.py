@@ -14,6 +14,33 @@ from .device import Device
 from .solver_base import SolverBase, Expression, NewtonNotConverged, newton_converged
 
 
+def initial_fields(dev, initial_conditions):
+    """(velocity in V numbering, pressure in Q numbering or None) of an initial-condition dictionary, on the
+    device; shared by the IPCS and the monolithic mirrors (source/ns_solver_base.py:1123-1171)"""
+    sp = dev.spaces
+    v = initial_conditions["velocity"]
+    if isinstance(v, Expression):
+        u0 = dev.project(v, "V", v.degree)
+    else:
+        x = sp.node_coordinates()
+        if callable(v):
+            u0 = np.asarray(v(x), dtype=np.float64).reshape(len(x), sp.dim)
+        else:
+            assert len(v) == sp.dim
+            u0 = np.broadcast_to(np.asarray(v, dtype=np.float64), (len(x), sp.dim))
+        u0 = dev.upload(np.ascontiguousarray(u0).reshape(-1))
+    p0 = None
+    if "pressure" in initial_conditions:
+        p = initial_conditions["pressure"]
+        if isinstance(p, Expression):
+            p0 = dev.project(p, "Q", p.degree)
+        else:
+            xv = sp.mesh.coords
+            p0 = np.asarray(p(xv), dtype=np.float64).reshape(-1) if callable(p) else np.full(len(xv), float(p))
+            p0 = dev.upload(p0)
+    return u0, p0
+
+
 class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
@@ -195,27 +222,21 @@ class IPCSSolver(SolverBase):
                                   co["viscous_term"])
 
     def set_initial_conditions(self, initial_conditions):
-        """source/ns_solver_base.py:1123-1171 + source/ns_ipcs_solver.py:229-238: nodal data of
-        degree <= 2 (velocity) / 1 (pressure), for which dolfin's L2 projection is the identity."""
+        """source/ns_solver_base.py:1123-1171 + source/ns_ipcs_solver.py:229-238: ``dolfin.project`` of the initial
+        data into the velocity / pressure space, assigned to velocities[0], [1], pressure, old_pressure.
+        An ``Expression(fn, degree=k)`` is projected on the device (cell-wise P_k interpolant, exact right-hand
+        side, mass solve: ``Device.project``); constants are in the space, their projection is the constant; a bare
+        callable is taken as nodal data of degree <= 2 (velocity) / 1 (pressure), for which the projection is the
+        identity."""
         assert isinstance(initial_conditions, dict) and "velocity" in initial_conditions
         sp, dev = self.dev.spaces, self.dev
-        v = initial_conditions["velocity"]
-        x = sp.node_coordinates()
-        if callable(v):
-            u0 = np.asarray(v(x), dtype=np.float64).reshape(len(x), sp.dim)
-        else:
-            assert len(v) == sp.dim
-            u0 = np.broadcast_to(np.asarray(v, dtype=np.float64), (len(x), sp.dim))
-        u0 = dev.upload(np.ascontiguousarray(u0).reshape(-1))
+        u0, p0 = initial_fields(dev, initial_conditions)
         self._velocities[0].copy_(u0)
         self._velocities[1].copy_(u0)
-        if "pressure" in initial_conditions:
-            p = initial_conditions["pressure"]
-            xv = sp.mesh.coords
-            p0 = np.asarray(p(xv), dtype=np.float64).reshape(-1) if callable(p) else np.full(len(xv), float(p))
-            p0 = dev.upload(p0)
+        if p0 is not None:
             self._pressure.copy_(p0)
             self._old_pressure.copy_(p0)
+        del sp
 
     # ---- one time step -------------------------------------------------------------------------
     def solve(self, upload_bcs=False):
@@ -342,8 +363,10 @@ class IPCSSolver(SolverBase):
         dev.scatter(self._v2w, self._velocities[0], self._w)
         dev.scatter(self._q2w, self._pressure, self._w)
         if hasattr(self, "_mean_pressure_value"):
+            # source/ns_solver_base.py:1190-1203, on the mixed copy like the reference: int p / int 1 from the P1
+            # mass weights, then p - shift (a constant shift of a P1 function IS its L2 projection)
             shift = self.mean_pressure() - self._mean_pressure_value
-            self._w[sp.dim * sp.n_nodes:] -= shift
+            dev.shift(self._w[sp.dim * sp.n_nodes:], shift)
         return self._w
 
     def checksums(self, lagged=False):
@@ -358,9 +381,11 @@ class IPCSSolver(SolverBase):
         return {"u_l2": float(np.sqrt(dev.dot(u, u))), "p_minus_mean_l2": float(np.sqrt(max(pp - ps * ps / nq, 0.0)))}
 
     def mean_pressure(self):
-        dev = self.dev
-        if not hasattr(self, "_p1_weights"):
-            self._p1_weights = dev.empty(self._nQ_own)
-            dev.assemble_p1_mass(L.VEC, w=self._p1_weights)
-            self._volume = dev.sum(self._p1_weights)
-        return dev.dot(self._p1_weights, self._pressure) / self._volume
+        """int p dx / int 1 dx (source/ns_solver_base.py:1194)"""
+        integral, volume = self.dev.p1_integral(self._pressure)
+        return integral / volume
+
+    def cfl_number(self, step_size=None):
+        """``InstationaryProblem._compute_cfl_number`` (source/ns_problem.py:554-587) for the current velocity"""
+        k = self._time_stepping.get_next_step_size() if step_size is None else step_size
+        return self.dev.cfl(self._velocities[0], k)

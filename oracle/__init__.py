@@ -42,4 +42,4 @@ sorting), so that it shares no closed-form tables or code with the CUDA path it
 checks.
 """
 
-from . import mesh, fem, dofmap, forms, bc, solvers, native, functionals  # noqa: F401
+from . import mesh, fem, dofmap, forms, bc, solvers, native, functionals, projection  # noqa: F401

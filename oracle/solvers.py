@@ -83,6 +83,18 @@ def project_Q(asm, f):
     return lu_solve(M, M @ g)
 
 
+def _initial_fields(asm, velocity, pressure, degree):
+    from . import projection
+    d = asm.sp.dim
+    vel = velocity if callable(velocity) else (lambda x: np.broadcast_to(np.asarray(velocity, float), (len(x), d)))
+    u0 = project_V(asm, vel) if degree is None else projection.project(asm, vel, "V", degree)
+    p0 = None
+    if pressure is not None:
+        prs = pressure if callable(pressure) else (lambda x: np.full(len(x), float(pressure)))
+        p0 = project_Q(asm, prs) if degree is None else projection.project(asm, prs, "Q", degree)
+    return u0, p0
+
+
 class _Base:
     def __init__(self, mesh, Re=None, coefficients=None, assembler="numpy", threads=None):
         self.mesh = mesh
@@ -126,16 +138,20 @@ class IPCSOracle(_Base):
         pb = obc.dirichlet_values(self.sp, [("Q", m, "p", bind(v)) for m, v in self.pressure_bcs])
         return vb, pb
 
-    def set_initial_conditions(self, velocity, pressure=None):
-        u0 = project_V(self.asm, velocity) if callable(velocity) else \
-            project_V(self.asm, lambda x: np.broadcast_to(np.asarray(velocity, float), (len(x), self.sp.dim)))
+    def set_initial_conditions(self, velocity, pressure=None, degree=None):
+        """``degree``: the degree of the dolfin Expression (App. A.7: interpolated into P_degree per cell, then
+        L2-projected); None = nodal data of the space's own degree"""
+        u0, p0 = _initial_fields(self.asm, velocity, pressure, degree)
         self.velocities[0][:] = u0
         self.velocities[1][:] = u0
-        if pressure is not None:
-            p0 = project_Q(self.asm, pressure if callable(pressure)
-                           else (lambda x: np.full(len(x), float(pressure))))
+        if p0 is not None:
             self.pressure[:] = p0
             self.old_pressure[:] = p0
+
+    def solution_pressure(self, mean_value=None):
+        """pressure part of ``solution`` incl. the mean-value shift of source/ns_solver_base.py:1190-1203"""
+        from . import projection
+        return self.pressure if mean_value is None else projection.mean_pressure_shift(self.asm, self.pressure, mean_value)
 
     def solve(self, alpha, k, t_next):
         """One ``_solve_time_step`` (source/ns_ipcs_solver.py:198-208)."""
@@ -221,16 +237,12 @@ class BDFOracle(_Base):
         lst += [("W", m, "p", bind(v)) for m, v in self.pressure_bcs]
         return obc.dirichlet_values(self.sp, lst)
 
-    def set_initial_conditions(self, velocity, pressure=None):
+    def set_initial_conditions(self, velocity, pressure=None, degree=None):
         s = self.sp
-        u0 = project_V(self.asm, velocity) if callable(velocity) else \
-            project_V(self.asm, lambda x: np.broadcast_to(np.asarray(velocity, float), (len(x), s.dim)))
+        u0, p0 = _initial_fields(self.asm, velocity, pressure, degree)
         for w in self.solutions[:2]:
             w[s.V_to_W] = u0
-        if pressure is not None:
-            p0 = project_Q(self.asm, pressure if callable(pressure)
-                           else (lambda x: np.full(len(x), float(pressure))))
-            for w in self.solutions[:2]:
+            if p0 is not None:
                 w[s.Q_to_W] = p0
 
     def solve(self, alpha, k, t_next, pin_pressure=False):

@@ -86,8 +86,12 @@ def _tgv(Re=100.0, gamma=2.0 * np.pi):
     return u, p
 
 
-def _run_tgv(n, nsteps, dt):
+def _run_tgv(n, nsteps, dt, with_oracle=False):
+    """IPCS on the Taylor-Green vortex exactly as demo/taylor_green_vortex.py:61-84 + convergence_test set it up, with
+    Dirichlet velocity from the exact solution on all four sides instead of the periodic constraint ("periodic-free",
+    BASELINE configs[2]): degree-3 Expressions as initial data (L2-projected), mean-value pressure 0."""
     import nsb200
+    import oracle
     V, P = nsb200.VelocityBCType, nsb200.PressureBCType
     u_ex, p_ex = _tgv()
     mesh, markers = nsb200.hyper_cube(2, n)
@@ -96,32 +100,44 @@ def _run_tgv(n, nsteps, dt):
     solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / 100.0))
     solver.set_boundary_conditions([(V.function, w, nsb200.Expression(u_ex)) for w in (1, 2, 3, 4)] +
                                    [(P.mean_value, None, 0.0)])
-    solver.set_initial_conditions(dict(velocity=lambda x: u_ex(x, 0.0), pressure=lambda x: p_ex(x, 0.0)))
+    solver.set_initial_conditions(dict(velocity=nsb200.Expression(u_ex, degree=3), pressure=nsb200.Expression(p_ex, degree=3)))
+    orc = None
+    if with_oracle:
+        orc = oracle.solvers.IPCSOracle(oracle.mesh.hyper_cube(2, n), 100.0, [(w, None, u_ex) for w in (1, 2, 3, 4)], [])
+        orc.set_initial_conditions(lambda x: u_ex(x, 0.0), lambda x: p_ex(x, 0.0), degree=3)
     for _ in range(nsteps):
         ts.update_coefficients()
         solver.solve()
+        if orc is not None:
+            a = list(ts.coefficients(1)) + [0.0]
+            orc.solve(tuple(a[:3]), ts.get_next_step_size(), ts.next_time)
+            orc.advance_time()
         ts.advance_time()
         solver.advance_time()
-    x = solver.dev.spaces.node_coordinates()
-    t = nsteps * dt
-    u = solver._velocities[1].cpu().numpy().reshape(-1, 2)
-    return float(np.abs(u - u_ex(x, t)).max()), solver
+    return solver, orc, nsteps * dt
 
 
-def test_c3_taylor_green_ipcs_converges(built_library):
-    """configs[2]: Taylor-Green vortex with the IPCS scheme, Dirichlet velocity from the exact solution on
-    all four sides ("periodic-free"), mean-value pressure: known-answer test -- the nodal max-norm
-    velocity error against the exact solution drops at least 2.5x per mesh halving at fixed small dt (observed
-    2.98x: the projection scheme's boundary splitting error rides on top of the P2 interpolation error)."""
-    e8, _ = _run_tgv(8, 4, 2.5e-4)
-    e16, solver = _run_tgv(16, 4, 2.5e-4)
+def test_c3_taylor_green_ipcs_matches_oracle_and_converges(built_library):
+    """configs[2]: (i) parity -- 3 IPCS steps from the projected degree-3 initial data agree with the LU oracle to 1e-8
+    (velocity, and the mean-value-shifted pressure of ``solution``), equal Newton counts; (ii) known-answer -- the
+    ``errornorm`` (dolfin definition, on the device) of the velocity against the exact solution drops at least 2.5x per
+    mesh halving at fixed small dt, and equals the oracle's errornorm of the oracle's field."""
+    from oracle import projection as opj
+    u_ex, p_ex = _tgv()
+    solver, orc, t = _run_tgv(16, 3, 2.5e-4, with_oracle=True)
+    osp = orc.sp
+    assert solver.newton_iterations == orc.newton_iterations
+    assert rel_max_err(solver._velocities[1].cpu().numpy(), orc.velocities[1]) < 1e-8
+    w = solver.solution.cpu().numpy()           # velocity + mean-value-shifted pressure of the last solve
+    assert rel_max_err(w[osp.Q_to_W], orc.solution_pressure(mean_value=0.0)) < 1e-8
+    assert abs(orc.asm.integral_Q(w[osp.Q_to_W])) < 1e-12 * orc.asm.volume()
+    e16 = solver.dev.errornorm(lambda x: u_ex(x, t), solver._velocities[1], "V")
+    assert abs(e16 - opj.errornorm(orc.asm, lambda x: u_ex(x, t), orc.velocities[1], "V")) < 1e-8 * e16
+    ep = solver.dev.errornorm(lambda x: p_ex(x, t), solver.dev.upload(w[osp.Q_to_W]), "Q")
+    assert ep < 0.05
+    s8, _, _ = _run_tgv(8, 3, 2.5e-4)
+    e8 = s8.dev.errornorm(lambda x: u_ex(x, t), s8._velocities[1], "V")
     assert e16 < 2e-3 and e8 / e16 > 2.5, (e8, e16)
-    # mean-value pressure condition (source/ns_solver_base.py:1190-1203) on the returned mixed solution
-    w = solver.solution
-    sp_ = solver.dev.spaces
-    pw = w[sp_.dim * sp_.n_nodes:]
-    mean = solver.dev.dot(solver._p1_weights, pw) / solver._volume
-    assert abs(mean) < 1e-12
 
 
 def test_c4_dfg_cylinder_drag_lift(built_library):

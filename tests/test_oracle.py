@@ -197,3 +197,48 @@ def test_stationary_oracle_cavity_converges():
     st.bc_dofs, st.bc_vals = st.bc_dofs[order], st.bc_vals[order]
     r = st.solve()
     assert r <= 1e-10 and st.newton_iterations[1] <= 10
+
+
+def test_c_krylov_matches_numpy_krylov():
+    """the C/OpenMP Jacobi-GMRES / CG of the timed CPU arm (nsoracle.c) against their numpy statement"""
+    from oracle import krylov as okr
+    om = oracle.mesh.hyper_rectangle((0.0, 0.0, 0.0), (1.0, 1.0, 1.0), (3, 3, 3))
+    asm = oracle.forms.Assembler(oracle.dofmap.Spaces(om))
+    rng = np.random.default_rng(5)
+    u = rng.uniform(-1, 1, asm.sp.ndofs_V)
+    J = asm.ipcs_momentum_jacobian(u, 1.5, 1e-2, 1.0, 0.01)
+    b = rng.uniform(-1, 1, asm.sp.ndofs_V)
+    x0, n0 = okr.gmres(J, b, rtol=1e-12)
+    x1, n1 = okr.gmres_c(J, b, rtol=1e-12)
+    assert n0 == n1 and np.abs(x0 - x1).max() < 1e-10 * np.abs(x0).max()
+    L = asm.poisson_matrix()
+    bq = rng.uniform(-1, 1, asm.sp.ndofs_Q)
+    y0, m0 = okr.pcg(L, bq, rtol=1e-12, nullspace=True)
+    y1, m1 = okr.pcg_c(L, bq, rtol=1e-12, nullspace=True)
+    assert abs(m0 - m1) <= 1 and np.abs(y0 - y1).max() < 1e-9 * np.abs(y0).max()
+
+
+def test_lagrange_tables_of_the_product_against_oracle_elements():
+    """navierstokes-with-fenics_b200/lagrange.py (exact rational tables, product-formula bases) against the oracle's
+    independent construction (Vandermonde inversion + Gauss-Jacobi quadrature)"""
+    import nsb200  # noqa: F401
+    from nsb200 import lagrange as lg
+    from oracle import projection as opj
+    for d in (2, 3):
+        for k in (1, 2, 3):
+            el = opj.LagrangeElement(d, k)
+            qp, qw = oracle.fem.simplex_quadrature(d, k + 2)
+            # same space: the two bases span the same polynomials -> mass tensors agree after matching the nodes
+            pts = lg.lattice_points(d, k)
+            match = [int(np.argmin(np.abs(el.nodes - p).sum(axis=1))) for p in pts]
+            psi = el.tabulate(qp)[:, match]
+            for space, tab in (("P2", oracle.fem.tabulate_p2), ("P1", oracle.fem.tabulate_p1)):
+                ref = np.einsum("q,qI,qJ->IJ", qw, tab(qp)[0], psi)
+                assert np.abs(lg.cross_mass(d, space, k) - ref).max() < 1e-14
+        X, W = lg.simplex_rule(d, 10)
+        assert abs(W.sum() - (0.5 if d == 2 else 1.0 / 6.0)) < 1e-15
+        Xf, Wf = lg.fiat_default_rule_degree4(d)
+        assert abs(Wf.sum() - W.sum()) < 1e-12
+        # degree-4 exactness of the FIAT default rule: x0^2 x1^2
+        ex = np.einsum("q,q->", W, X[:, 0] ** 2 * X[:, 1] ** 2)
+        assert abs(np.einsum("q,q->", Wf, Xf[:, 0] ** 2 * Xf[:, 1] ** 2) - ex) < 1e-12
