@@ -68,7 +68,8 @@ typedef struct nsb_pattern_builder nsb_pattern_builder;
 #define NSB_T_VEC 8          /* vector ops, history shift, gather/scatter (K13, K15) */
 #define NSB_T_COMM 9         /* halo pack + NCCL send/recv, NCCL all-reduce (K14)    */
 #define NSB_T_SPMV_BSR32 10  /* BSR-d SpMV on the single-precision value copy (Chebyshev preconditioner only) */
-#define NSB_T_NCLASS 11
+#define NSB_T_CG_FUSED 11    /* whole CG solves as one persistent cooperative kernel (csrc/cg_persistent.cu) */
+#define NSB_T_NCLASS 12
 
 /* index spaces with a halo plan (nsb_set_halo, nsb_matrix.halo) */
 #define NSB_HALO_NONE 0

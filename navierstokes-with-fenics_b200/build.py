@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnsb200.so")
 STAMP = os.path.join(HERE, ".libnsb200.stamp")
-SOURCES = ["setup_host.cu", "context.cu", "assemble.cu", "assemble_jac.cu", "assemble_res.cu", "linalg.cu", "krylov.cu", "comm.cu", "direct.cu", "functionals.cu", "project.cu"]
+SOURCES = ["setup_host.cu", "context.cu", "assemble.cu", "assemble_jac.cu", "assemble_res.cu", "linalg.cu", "krylov.cu", "comm.cu", "direct.cu", "functionals.cu", "project.cu", "cg_persistent.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "--use_fast_math=false", "-Xcompiler", "-fPIC,-fopenmp,-O3", "-shared", "-lgomp", "-ldl"]
 

@@ -1,0 +1,316 @@
+// cg_persistent.cu -- the whole preconditioned CG solve of a scalar CSR system as ONE persistent cooperative
+// kernel (K10 + K11 + K12 fused): the pressure Poisson problem of source/ns_ipcs_solver.py:166-171,205.
+//
+// Why: at C5 that system has 405 224 rows and a 79.5 MB operator -- it fits the 126 MB L2 of a B200 whole --
+// and a solve is ~80 CG iterations x (1 + 7 polynomial) SpMVs x a handful of vector kernels.  As separate
+// launches every SpMV costs 21-25 us against an L2-resident floor of a few us, and the ~1 200 launches per
+// solve bound the step (19 % of the step in `spmv_csr`, 12 % in `krylov_vec`).  Here one CTA per
+// SM owns a contiguous row range for the whole solve; the phases of an iteration are separated by
+// grid-wide barriers (cooperative launch), every inner product is a per-CTA partial + one barrier after which
+// each CTA sums the partials in CTA order (deterministic, bit-identical on every CTA, so the convergence
+// decision is uniform without a broadcast), the Chebyshev recurrence and all CG vector updates live in the
+// SpMV epilogues.  degree + 2 barriers per iteration, no host round trip before the solve ends.
+//
+// Memory-model notes: vectors written inside the kernel are read with ld.global.cg (L2, never a stale L1
+// line of another SM's data); the matrix, D^-1 and b are read-only for the kernel's lifetime and go through
+// the non-coherent path.
+#include <cooperative_groups.h>
+#include <math.h>
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+#define PCG_THREADS 1024
+#define PCG_LANES 4
+#define PCG_MAXDEG 32
+
+struct pcg_params {
+    int32_t nrows;
+    const int32_t* rowptr;
+    const int32_t* col;
+    const double* vals;
+    const uint8_t* mask;
+    const double* dinv;
+    const double* b;
+    double *x, *r, *z, *p, *q, *rc, *d0, *d1;
+    double* partials;          // [6][gridDim.x]
+    double* out;               // [4]: iterations, ||r||^2, ||b||^2
+    double rtol, atol, n_all, inv_theta;
+    int32_t maxit, nullspace, degree;     // degree 0: Jacobi; >= 2: Chebyshev polynomial with degree terms
+    double ca[PCG_MAXDEG], cb[PCG_MAXDEG];
+};
+
+namespace {
+
+__device__ __forceinline__ double ldv(const double* p) { return __ldcg(p); }
+
+// per-CTA partials -> barrier -> every CTA sums all partials in CTA order
+template <int NV>
+__device__ __forceinline__ void grid_reduce(cg::grid_group& grid, double (&v)[NV], double* slots, double* smem) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    constexpr int NW = PCG_THREADS / 32;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = warp_sum(v[i]);
+    __syncthreads();                       // smem reuse
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) smem[i * NW + w] = v[i];
+    }
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            double s = lane < NW ? smem[i * NW + lane] : 0.0;
+            s = warp_sum(s);
+            if (lane == 0) slots[(size_t)i * gridDim.x + blockIdx.x] = s;
+        }
+    }
+    grid.sync();
+    if (w == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            double s = 0.0;
+            for (int j = lane; j < (int)gridDim.x; j += 32) s += ldv(slots + (size_t)i * gridDim.x + j);
+            s = warp_sum(s);
+            if (lane == 0) smem[NV * NW + i] = s;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = smem[NV * NW + i];
+}
+
+// (A x)_row by PCG_LANES cooperating lanes; the result is valid in every lane of the group.  Every lane of the
+// warp calls it (row >= hi: contributes nothing) so that the shuffles of the group sum are warp-uniform.
+__device__ __forceinline__ double row_dot(const pcg_params& P, int32_t row, int32_t hi, int lane, const double* x) {
+    double acc = 0.0;
+    if (row < hi) {
+        const int32_t end = __ldg(P.rowptr + row + 1);
+        constexpr int U = 4;
+        for (int32_t s = __ldg(P.rowptr + row) + lane; s < end; s += PCG_LANES * U) {
+            double v[U];
+            int32_t cn[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int32_t ss = s + u * PCG_LANES;
+                const bool ok = ss < end;
+                v[u] = ok ? __ldg(P.vals + ss) : 0.0;
+                cn[u] = ok ? __ldg(P.col + ss) : row;
+            }
+            double xv[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) xv[u] = ldv(x + cn[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) acc += v[u] * xv[u];
+        }
+    }
+    __syncwarp();
+    return group_sum<PCG_LANES>(acc);       // one call site for the whole warp
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_params P) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ double smem[3 * (PCG_THREADS / 32) + 4];
+    const int32_t n = P.nrows;
+    const int32_t per = (n + (int32_t)gridDim.x - 1) / (int32_t)gridDim.x;
+    const int32_t lo = min(n, (int32_t)blockIdx.x * per), hi = min(n, lo + per);
+    const int lane = threadIdx.x % PCG_LANES, grp = threadIdx.x / PCG_LANES;
+    constexpr int GROUPS = PCG_THREADS / PCG_LANES;
+    double* slot_a = P.partials;                       // 3 values
+    double* slot_b = P.partials + 3 * (size_t)gridDim.x;   // 3 values (alternates with slot_a)
+    const bool cheb = P.degree >= 2;
+
+    // ---- zero-mean projection of the right-hand side (constant null space) --------------------------
+    double shift = 0.0;
+    if (P.nullspace) {
+        double s[1] = {0.0};
+        for (int32_t i = lo + threadIdx.x; i < hi; i += PCG_THREADS) s[0] += __ldg(P.b + i);
+        grid_reduce<1>(grid, s, slot_a, smem);
+        shift = s[0] / P.n_all;
+    }
+    // ---- r = (b - shift) - A x ; preconditioner start for the first iteration --------------------------
+    double red[3] = {0.0, 0.0, 0.0};                   // rr, bb, rz (Jacobi)
+    for (int32_t row = lo + grp; row - grp < hi; row += GROUPS) {
+        double v = row_dot(P, row, hi, lane, P.x);
+        if (lane == 0 && row < hi) {
+            if (P.mask != nullptr && P.mask[row]) v = ldv(P.x + row);
+            const double bi = __ldg(P.b + row) - shift;
+            const double ri = bi - v;
+            P.r[row] = ri;
+            red[0] += ri * ri;
+            red[1] += bi * bi;
+            const double di = __ldg(P.dinv + row) * ri;
+            if (cheb) {
+                P.rc[row] = di;
+                const double d = di * P.inv_theta;
+                P.d0[row] = d;
+                P.z[row] = d;
+            } else {
+                P.z[row] = di;
+                red[2] += ri * di;
+            }
+        }
+    }
+    grid_reduce<3>(grid, red, slot_b, smem);
+    double rr = red[0];
+    const double bb = red[1];
+    double rz_next = red[2];
+    const double tol = fmax(P.rtol * sqrt(bb), P.atol);
+    const double tol2 = tol * tol;
+    double rz_old = 0.0;
+    int it = 0;
+    while (rr > tol2 && it < P.maxit) {
+        double rz;
+        if (cheb) {
+            // z = p_degree(D^-1 A) D^-1 r : degree-1 SpMVs, each with the recurrence in its epilogue
+            double* dold = P.d0;
+            double* dnew = P.d1;
+            double s[1] = {0.0};
+            for (int k = 1; k < P.degree; ++k) {
+                const double a = P.ca[k], bcoef = P.cb[k];
+                const bool last = k == P.degree - 1;
+                for (int32_t row = lo + grp; row - grp < hi; row += GROUPS) {
+                    double v = row_dot(P, row, hi, lane, dold);
+                    if (lane == 0 && row < hi) {
+                        const double dk = ldv(dold + row);
+                        if (P.mask != nullptr && P.mask[row]) v = dk;
+                        const double rci = ldv(P.rc + row) - __ldg(P.dinv + row) * v;
+                        const double dn = a * dk + bcoef * rci;
+                        const double zi = ldv(P.z + row) + dn;
+                        P.rc[row] = rci;
+                        dnew[row] = dn;
+                        P.z[row] = zi;
+                        if (last) s[0] += ldv(P.r + row) * zi;
+                    }
+                }
+                if (!last) grid.sync();
+                double* t = dold; dold = dnew; dnew = t;
+            }
+            grid_reduce<1>(grid, s, slot_a, smem);
+            rz = s[0];
+        } else {
+            rz = rz_next;
+        }
+        // p = z + beta p
+        const double beta = (it == 0 || rz_old == 0.0) ? 0.0 : rz / rz_old;
+        for (int32_t i = lo + threadIdx.x; i < hi; i += PCG_THREADS) {
+            const double zi = ldv(P.z + i);
+            P.p[i] = it == 0 ? zi : zi + beta * ldv(P.p + i);
+        }
+        grid.sync();
+        // q = A p ; p.q
+        double s1[1] = {0.0};
+        for (int32_t row = lo + grp; row - grp < hi; row += GROUPS) {
+            double v = row_dot(P, row, hi, lane, P.p);
+            if (lane == 0 && row < hi) {
+                const double pi = ldv(P.p + row);
+                if (P.mask != nullptr && P.mask[row]) v = pi;
+                P.q[row] = v;
+                s1[0] += pi * v;
+            }
+        }
+        grid_reduce<1>(grid, s1, slot_b, smem);
+        const double pq = s1[0];
+        const double alpha = pq != 0.0 ? rz / pq : 0.0;
+        // x += alpha p ; r -= alpha q ; r.r ; preconditioner start of the next iteration
+        double s2[2] = {0.0, 0.0};
+        for (int32_t i = lo + threadIdx.x; i < hi; i += PCG_THREADS) {
+            P.x[i] = ldv(P.x + i) + alpha * ldv(P.p + i);
+            const double ri = ldv(P.r + i) - alpha * ldv(P.q + i);
+            P.r[i] = ri;
+            s2[0] += ri * ri;
+            const double di = __ldg(P.dinv + i) * ri;
+            if (cheb) {
+                P.rc[i] = di;
+                const double d = di * P.inv_theta;
+                P.d0[i] = d;
+                P.z[i] = d;
+            } else {
+                P.z[i] = di;
+                s2[1] += ri * di;
+            }
+        }
+        grid_reduce<2>(grid, s2, slot_a, smem);
+        rr = s2[0];
+        rz_next = s2[1];
+        rz_old = rz;
+        ++it;
+        if (!(rr == rr)) break;            // NaN: uniform on every CTA
+    }
+    if (P.nullspace) {
+        double s[1] = {0.0};
+        for (int32_t i = lo + threadIdx.x; i < hi; i += PCG_THREADS) s[0] += ldv(P.x + i);
+        grid_reduce<1>(grid, s, slot_b, smem);
+        const double mean = s[0] / P.n_all;
+        for (int32_t i = lo + threadIdx.x; i < hi; i += PCG_THREADS) P.x[i] = ldv(P.x + i) - mean;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        P.out[0] = (double)it;
+        P.out[1] = rr;
+        P.out[2] = bb;
+    }
+}
+
+// 0 = solved (or failed to converge: status via the outputs), 1 = not applicable (caller keeps the multi-kernel
+// path), -1 = error.  work: 7 n doubles (nsb_cg_workspace_doubles).
+int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x, double rtol,
+                      double atol, int32_t maxit, int32_t nullspace, double* work, int32_t* iters_out, double* resid_out,
+                      cudaStream_t st) {
+    if (A->kind != NSB_CSR || A->bs != 1) return 1;
+    if (ctx->nranks > 1 && A->halo != NSB_HALO_NONE) return 1;           // partitioned operator: needs halo exchanges
+    if (!(M->kind == NSB_PC_JACOBI || (M->kind == NSB_PC_CHEBYSHEV && M->degree >= 2 && M->degree <= PCG_MAXDEG))) return 1;
+    static int coop = -1, per_sm = 0;
+    if (coop < 0) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, ctx->device);
+        coop = v;
+        if (coop) {
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_persistent, PCG_THREADS, 0) != cudaSuccess) per_sm = 0;
+        }
+    }
+    if (!coop || per_sm < 1) return 1;
+    const int64_t n = A->nrows;
+    int grid = ctx->sm_count;                       // one CTA per SM: the barrier cost grows with the CTA count
+    const int64_t need = (n + 255) / 256;           // at least 256 rows per CTA
+    if (grid > need) grid = (int)(need < 1 ? 1 : need);
+    if (6 * (int64_t)grid > NSB_MAX_PARTIALS * 8) return 1;
+    pcg_params P;
+    memset(&P, 0, sizeof P);
+    P.nrows = A->nrows; P.rowptr = A->rowptr; P.col = A->col; P.vals = A->vals; P.mask = A->bc_mask;
+    P.dinv = M->inv_diag; P.b = b; P.x = x;
+    P.r = work; P.z = work + n; P.p = work + 2 * n; P.q = work + 3 * n; P.rc = work + 4 * n; P.d0 = work + 5 * n; P.d1 = work + 6 * n;
+    P.partials = ctx->d_partials;
+    P.out = ctx->d_scalars;
+    P.rtol = rtol; P.atol = atol; P.maxit = maxit; P.nullspace = nullspace;
+    P.n_all = (double)n;
+    P.degree = M->kind == NSB_PC_CHEBYSHEV ? M->degree : 0;
+    if (P.degree) {
+        const double theta = 0.5 * (M->lambda_max + M->lambda_min), delta = 0.5 * (M->lambda_max - M->lambda_min);
+        const double sigma1 = theta / delta;
+        double rho_old = 1.0 / sigma1;
+        P.inv_theta = 1.0 / theta;
+        for (int k = 1; k < P.degree; ++k) {
+            const double rho = 1.0 / (2.0 * sigma1 - rho_old);
+            P.ca[k] = rho * rho_old;
+            P.cb[k] = 2.0 * rho / delta;
+            rho_old = rho;
+        }
+    }
+    void* args[] = {(void*)&P};
+    {
+        NSB_TIMED(ctx, NSB_T_CG_FUSED, st);
+        NSB_CUDA(ctx, cudaLaunchCooperativeKernel((const void*)k_pcg_persistent, dim3(grid), dim3(PCG_THREADS), args, 0, st));
+    }
+    NSB_LAUNCH_CHECK(ctx, "k_pcg_persistent");
+    NSB_CUDA(ctx, cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(double) * 3, cudaMemcpyDeviceToHost, st));
+    NSB_CUDA(ctx, cudaStreamSynchronize(st));
+    const int it = (int)ctx->h_scalars[0];
+    const double rnorm = sqrt(ctx->h_scalars[1]), bnorm = sqrt(ctx->h_scalars[2]);
+    if (iters_out) *iters_out = it;
+    if (resid_out) *resid_out = rnorm;
+    if (!(rnorm == rnorm)) return nsb_fail(ctx, "CG breakdown: residual is NaN%s%s");
+    if (rnorm > fmax(rtol * bnorm, atol)) return nsb_fail(ctx, "CG did not converge within the iteration limit%s%s");
+    return 0;
+}

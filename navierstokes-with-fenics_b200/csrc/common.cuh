@@ -128,6 +128,7 @@ struct nsb_ctx {
     bool ar_ready = false;
     nsb_halo halo[3];                 // [NSB_HALO_NODES], [NSB_HALO_VERTS]; [0] unused
     int sm_count = 148;
+    bool no_persistent_cg = false;    // NSB_CG=multi: keep the multi-kernel CG (A/B measurements)
     std::string err;
     // mesh
     int32_t dim = 0, nverts = 0, ncells = 0, nnodes = 0;
@@ -164,6 +165,10 @@ struct nsb_ctx {
 };
 
 int nsb_timer_flush(nsb_ctx* ctx);
+// cg_persistent.cu: 0 = solved, 1 = not applicable (caller keeps the multi-kernel path), -1 = error
+int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x, double rtol,
+                      double atol, int32_t maxit, int32_t nullspace, double* work, int32_t* iters_out, double* resid_out,
+                      cudaStream_t st);
 // comm.cu: no-ops (return 0) on a single rank
 int nsb_allreduce_sum(nsb_ctx* ctx, double* dev_buf, int count, cudaStream_t st);
 int nsb_comm_destroy(nsb_ctx* ctx);

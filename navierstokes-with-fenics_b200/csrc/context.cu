@@ -1,5 +1,6 @@
 // context.cu -- life cycle of nsb_ctx, registration of device-resident mesh / pattern arrays,
 // Dirichlet-row kernels (K9) and the FP64 peak probe.
+#include <stdlib.h>
 #include "common.cuh"
 
 extern "C" int nsb_version(void) { return NSB_VERSION; }
@@ -22,6 +23,10 @@ extern "C" int nsb_create(nsb_ctx** out, int device) {
     cudaDeviceProp prop;
     NSB_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
+    {
+        const char* e = getenv("NSB_CG");
+        ctx->no_persistent_cg = e && !strcmp(e, "multi");
+    }
     NSB_CUDA(ctx, cudaMalloc(&ctx->d_partials, sizeof(double) * NSB_MAX_PARTIALS * 8));
     NSB_CUDA(ctx, cudaMalloc(&ctx->d_scalars, sizeof(double) * 256));
     NSB_CUDA(ctx, cudaMalloc(&ctx->d_counter, sizeof(unsigned int) * 4));

@@ -394,6 +394,11 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     NSB_REQUIRE(ctx, A && b && x && work, "null argument");
     if (check_pc(ctx, M)) return -1;
     cudaStream_t st = (cudaStream_t)stream;
+    // scalar systems without halo exchanges: the whole solve is one persistent cooperative kernel
+    if (!ctx->no_persistent_cg) {
+        const int pst = nsb_cg_persistent(ctx, A, M, b, x, rtol, atol, maxit, nullspace, work, iters_out, resid_out, st);
+        if (pst <= 0) return pst;
+    }
     const int64_t n = (int64_t)A->nrows * A->bs;
     double *r = work, *z = work + n, *p = work + 2 * n, *q = work + 3 * n, *scratch = work + 4 * n;
     double* ds = ctx->d_scalars;
