@@ -334,23 +334,23 @@ def run_nsb200(args):
         #                                     one-time pinned allocations and map uploads are not inside a timed region
     sampler = ClockSampler(local)
     sampler.start()
-    l0 = dev.launch_count()
+    l0 = solver.launch_count()
     state = solver.get_state()              # all three legs advance the SAME K time steps
     # leg 1, the headline: CUDA-event pairs only around the large kernels (assembly, velocity SpMVs: ~170 launch
     # groups per step) -- the roofline numbers come from here
-    dev.timer_enable(True, classes=BIG_CLASSES)
+    solver.timer_enable(True, classes=BIG_CLASSES)
     ms, _, _ = timed(args.steps, False)
-    big = dev.timer_report()
-    dev.timer_enable(False)
-    launches = dev.launch_count() - l0
+    big = solver.timer_report()
+    solver.timer_enable(False)
+    launches = solver.launch_count() - l0
     clocks = sampler.result()
     # leg 2, the breakdown: every launch group of every class timed (an event pair costs about a microsecond on
     # each of the ~1400 small Krylov launches per step, so this leg is not the headline)
     solver.set_state(state)
-    dev.timer_enable(True)
+    solver.timer_enable(True)
     ms_instrumented, _, _ = timed(args.steps, False)
-    classes = dev.timer_report()
-    dev.timer_enable(False)
+    classes = solver.timer_report()
+    solver.timer_enable(False)
     # leg 3, end to end through the public API: host Dirichlet tables in, mixed solution out, every step
     solver.set_state(state)
     del state

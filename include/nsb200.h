@@ -331,6 +331,13 @@ int nsb_set_halo(nsb_ctx* ctx, int32_t which, int32_t n_owned, int32_t n_ghost, 
 int nsb_halo_exchange(nsb_ctx* ctx, int32_t which, int32_t bs, const double* x, double* ghost_dst,
                       void* stream);
 
+/* buf += the same buffer of every other rank (in place, FP64 sum; no-op on one rank): the one exchange of the
+ * REPLICATED pressure solve -- every rank scatters its owned right-hand-side entries into a zeroed global
+ * vector, all-reduces it (every entry has exactly one non-zero contributor: exact and bit-identical on all
+ * ranks) and then solves the whole 405 k-row system itself with the persistent CG kernel, with no halo
+ * exchange and no all-reduce inside the solve. */
+int nsb_allreduce(nsb_ctx* ctx, double* buf_dev, int64_t count, void* stream);
+
 /* Halo exchange and scalar all-reduce through NVLink peer memory instead of NCCL (optional, after
  * nsb_comm_init / nsb_set_halo; single node, CUDA IPC).
  * nsb_p2p_export allocates this rank's IPC-shared block for `which` and returns its

@@ -101,6 +101,7 @@ PROTOTYPES = {
     "nsb_p2p_connect": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp]),
     "nsb_p2p_status": (C.c_int, [vp, c_i32p]),
     "nsb_p2p_disconnect": (C.c_int, [vp]),
+    "nsb_allreduce": (C.c_int, [vp, vp, C.c_int64, vp]),
     "nsb_halo_exchange": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp]),
     "nsb_timer_enable": (C.c_int, [vp, C.c_int32]),
     "nsb_timer_report": (C.c_int, [vp, c_f64p, c_i64p]),

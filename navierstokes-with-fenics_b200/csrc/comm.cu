@@ -163,6 +163,11 @@ extern "C" int nsb_halo_exchange(nsb_ctx* ctx, int32_t which, int32_t bs, const 
     return 0;
 }
 
+extern "C" int nsb_allreduce(nsb_ctx* ctx, double* buf_dev, int64_t count, void* stream) {
+    NSB_REQUIRE(ctx, ctx && buf_dev && count >= 0 && count < (int64_t)1 << 31, "bad arguments");
+    return nsb_allreduce_sum(ctx, buf_dev, (int)count, (cudaStream_t)stream);
+}
+
 int nsb_allreduce_sum(nsb_ctx* ctx, double* buf, int count, cudaStream_t st) {
     if (ctx->nranks <= 1) return 0;
     if (ctx->ar_ready && count <= NSB_AR_MAX) return p2p_allreduce(ctx, buf, count, st);

@@ -90,13 +90,16 @@ class Pattern:
 class Device:
     """One GPU, one mesh.  Raises if CUDA or libnsb200.so is unavailable (no CPU fallback)."""
 
-    def __init__(self, mesh, device_index=0, mixed=False, partition=None, node_perm=None):
+    def __init__(self, mesh, device_index=0, mixed=False, partition=None, node_perm=None, patterns=None):
         """``partition`` (partition.Partition with finalized halo plans): this rank's share of a
         mesh-partitioned run; ``mesh`` is then ignored in favour of the partition's local mesh and
         torch.distributed must be initialised (it carries the NCCL id to the other ranks).
         ``node_perm`` (ingest mode): natural P2 node number (vertex v / N0 + e) -> the node
         number to use on the device, e.g. the one a real dolfin's re-ordered dofmap assigns; every map,
-        pattern and kernel then works in that numbering."""
+        pattern and kernel then works in that numbering.
+        ``patterns``: names of the patterns to build up front (default: "WW" if mixed else "P2P2", "P1P1"); a
+        device that only serves the pressure space (the replicated pressure solve of a partitioned run) passes
+        ("P1P1",) and gets no cell scratch."""
         if not torch.cuda.is_available():
             raise RuntimeError("nsb200 needs a CUDA device: there is no CPU fallback")
         self.lib = L.load()
@@ -121,16 +124,16 @@ class Device:
         self.cell_nodes = self.upload(sp.cell_nodes)
         self.check(self.lib.nsb_set_mesh(self.ctx, sp.dim, mesh.num_vertices, _ptr(self.coords), mesh.num_cells,
                                          _ptr(self.cell_verts), sp.n_nodes, _ptr(self.cell_nodes)))
-        self.scratch = self.empty(mesh.num_cells * sp.nloc2 * sp.dim)
-        self.check(self.lib.nsb_set_scratch(self.ctx, _ptr(self.scratch), self.scratch.numel()))
+        if patterns is None:
+            patterns = ("WW",) if mixed else ("P2P2", "P1P1")
+        if "P2P2" in patterns:
+            self.scratch = self.empty(mesh.num_cells * sp.nloc2 * sp.dim)
+            self.check(self.lib.nsb_set_scratch(self.ctx, _ptr(self.scratch), self.scratch.numel()))
         self.patterns = {}
         self.coef = None
         self._launch_hint = 0
-        if mixed:
-            self.pattern("WW")
-        else:
-            self.pattern("P2P2")
-            self.pattern("P1P1")
+        for name in patterns:
+            self.pattern(name)
 
     def __del__(self):
         try:
@@ -250,6 +253,12 @@ class Device:
         n_owned = self.n_owned_nodes if which == L.HALO_NODES else self.n_owned_verts
         ghost = C.c_void_p(x.data_ptr() + 8 * bs * n_owned)
         self.check(self.lib.nsb_halo_exchange(self.ctx, which, bs, _ptr(x), ghost, self.stream))
+
+    def allreduce(self, x):
+        """x += the same vector of every other rank, in place (no-op on one GPU)"""
+        if self.partition is None or self.partition.nranks == 1:
+            return
+        self.check(self.lib.nsb_allreduce(self.ctx, _ptr(x), x.numel(), self.stream))
 
     # ---- plumbing ---------------------------------------------------------------------------
     def check(self, status):

@@ -46,7 +46,7 @@ class IPCSSolver(SolverBase):
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
                  momentum_preconditioner="chebyshev", chebyshev_degree=8, chebyshev_ratio=30.0, partition=None,
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
-                 pressure_chebyshev_ratio=300.0):
+                 pressure_chebyshev_ratio=300.0, pressure_solve="auto"):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -104,6 +104,24 @@ class IPCSSolver(SolverBase):
         self._bQ, self._dinvQ = dev.empty(nQo), dev.empty(nQo)
         self._work = dev.empty(max(dev.lib.nsb_gmres_workspace_doubles(nVo, gmres_restart, 1 if self._pc_lowp else 0),
                                    dev.lib.nsb_cg_workspace_doubles(nVo)))
+        # Pressure problem on a partitioned mesh (405 k rows at C5, an operator that fits one GPU's
+        # L2): "replicated" = every rank all-reduces the right-hand side once and solves the WHOLE system itself with
+        # the persistent CG kernel -- no halo exchange, no all-reduce inside the solve, bit-identical on all ranks;
+        # "partitioned" = owned rows per rank, one halo exchange per SpMV and one all-reduce per inner product.
+        assert pressure_solve in ("auto", "replicated", "partitioned")
+        if pressure_solve == "auto":
+            pressure_solve = "replicated" if (partition is not None and partition.nranks > 1
+                                              and partition.verts.n_global <= 4_000_000) else "partitioned"
+        self._p_replicated = partition is not None and pressure_solve == "replicated"
+        if self._p_replicated:
+            self._pdev = pdev = Device(partition.global_mesh, device_index, patterns=("P1P1",))
+            nQg = pdev.spaces.ndofs_Q
+            self._A_lap_g = pdev.empty(pdev.patterns["P1P1"].nnz)
+            self._bQ_g, self._p_g, self._dinvQ_g = pdev.zeros(nQg), pdev.zeros(nQg), pdev.empty(nQg)
+            self._work_g = pdev.empty(pdev.lib.nsb_cg_workspace_doubles(nQg))
+            self._own_gid = dev.upload(partition.vert_gid[:nQo].astype(np.int32))     # owned local vertex -> global
+            self._loc_gid = dev.upload(partition.vert_gid.astype(np.int32))           # every local vertex -> global
+            self._p_g_stale = True
         self._pi_work = None
         self._have_constant = False
         self._bc_ready = False
@@ -132,6 +150,12 @@ class IPCSSolver(SolverBase):
         mQ = np.zeros(sp.ndofs_Q, dtype=np.uint8)
         mQ[pd] = 1
         self._maskV, self._maskQ = dev.upload(mV), dev.upload(mQ)
+        if self._p_replicated:
+            gsp = self._pdev.spaces
+            gd, gv = gsp.dirichlet_table(self._pressure_bcs, "Q")
+            mg = np.zeros(gsp.ndofs_Q, dtype=np.uint8)
+            mg[gd] = 1
+            self._pbc_dofs_g, self._pbc_vals_g, self._maskQ_g = dev.upload(gd), dev.upload(gv), dev.upload(mg)
         self._time_dependent_bcs = any(isinstance(v, Expression) for _, _, v in
                                        self._velocity_bcs + self._pressure_bcs)
         self._bc_ready = True
@@ -156,6 +180,9 @@ class IPCSSolver(SolverBase):
             if self._pbc_dofs.numel():
                 _, pv = sp.dirichlet_table(self._pressure_bcs, "Q")
                 self._pbc_host.copy_(torch.from_numpy(pv[self._pbc_keep]))
+            if self._p_replicated and self._pbc_dofs_g.numel():
+                _, gv = self._pdev.spaces.dirichlet_table(self._pressure_bcs, "Q")
+                self._pbc_vals_g.copy_(self.dev.upload(gv))
         self._vbc_vals.copy_(self._vbc_host, non_blocking=True)
         nbytes = self._vbc_host.numel() * 8
         if self._pbc_dofs.numel():
@@ -179,6 +206,8 @@ class IPCSSolver(SolverBase):
         self._intermediate_velocity.copy_(state["ustar"])
         self._pressure.copy_(state["pressure"])
         self._old_pressure.copy_(state["old_pressure"])
+        if self._p_replicated:
+            self._p_g_stale = True
         self._time_stepping.__dict__.update(copy.deepcopy(state["time_stepping"]))
 
     def fetch_solution(self, out=None):
@@ -201,12 +230,19 @@ class IPCSSolver(SolverBase):
         self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pressure_dirichlet else None)
         self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
         self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None, vals32=self._A_mom32, diag32=self._S_mom32)
-        dev.inv_diagonal(self._lap, self._dinvQ)
-        if self._p_pc[0] == "chebyshev":
-            lmax = 1.1 * dev.lambda_max(self._lap, self._dinvQ, iters=30, work=self._work)
-            self._pcQ = dev.precond(self._dinvQ, L.PC_CHEBYSHEV, self._p_pc[1], lmax / self._p_pc[2], lmax)
+        if self._p_replicated:          # the whole pressure operator on every rank (its own single-rank context)
+            pdev = self._pdev
+            pdev.assemble_poisson(L.MAT, A=self._A_lap_g)
+            self._lap_g = pdev.matrix("P1P1", self._A_lap_g, L.CSR, 1, self._maskQ_g if self._pressure_dirichlet else None)
+            lap, dinvQ, ldev = self._lap_g, self._dinvQ_g, pdev
         else:
-            self._pcQ = dev.precond(self._dinvQ)
+            lap, dinvQ, ldev = self._lap, self._dinvQ, dev
+        ldev.inv_diagonal(lap, dinvQ)
+        if self._p_pc[0] == "chebyshev":
+            lmax = 1.1 * ldev.lambda_max(lap, dinvQ, iters=30, work=self._work_g if self._p_replicated else self._work)
+            self._pcQ = ldev.precond(dinvQ, L.PC_CHEBYSHEV, self._p_pc[1], lmax / self._p_pc[2], lmax)
+        else:
+            self._pcQ = ldev.precond(dinvQ)
         dev.inv_diagonal(self._mass, self._dinv_mass)
         self._have_constant = True
 
@@ -236,6 +272,8 @@ class IPCSSolver(SolverBase):
         if p0 is not None:
             self._pressure.copy_(p0)
             self._old_pressure.copy_(p0)
+        if self._p_replicated:
+            self._p_g_stale = True
         del sp
 
     # ---- one time step -------------------------------------------------------------------------
@@ -318,14 +356,17 @@ class IPCSSolver(SolverBase):
         # (2) pressure Poisson
         a0 = self._alpha[0]
         dev.assemble_poisson(L.VEC, pn=self._old_pressure, ustar=ustar, b=self._bQ)
-        if self._pressure_dirichlet:
+        if self._p_replicated:
+            n_p = self._solve_pressure_replicated()
+        elif self._pressure_dirichlet:
             dev.bc_apply_vector(L.BC_LINEAR, self._bQ, self._pbc_dofs, self._pbc_vals)
             dev.bc_apply_vector(L.BC_LINEAR, self._pressure, self._pbc_dofs, self._pbc_vals)
             n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol, work=self._work)
+            dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
         else:
             n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol,
                             nullspace=True, work=self._work)
-        dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
+            dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
         # (3) velocity correction
         dev.assemble_correction(L.VEC, ustar=ustar, pnew=self._pressure, pold=self._old_pressure, b=self._bV)
         dev.bc_apply_vector(L.BC_LINEAR, self._bV, self._vbc_dofs, self._vbc_vals)
@@ -337,6 +378,46 @@ class IPCSSolver(SolverBase):
         dev.halo_status()
         self.krylov_iterations.append(dict(momentum=kry, pressure=n_p, correction=n_c))
         del a0
+
+    def _solve_pressure_replicated(self):
+        """every rank solves the whole pressure system: owned right-hand-side entries -> zeroed global vector ->
+        one all-reduce (each entry has a single non-zero contributor: exact) -> persistent CG on the global operator
+        (no exchange inside) -> local [owned | ghost] entries gathered back, ghosts included"""
+        dev, pdev = self.dev, self._pdev
+        if self._p_g_stale:              # initial guess = the current pressure field (initial conditions)
+            self._p_g.zero_()
+            dev.scatter(self._own_gid, self._pressure[:self._nQ_own], self._p_g)
+            dev.allreduce(self._p_g)
+            self._p_g_stale = False
+        self._bQ_g.zero_()
+        dev.scatter(self._own_gid, self._bQ, self._bQ_g)
+        dev.allreduce(self._bQ_g)
+        if self._pressure_dirichlet:
+            pdev.bc_apply_vector(L.BC_LINEAR, self._bQ_g, self._pbc_dofs_g, self._pbc_vals_g)
+            pdev.bc_apply_vector(L.BC_LINEAR, self._p_g, self._pbc_dofs_g, self._pbc_vals_g)
+        n_p, _ = pdev.cg(self._lap_g, self._pcQ, self._bQ_g, self._p_g, rtol=self._linear_rtol,
+                         nullspace=not self._pressure_dirichlet, work=self._work_g)
+        dev.gather(self._loc_gid, self._p_g, self._pressure)
+        return n_p
+
+    # ---- instrumentation over both contexts (the replicated pressure solve has its own) -------------
+    def _devices(self):
+        return [self.dev] + ([self._pdev] if self._p_replicated else [])
+
+    def timer_enable(self, on=True, classes=None):
+        for d in self._devices():
+            d.timer_enable(on, classes)
+
+    def timer_report(self):
+        out = {}
+        for d in self._devices():
+            for k, (ms, cnt) in d.timer_report().items():
+                a = out.get(k, (0.0, 0))
+                out[k] = (a[0] + ms, a[1] + cnt)
+        return out
+
+    def launch_count(self):
+        return sum(d.launch_count() for d in self._devices())
 
     def advance_time(self):
         """``_advance_solution`` source/ns_ipcs_solver.py:35-43"""

@@ -173,7 +173,9 @@ def build_partition(mesh, rank, nranks, axis=None, crank=None):
 
     nodes = plan(lnodes, nvg + mesh.num_edges)
     verts = plan(lverts, nvg)
-    return Partition(rank, nranks, local, node_perm, nodes, verts, lverts, lnodes, cell_gid)
+    part = Partition(rank, nranks, local, node_perm, nodes, verts, lverts, lnodes, cell_gid)
+    part.global_mesh = mesh          # host reference only: the replicated pressure solve works on the whole mesh
+    return part
 
 
 def connect(parts):
