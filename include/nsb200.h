@@ -106,6 +106,9 @@ typedef struct nsb_matrix {
 #define NSB_PC_JACOBI 1      /* z = D^-1 v                                                    */
 #define NSB_PC_CHEBYSHEV 2   /* z = p(D^-1 A) D^-1 v, p = Chebyshev polynomial of `degree` terms
                                 (degree-1 SpMVs) for the interval [lambda_min, lambda_max] of D^-1 A */
+#define NSB_PC_SADDLE 3      /* block-triangular preconditioner of the mixed Taylor-Hood Newton system (nsb_gmres only,
+                                flexible), described by nsb_precond.saddle */
+struct nsb_saddle;
 typedef struct nsb_precond {
     int32_t kind;
     int32_t degree;
@@ -117,7 +120,42 @@ typedef struct nsb_precond {
                                 the rounding inside M never enters the solution: Arnoldi, the residual test and
                                 the operator stay FP64.  Ignored by nsb_cg. */
     int32_t reserved;
+    const struct nsb_saddle* saddle;   /* NSB_PC_SADDLE only, else NULL */
 } nsb_precond;
+
+/* K16, hand-written: right block-triangular preconditioner for the monolithic Newton system
+ *     A = [ F  B ; B^T 0 ]  (+ Dirichlet identity rows),   dofs = [velocity (n_u) | pressure (n_p)]  (W numbering)
+ * which the reference hands to sparse LU (source/ns_solver_base.py:938-949, source/ns_bdf_solver.py:91-106):
+ *     z_p = -S~^-1 v_p,  S~^-1 = c_mass Mp^-1 + c_lap Lp^-1   (Cahouet-Chabard: c_mass = c_visc / c_p^2,
+ *                                                               c_lap = (alpha0 / k) / c_p^2; 0 when stationary)
+ *     z_u = F~^-1 (v_u - B z_p),  F~^-1 = Chebyshev polynomial of vel_degree terms in D^-1 F
+ * Mp / Lp: P1 mass / stiffness matrices on NSB_PAT_P1P1 (their bc_mask marks the vertices where the Schur
+ * complement is replaced by the identity: pressure Dirichlet dofs; for Lp additionally the vertices of natural
+ * (do-nothing) velocity boundaries).  The inner solves are nsb_cg to inner_rtol (Jacobi for Mp, Chebyshev-CG of
+ * lp_degree for Lp; persistent kernel), so the preconditioner varies from one application to the next and nsb_gmres
+ * runs FLEXIBLE.  work: n_u + 11 n_p doubles.  inner_iterations accumulates the inner CG iterations. */
+typedef struct nsb_saddle {
+    int32_t n_u, n_p;
+    nsb_matrix Mp, Lp;
+    const double* Mp_inv_diag;
+    const double* Lp_inv_diag;
+    const uint8_t* p_identity;     /* dev [n_p] or NULL: pressure dofs whose row of A is an identity row */
+    double c_mass, c_lap;
+    int32_t lp_nullspace;          /* Lp has the constant null space (no identity row at all) */
+    int32_t vel_degree;
+    double vel_lambda_min, vel_lambda_max;
+    int32_t lp_degree;
+    double lp_lambda_min, lp_lambda_max;
+    double inner_rtol;
+    int32_t inner_maxit;
+    int32_t reserved;
+    double* work;
+    int64_t inner_iterations;
+} nsb_saddle;
+/* largest eigenvalue (modulus) of D^-1 F, F = the velocity block (first n_u rows / columns) of the mixed matrix A,
+ * by power iteration; work: 2 n doubles */
+int nsb_saddle_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t n_u, int32_t iters,
+                          double* work, double* lambda_out_host, void* stream);
 
 /* ---------------------------------------------------------------- life cycle ---------- */
 int nsb_version(void);

@@ -32,13 +32,23 @@ class Matrix(C.Structure):
                 ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp), ("diag32", vp)]
 
 
+class Saddle(C.Structure):
+    """struct nsb_saddle"""
+    _fields_ = [("n_u", C.c_int32), ("n_p", C.c_int32), ("Mp", Matrix), ("Lp", Matrix), ("Mp_inv_diag", vp),
+                ("Lp_inv_diag", vp), ("p_identity", vp), ("c_mass", C.c_double), ("c_lap", C.c_double),
+                ("lp_nullspace", C.c_int32), ("vel_degree", C.c_int32), ("vel_lambda_min", C.c_double),
+                ("vel_lambda_max", C.c_double), ("lp_degree", C.c_int32), ("lp_lambda_min", C.c_double),
+                ("lp_lambda_max", C.c_double), ("inner_rtol", C.c_double), ("inner_maxit", C.c_int32),
+                ("reserved", C.c_int32), ("work", vp), ("inner_iterations", C.c_int64)]
+
+
 class Precond(C.Structure):
     """struct nsb_precond"""
     _fields_ = [("kind", C.c_int32), ("degree", C.c_int32), ("inv_diag", vp), ("lambda_min", C.c_double),
-                ("lambda_max", C.c_double), ("lowp", C.c_int32), ("reserved", C.c_int32)]
+                ("lambda_max", C.c_double), ("lowp", C.c_int32), ("reserved", C.c_int32), ("saddle", C.POINTER(Saddle))]
 
 
-PC_NONE, PC_JACOBI, PC_CHEBYSHEV = 0, 1, 2
+PC_NONE, PC_JACOBI, PC_CHEBYSHEV, PC_SADDLE = 0, 1, 2, 3
 
 # name -> (restype, argtypes); every symbol include/nsb200.h declares
 PROTOTYPES = {
@@ -71,6 +81,7 @@ PROTOTYPES = {
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
+    "nsb_saddle_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
     "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                          vp, c_i32p, c_f64p, vp]),
     "nsb_gmres": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,

@@ -13,8 +13,8 @@ from .monolithic import MixedSolverBase
 
 class ImplicitBDFSolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
-                 device_index=0, reorder=1):
-        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder)
+                 device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12):
+        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol)
         assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
         assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
         self._time_stepping = time_stepping
@@ -29,6 +29,8 @@ class ImplicitBDFSolver(MixedSolverBase):
         while len(alpha) < 3:
             alpha.append(0.0)
         self._alpha, self._next_step_size = tuple(alpha), ts.get_next_step_size()
+        self._mass_coefficient = self._alpha[0] / self._next_step_size
+        self._vel_lmax = None            # the velocity block changes with alpha0 / k: re-estimate its spectrum
         co = self._equation_coefficients
         self.dev.set_coefficients(self._next_step_size, self._alpha, co["convective_term"], co["pressure_term"],
                                   co["viscous_term"])

@@ -264,9 +264,13 @@ static int apply_cheb32(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M,
     return 0;
 }
 
+static int saddle_apply(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* v, double* z,
+                        double* scratch, cudaStream_t st);
+
 static int apply_pc(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* v, double* z,
                     double* scratch, int64_t n, cudaStream_t st, bool flexible = false) {
     const int G = krylov_grid(ctx, n);
+    if (M->kind == NSB_PC_SADDLE) return saddle_apply(ctx, A, M, v, z, scratch, st);
     if (flexible && pc_single_precision(A, M))
         return A->bs == 3 ? apply_cheb32<3>(ctx, A, M, v, z, scratch, st) : apply_cheb32<2>(ctx, A, M, v, z, scratch, st);
     if (M->kind == NSB_PC_NONE) {
@@ -313,8 +317,15 @@ static int apply_pc(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, con
 
 static int check_pc(nsb_ctx* ctx, const nsb_precond* M) {
     NSB_REQUIRE(ctx, M != nullptr, "null preconditioner");
-    NSB_REQUIRE(ctx, M->kind == NSB_PC_NONE || M->kind == NSB_PC_JACOBI || M->kind == NSB_PC_CHEBYSHEV,
-                "unknown preconditioner kind");
+    NSB_REQUIRE(ctx, M->kind == NSB_PC_NONE || M->kind == NSB_PC_JACOBI || M->kind == NSB_PC_CHEBYSHEV ||
+                M->kind == NSB_PC_SADDLE, "unknown preconditioner kind");
+    if (M->kind == NSB_PC_SADDLE) {
+        const nsb_saddle* S = M->saddle;
+        NSB_REQUIRE(ctx, S && S->work && S->Mp_inv_diag && S->Lp_inv_diag && S->n_u > 0 && S->n_p > 0,
+                    "saddle preconditioner: incomplete description");
+        NSB_REQUIRE(ctx, S->vel_degree >= 1 && S->vel_degree <= 64 && S->vel_lambda_min > 0.0 &&
+                    S->vel_lambda_max > S->vel_lambda_min, "saddle preconditioner: bad velocity Chebyshev interval");
+    }
     NSB_REQUIRE(ctx, M->kind == NSB_PC_NONE || M->inv_diag != nullptr, "preconditioner needs the inverse diagonal");
     if (M->kind == NSB_PC_CHEBYSHEV)
         NSB_REQUIRE(ctx, M->degree >= 1 && M->degree <= 64 && M->lambda_min > 0.0 && M->lambda_max > M->lambda_min,
@@ -627,6 +638,9 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
     NSB_REQUIRE(ctx, A && b && x && work, "null argument");
     NSB_REQUIRE(ctx, restart >= 1 && restart <= NSB_GMRES_MAX_RESTART, "restart must be in [1, 60]");
     if (check_pc(ctx, M)) return -1;
+    NSB_REQUIRE(ctx, M->kind != NSB_PC_SADDLE || ((int64_t)M->saddle->n_u + M->saddle->n_p == (int64_t)A->nrows * A->bs &&
+                                                   A->kind == NSB_CSR && A->bs == 1 && ctx->nranks == 1),
+                "saddle preconditioner needs the scalar CSR mixed matrix on one GPU");
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t n = (int64_t)A->nrows * A->bs;
     const int m = restart;
@@ -637,7 +651,7 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
     // Flexible GMRES (Saad 1993) when the preconditioner runs in single precision: z_j = M^-1 v_j is kept
     // (Z, restart x n behind the scratch) and x += Z y, so the preconditioner need not be a fixed linear
     // operator; Arnoldi, the Hessenberg system and the residual test stay FP64 on the FP64 matrix.
-    const bool flex = pc_single_precision(A, M);
+    const bool flex = pc_single_precision(A, M) || M->kind == NSB_PC_SADDLE;
     double* Z = scratch + 3 * n;
     double* ds = ctx->d_scalars;
     double* hs = ctx->h_scalars;
@@ -791,5 +805,126 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
     if (iters_out) *iters_out = it;
     if (resid_out) *resid_out = rnorm;
     if (rnorm > tol) return nsb_fail(ctx, "GMRES did not converge within the iteration limit%s%s");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K16: block-triangular preconditioner of the mixed Newton system (include/nsb200.h, nsb_saddle)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_mask_copy(int64_t n, const double* __restrict__ src, const uint8_t* __restrict__ m1, const uint8_t* __restrict__ m2,
+            double* __restrict__ dst) {
+    GRID_STRIDE(i, n) dst[i] = ((m1 && m1[i]) || (m2 && m2[i])) ? 0.0 : src[i];
+}
+// z_p = -(cm t1 + cl t2); identity rows of A: z_p = v_p
+__global__ void __launch_bounds__(256)
+k_schur_combine(int64_t n, const double* __restrict__ t1, const double* __restrict__ t2, double cm, double cl,
+                const double* __restrict__ vp, const uint8_t* __restrict__ ident, double* __restrict__ zp) {
+    GRID_STRIDE(i, n) zp[i] = (ident && ident[i]) ? vp[i] : -(cm * t1[i] + (t2 ? cl * t2[i] : 0.0));
+}
+// t = v - t
+__global__ void __launch_bounds__(256)
+k_rsub(int64_t n, const double* __restrict__ v, double* __restrict__ t) {
+    GRID_STRIDE(i, n) t[i] = v[i] - t[i];
+}
+
+static int saddle_apply(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* v, double* z,
+                        double* scratch, cudaStream_t st) {
+    nsb_saddle* S = const_cast<nsb_saddle*>(M->saddle);
+    const int64_t nu = S->n_u, np_ = S->n_p, n = nu + np_;
+    double* t = S->work;                       // [n]   B z_p, then the velocity right-hand side
+    double* vm = t + n;                        // [n_p] masked copy of v_p
+    double* t1 = vm + np_;                     // [n_p] Mp^-1 v_p
+    double* t2 = t1 + np_;                     // [n_p] Lp^-1 v_p
+    double* cgw = t2 + np_;                    // [7 n_p]
+    const double* vp = v + nu;
+    const int Gp = krylov_grid(ctx, np_), Gu = krylov_grid(ctx, nu);
+    int32_t its = 0;
+    // ---- pressure: z_p = -(c_mass Mp^-1 + c_lap Lp^-1) v_p -------------------------------------------
+    nsb_precond jac;
+    memset(&jac, 0, sizeof jac);
+    jac.kind = NSB_PC_JACOBI; jac.degree = 1; jac.inv_diag = S->Mp_inv_diag;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_mask_copy<<<Gp, 256, 0, st>>>(np_, vp, S->Mp.bc_mask, nullptr, vm);
+        NSB_LAUNCH_CHECK(ctx, "k_mask_copy");
+    }
+    NSB_CUDA(ctx, cudaMemsetAsync(t1, 0, sizeof(double) * np_, st));
+    if (nsb_cg(ctx, &S->Mp, &jac, vm, t1, S->inner_rtol, 0.0, S->inner_maxit, 0, cgw, &its, nullptr, st)) return -1;
+    S->inner_iterations += its;
+    const bool lap = S->c_lap != 0.0;
+    if (lap) {
+        nsb_precond pc;
+        memset(&pc, 0, sizeof pc);
+        pc.inv_diag = S->Lp_inv_diag;
+        if (S->lp_degree >= 2) {
+            pc.kind = NSB_PC_CHEBYSHEV; pc.degree = S->lp_degree; pc.lambda_min = S->lp_lambda_min; pc.lambda_max = S->lp_lambda_max;
+        } else {
+            pc.kind = NSB_PC_JACOBI; pc.degree = 1;
+        }
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_mask_copy<<<Gp, 256, 0, st>>>(np_, vp, S->Lp.bc_mask, nullptr, vm);
+            NSB_LAUNCH_CHECK(ctx, "k_mask_copy");
+        }
+        NSB_CUDA(ctx, cudaMemsetAsync(t2, 0, sizeof(double) * np_, st));
+        if (nsb_cg(ctx, &S->Lp, &pc, vm, t2, S->inner_rtol, 0.0, S->inner_maxit, S->lp_nullspace, cgw, &its, nullptr, st)) return -1;
+        S->inner_iterations += its;
+    }
+    NSB_CUDA(ctx, cudaMemsetAsync(z, 0, sizeof(double) * nu, st));
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_schur_combine<<<Gp, 256, 0, st>>>(np_, t1, lap ? t2 : nullptr, S->c_mass, S->c_lap, vp, S->p_identity, z + nu);
+        NSB_LAUNCH_CHECK(ctx, "k_schur_combine");
+    }
+    // ---- velocity: z_u = Cheb(D^-1 F) D^-1 (v_u - B z_p);  (A [0; z_p])_u = B z_p ---------------------
+    if (nsb_launch_spmv(ctx, A, z, t, nullptr, nullptr, st)) return -1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_rsub<<<Gu, 256, 0, st>>>(nu, v, t);
+        NSB_LAUNCH_CHECK(ctx, "k_rsub");
+    }
+    double *r = scratch, *d = scratch + n, *q = scratch + 2 * n;
+    NSB_CUDA(ctx, cudaMemsetAsync(d + nu, 0, sizeof(double) * np_, st));      // the direction's pressure part stays 0
+    const double theta = 0.5 * (S->vel_lambda_max + S->vel_lambda_min), delta = 0.5 * (S->vel_lambda_max - S->vel_lambda_min);
+    const double sigma1 = theta / delta;
+    double rho_old = 1.0 / sigma1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cheb_first<<<Gu, 256, 0, st>>>(nu, M->inv_diag, t, 1.0 / theta, r, d, z);
+        NSB_LAUNCH_CHECK(ctx, "k_cheb_first");
+    }
+    for (int k = 1; k < S->vel_degree; ++k) {
+        const double rho = 1.0 / (2.0 * sigma1 - rho_old);
+        if (nsb_launch_spmv(ctx, A, d, q, nullptr, nullptr, st)) return -1;
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_cheb_step<<<Gu, 256, 0, st>>>(nu, M->inv_diag, q, rho * rho_old, 2.0 * rho / delta, r, d, z);
+        NSB_LAUNCH_CHECK(ctx, "k_cheb_step");
+        rho_old = rho;
+    }
+    return 0;
+}
+
+extern "C" int nsb_saddle_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t n_u, int32_t iters,
+                                     double* work, double* lambda_out, void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, A && inv_diag && work && lambda_out && iters >= 1 && A->kind == NSB_CSR && A->bs == 1 && n_u > 0 &&
+                n_u <= A->nrows, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = A->nrows;
+    const int G = krylov_grid(ctx, n_u);
+    double *v = work, *q = work + n;
+    double* ds = ctx->d_scalars;
+    NSB_CUDA(ctx, cudaMemsetAsync(v, 0, sizeof(double) * n, st));
+    k_pi_init<<<G, 256, 0, st>>>(n_u, v);
+    NSB_LAUNCH_CHECK(ctx, "k_pi_init");
+    for (int k = 0; k <= iters; ++k) {
+        if (nsb_launch_spmv(ctx, A, v, q, nullptr, nullptr, st)) return -1;
+        k_pi_step<<<G, 256, 0, st>>>(n_u, inv_diag, q, k == 0 ? nullptr : ds + S_H1 + ((k - 1) & 1), v, ctx->d_partials,
+                                     ctx->d_counter, ds + S_H1 + (k & 1));
+        NSB_LAUNCH_CHECK(ctx, "k_pi_step");
+    }
+    if (fetch(ctx, S_H1, 2, st)) return -1;
+    *lambda_out = sqrt(ctx->h_scalars[S_H1 + (iters & 1)]);
     return 0;
 }

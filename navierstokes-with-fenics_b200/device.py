@@ -376,7 +376,7 @@ class Device:
         """nsb_precond descriptor; a plain tensor passed to cg/gmres means Jacobi.  ``lowp``: the Chebyshev
         polynomial runs in single precision inside a flexible GMRES (needs the matrix's vals32 copy)."""
         m = L.Precond(kind, degree, inv_diag.data_ptr() if inv_diag is not None else None, lambda_min, lambda_max,
-                      1 if lowp else 0, 0)
+                      1 if lowp else 0, 0, None)
         m._keep = inv_diag
         return m
 
@@ -394,6 +394,16 @@ class Device:
                                            _ptr(work), C.byref(out), self.stream))
         return out.value
 
+    def saddle_lambda_max(self, A, inv_diag, n_u, iters=12, work=None):
+        """largest eigenvalue of D^-1 F, F = velocity block of the mixed matrix ``A``"""
+        n = A.nrows
+        if work is None or work.numel() < 2 * n:
+            work = self.empty(2 * n)
+        out = C.c_double()
+        self.check(self.lib.nsb_saddle_lambda_max(self.ctx, C.byref(A), _ptr(inv_diag), n_u, iters, _ptr(work), C.byref(out),
+                                                  self.stream))
+        return out.value
+
     def cg(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=10000, nullspace=False, work=None):
         n = A.nrows * A.bs
         need = self.lib.nsb_cg_workspace_doubles(n)
@@ -409,7 +419,7 @@ class Device:
     def gmres(self, A, M, b, x, rtol=1e-12, atol=0.0, maxit=2000, restart=40, work=None, x0_is_zero=False):
         n = A.nrows * A.bs
         M = self._pc(M)
-        need = self.lib.nsb_gmres_workspace_doubles(n, restart, M.lowp)
+        need = self.lib.nsb_gmres_workspace_doubles(n, restart, 1 if (M.lowp or M.kind == L.PC_SADDLE) else 0)
         if work is None or work.numel() < need:
             work = self.empty(need)
         it, res = C.c_int32(), C.c_double()

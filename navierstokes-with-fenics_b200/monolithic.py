@@ -13,8 +13,16 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged
 
 
 class MixedSolverBase(SolverBase):
-    def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=1):
+    def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=1,
+                 linear_solver="auto", linear_rtol=1e-12, gmres_restart=60):
+        """``linear_solver`` (K16, the Newton update the reference hands to sparse LU): "gmres" = hand-written
+        flexible GMRES with the block-triangular Cahouet-Chabard preconditioner (csrc/krylov.cu saddle_apply);
+        "direct" = cuSOLVER sparse QR (library leg); "auto" = direct below 20 000 dofs and for stationary problems
+        (no mass term: the Schur complement approximation degrades with the Reynolds number), gmres otherwise."""
         super().__init__(mesh, boundary_markers, form_convective_term)
+        assert linear_solver in ("auto", "gmres", "direct")
+        self._linear_solver, self._linear_rtol, self._gmres_restart = linear_solver, linear_rtol, gmres_restart
+        self.krylov_iterations, self.inner_iterations = [], 0
         self.dev = dev = Device(mesh, device_index, mixed=True)
         self._nW = dev.spaces.ndofs_W
         self._pat = dev.patterns["WW"]
@@ -73,7 +81,10 @@ class MixedSolverBase(SolverBase):
         converged = (r / r0 < rtol if r0 > 0 else False) or r < atol
         while not converged and it < maxit:
             jacobian()
-            dev.direct_solve("WW", self._A, self._b, self._dx, self._reorder)
+            if self._use_gmres():
+                self._gmres_update(r0)
+            else:
+                dev.direct_solve("WW", self._A, self._b, self._dx, self._reorder)
             dev.axpy(-1.0, self._dx, x)
             r = residual()
             hist.append(r)
@@ -83,6 +94,75 @@ class MixedSolverBase(SolverBase):
         if not converged and error_on_nonconvergence:
             raise NewtonNotConverged("Newton solver did not converge (%d iterations, residual %g)" % (it, r))
         return it
+
+    # ---- K16: hand-written Krylov solve of the Newton update ---------------------------------------
+    _mass_coefficient = 0.0      # alpha0 / k of the Jacobian's mass term; set by the instationary mirror
+
+    def _use_gmres(self):
+        if self._linear_solver == "auto":
+            return self._nW >= 20000 and self._mass_coefficient > 0.0
+        return self._linear_solver == "gmres"
+
+    def _setup_saddle(self):
+        """P1 mass / stiffness matrices, masks and work space of the block-triangular preconditioner (once)"""
+        import ctypes as C
+        dev, sp = self.dev, self.dev.spaces
+        nu, npr = sp.dim * sp.n_nodes, sp.n_vertices
+        pat = dev.pattern("P1P1")
+        self._Mp_vals, self._Lp_vals = dev.empty(pat.nnz), dev.empty(pat.nnz)
+        dev.assemble_p1_mass(L.MAT, A=self._Mp_vals)
+        dev.assemble_poisson(L.MAT, A=self._Lp_vals)
+        dofs = self._bc_dofs.cpu().numpy()
+        ident = np.zeros(npr, dtype=np.uint8)
+        ident[dofs[dofs >= nu] - nu] = 1                       # pressure Dirichlet dofs (and the pin): identity rows of A
+        # natural (do-nothing) velocity boundaries: the Schur complement acts like a Dirichlet Laplacian there
+        m = self._mesh
+        with_bc = set(int(b) for b, _, _ in self._velocity_bcs)
+        lmask = ident.copy()
+        for marker in np.unique(m.bfacet_marker):
+            if int(marker) not in with_bc:
+                lmask[np.unique(m.bfacets[m.bfacet_marker == marker])] = 1
+        self._p_ident = dev.upload(ident) if ident.any() else None
+        self._lp_mask = dev.upload(lmask) if lmask.any() else None
+        self._Mp = dev.matrix("P1P1", self._Mp_vals, L.CSR, 1, self._p_ident)
+        self._Lp = dev.matrix("P1P1", self._Lp_vals, L.CSR, 1, self._lp_mask)
+        self._Mp_dinv, self._Lp_dinv = dev.empty(npr), dev.empty(npr)
+        dev.inv_diagonal(self._Mp, self._Mp_dinv)
+        dev.inv_diagonal(self._Lp, self._Lp_dinv)
+        lmax = 1.1 * dev.lambda_max(self._Lp, self._Lp_dinv, iters=30)
+        self._saddle_work = dev.empty(nu + 11 * npr)
+        self._Amat = dev.matrix("WW", self._A, L.CSR, 1)
+        self._A_dinv = dev.empty(self._nW)
+        self._gmres_work = dev.empty(dev.lib.nsb_gmres_workspace_doubles(self._nW, self._gmres_restart, 1))
+        co = self._equation_coefficients
+        cp2 = co["pressure_term"] ** 2
+        self._saddle = L.Saddle(nu, npr, self._Mp, self._Lp, self._Mp_dinv.data_ptr(), self._Lp_dinv.data_ptr(),
+                                self._p_ident.data_ptr() if self._p_ident is not None else None,
+                                co["viscous_term"] / cp2, 0.0, 0 if lmask.any() else 1, 8, 0.0, 0.0,
+                                8, lmax / 300.0, lmax, 1e-2, 2000, 0, self._saddle_work.data_ptr(), 0)
+        self._vel_lmax = None
+        del C
+
+    def _gmres_update(self, r0):
+        """dx = J^-1 b by flexible GMRES, right-preconditioned by the block-triangular Cahouet-Chabard operator;
+        solved to ``linear_rtol`` relative to the step's initial Newton residual, like the IPCS momentum solve"""
+        import ctypes as C
+        dev = self.dev
+        if not hasattr(self, "_saddle"):
+            self._setup_saddle()
+        S = self._saddle
+        S.c_lap = self._mass_coefficient / self._equation_coefficients["pressure_term"] ** 2
+        dev.inv_diagonal(self._Amat, self._A_dinv)
+        if self._vel_lmax is None:
+            self._vel_lmax = 1.1 * dev.saddle_lambda_max(self._Amat, self._A_dinv, S.n_u, iters=12, work=self._gmres_work)
+        S.vel_lambda_max, S.vel_lambda_min = self._vel_lmax, self._vel_lmax / 30.0
+        pc = L.Precond(L.PC_SADDLE, 1, self._A_dinv.data_ptr(), 0.0, 0.0, 0, 0, C.pointer(S))
+        self._dx.zero_()
+        t0 = S.inner_iterations
+        n_it, _ = dev.gmres(self._Amat, pc, self._b, self._dx, rtol=self._linear_rtol, atol=self._linear_rtol * r0,
+                            maxit=20 * self._gmres_restart, restart=self._gmres_restart, work=self._gmres_work, x0_is_zero=True)
+        self.krylov_iterations.append(n_it)
+        self.inner_iterations += S.inner_iterations - t0
 
     # ---- sub-space views of a mixed vector (FunctionAssigner, source/ns_solver_base.py:424-476) --
     def _maps(self):

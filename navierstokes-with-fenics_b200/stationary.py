@@ -13,8 +13,8 @@ from .monolithic import MixedSolverBase
 
 class StationarySolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", tol=1e-10, maxiter=50,
-                 tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1):
-        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder)
+                 tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12):
+        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol)
         assert isinstance(maxiter, int) and maxiter > 0 and isinstance(tol, float) and tol > 0.0
         assert isinstance(maxiter_picard, int) and maxiter_picard > 0 and isinstance(tol_picard, float)
         self._tol, self._maxiter = tol, maxiter

@@ -40,9 +40,11 @@ def test_c1_stationary_cavity_re100(built_library):
     assert solver.newton_iterations == orc.newton_iterations
 
 
-def test_c2_channel_bdf2(built_library):
+@pytest.mark.parametrize("linear_solver", ["direct", "gmres"])
+def test_c2_channel_bdf2(built_library, linear_solver):
     """configs[1] in small: instationary channel [0,10] x [0,1], Re = 10, inlet 6y(1-y)(1 + 0.5 sin(pi t)),
-    dt = 0.01, monolithic BDF-2 Newton (tests/test_transient_solvers.py:50-84 of the reference)"""
+    dt = 0.01, monolithic BDF-2 Newton (tests/test_transient_solvers.py:50-84 of the reference); the Newton update
+    by the library QR and by the hand-written block-preconditioned flexible GMRES (K16)"""
     import nsb200
     import oracle
     V, P = nsb200.VelocityBCType, nsb200.PressureBCType
@@ -52,7 +54,7 @@ def test_c2_channel_bdf2(built_library):
         return np.stack([6.0 * x[:, 1] * (1.0 - x[:, 1]) * (1.0 + 0.5 * np.sin(np.pi * t)), 0.0 * x[:, 0]], axis=1)
     mesh, markers = nsb200.hyper_rectangle((0.0, 0.0), (10.0, 1.0), (nx, ny))
     ts = nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=dt)
-    solver = nsb200.ImplicitBDFSolver(mesh, markers, "standard", ts)
+    solver = nsb200.ImplicitBDFSolver(mesh, markers, "standard", ts, linear_solver=linear_solver)
     solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / Re))
     solver.set_boundary_conditions([(V.function, 1, nsb200.Expression(inflow)), (V.no_slip, 3, None),
                                     (V.no_slip, 4, None), (P.constant, 2, 0.0)])
@@ -72,6 +74,9 @@ def test_c2_channel_bdf2(built_library):
     assert rel_max_err(w[osp.V_to_W], orc.solutions[1][osp.V_to_W]) < 1e-8
     assert rel_max_err(w[osp.Q_to_W], orc.solutions[1][osp.Q_to_W]) < 1e-8
     assert solver.newton_iterations == orc.newton_iterations
+    if linear_solver == "gmres":
+        assert len(solver.krylov_iterations) == sum(solver.newton_iterations) and max(solver.krylov_iterations) < 200
+        assert solver.direct_solve_seconds()[1] == 0
 
 
 def _tgv(Re=100.0, gamma=2.0 * np.pi):
@@ -140,7 +145,8 @@ def test_c3_taylor_green_ipcs_matches_oracle_and_converges(built_library):
     assert e16 < 2e-3 and e8 / e16 > 2.5, (e8, e16)
 
 
-def test_c4_dfg_cylinder_drag_lift(built_library):
+@pytest.mark.parametrize("linear_solver", ["direct", "gmres"])
+def test_c4_dfg_cylinder_drag_lift(built_library, linear_solver):
     """configs[3]: DFG 2D-2 (Re = 100, BDF-2, dt = 0.005, inlet 6 y/h (1 - y/h), demo/dfg_benchmark.py) on the
     synthetic block-structured cylinder mesh: fields, drag and lift coefficients against the LU oracle on the
     same mesh to 1e-8 relative."""
@@ -153,7 +159,7 @@ def test_c4_dfg_cylinder_drag_lift(built_library):
     def inlet(x, t=0.0):
         return np.stack([6.0 * x[:, 1] / h * (1.0 - x[:, 1] / h), 0.0 * x[:, 0]], axis=1)
     ts = nsb200.BDFTimeStepping(0.0, 80.0, order=2, desired_start_time_step=dt)
-    solver = nsb200.ImplicitBDFSolver(mesh, markers, "standard", ts)
+    solver = nsb200.ImplicitBDFSolver(mesh, markers, "standard", ts, linear_solver=linear_solver)
     solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / Re))
     solver.set_boundary_conditions([(V.function, ids["inlet"], inlet), (V.no_slip, ids["cylinder"], None),
                                     (V.no_slip, ids["upper wall"], None), (V.no_slip, ids["lower wall"], None)])
