@@ -217,6 +217,14 @@ int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs_d
  * (source/auxiliary_classes.py:251-306).  coef = {k, a0, a1, a2, c_conv, c_p, c_visc, c_body} */
 int nsb_set_coefficients(nsb_ctx* ctx, const double* coef_host8);
 
+/* weak-form variants of the momentum equation: constructor arguments form_convective_term / form_viscous_term of
+ * source/ns_solver_base.py:78-115 (terms :370-390, :478-499, :662-673) and the Coriolis term :173-191.
+ * conv: 0 standard | 1 rotational | 2 divergence | 3 skew_symmetric; visc: 0 reduced | 1 traction;
+ * coriolis_host3 = 2 c_Omega Omega (2D: only [2] = the z component; NULL = none).  The default combination
+ * (0, 0, none) runs the tuned IPCS kernels, every other one the generic row kernels; generic != 0 forces the generic
+ * kernels for the default combination too (they are tested against the tuned ones). */
+int nsb_set_forms(nsb_ctx* ctx, int32_t conv, int32_t visc, const double* coriolis_host3, int32_t generic);
+
 /* ---------------------------------------------------------------- assembly (K1-K8) ------ */
 /* IPCS tentative velocity F / J = derivative(F,u*)   source/ns_ipcs_solver.py:106-147 (:126-130, :136)
  * b_out [d*nnodes]; A_out BSR-d values on NSB_PAT_P2P2. */

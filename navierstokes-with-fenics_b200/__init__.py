@@ -12,8 +12,8 @@ from .grid import (SimplexMesh, HyperCubeBoundaryMarkers, hyper_cube, hyper_rect
                    channel_with_cylinder, DFG_BOUNDARY_IDS)
 from .spaces import TaylorHoodSpaces                                          # noqa: F401
 from .timestepping import BDFTimeStepping                                     # noqa: F401
-from .solver_base import (VelocityBCType, PressureBCType, WeakFormConvectiveTerm,      # noqa: F401
-                          Expression, NewtonNotConverged)
+from .solver_base import (VelocityBCType, PressureBCType, TractionBCType, WeakFormConvectiveTerm,      # noqa: F401
+                          WeakFormViscousTerm, Expression, NewtonNotConverged)
 
 
 def __getattr__(name):

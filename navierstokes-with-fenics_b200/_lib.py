@@ -68,6 +68,7 @@ PROTOTYPES = {
     "nsb_set_scratch": (C.c_int, [vp, vp, C.c_int64]),
     "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),
     "nsb_set_coefficients": (C.c_int, [vp, c_f64p]),
+    "nsb_set_forms": (C.c_int, [vp, C.c_int32, C.c_int32, c_f64p, C.c_int32]),
     "nsb_assemble_ipcs_momentum": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp]),
     "nsb_assemble_poisson": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp]),
     "nsb_assemble_correction": (C.c_int, [vp, C.c_int32, vp, vp, vp, vp, vp, vp]),

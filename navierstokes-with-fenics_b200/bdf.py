@@ -13,8 +13,9 @@ from .monolithic import MixedSolverBase
 
 class ImplicitBDFSolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
-                 device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12):
-        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol)
+                 device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12, form_viscous_term="standard"):
+        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol,
+                         form_viscous_term=form_viscous_term)
         assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
         assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
         self._time_stepping = time_stepping
@@ -55,6 +56,7 @@ class ImplicitBDFSolver(MixedSolverBase):
         if not self._bc_ready:
             self._setup_boundary_conditions()
         self._set_time(self._time_stepping.next_time)
+        self._prepare_forms_and_load()
         self._update_bc_values()
         self._update_time_stepping_coefficients()
         self._solve_time_step()
@@ -76,6 +78,8 @@ class ImplicitBDFSolver(MixedSolverBase):
     def _residual(self):
         dev, w = self.dev, self._solutions
         dev.assemble_mixed(L.VEC | L.BDF, w[0], w[1], w[2], b=self._b)
+        if self._loadW is not None:
+            dev.axpy(1.0, self._loadW, self._b)
         dev.bc_apply_vector(L.BC_NEWTON, self._b, self._bc_dofs, self._bc_vals, x=w[0])
         return dev.norm(self._b)
 

@@ -75,6 +75,8 @@ __device__ __forceinline__ void vertex_gradients(const Geo<D>& g, const double (
     }
 }
 
+#include "assemble_forms.cuh"
+
 // ===========================================================================================
 // K2  IPCS momentum Jacobian, BSR-D rows
 //   A[(I,b),(J,a)] = delta_ab S_IJ + c_c detJ sum_M T_IJM gM[b][a]
@@ -88,7 +90,7 @@ k_momentum_jacobian(int32_t nrows, const int32_t* __restrict__ rowptr,
                     const uint8_t* __restrict__ pair_iloc, const uint8_t* __restrict__ pair_slots,
                     const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
                     const int32_t* __restrict__ cell_verts,
-                    const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc,
+                    const double* __restrict__ ustar, double mass_coef, nsb_coef cf, nsb_forms fm,
                     int newton, double* __restrict__ vals) {
     using TB = Tab<D>;
     constexpr int NL = TB::NL2, DD = D * D;
@@ -100,80 +102,25 @@ k_momentum_jacobian(int32_t nrows, const int32_t* __restrict__ rowptr,
     for (int32_t p = pair_ptr[row]; p < pair_ptr[row + 1]; ++p) {
         const int32_t c = pair_cell[p];
         const int I = pair_iloc[p];
-        int32_t nodes[NL];
-#pragma unroll
-        for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
         int32_t vtx[D + 1];
 #pragma unroll
         for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
-        Geo<D> g;
-        cell_geometry(coords, vtx, g);
-        double U[NL][D];
-#pragma unroll
-        for (int L = 0; L < NL; ++L)
-#pragma unroll
-            for (int b = 0; b < D; ++b) U[L][b] = ustar[(int64_t)D * nodes[L] + b];
-        double G[D][D];
-        metric<D>(g, G);
-        // y[M][k]
-        double y[D + 1][D];
-#pragma unroll
-        for (int M = 0; M <= D; ++M)
-#pragma unroll
-            for (int k = 0; k < D; ++k) y[M][k] = 0.0;
+        CellCtx<D> cc;
+        cell_geometry(coords, vtx, cc.g);
         for (int L = 0; L < NL; ++L) {
-            double z[D];
+            const int64_t nd = cell_nodes[(int64_t)c * NL + L];
 #pragma unroll
-            for (int k = 0; k < D; ++k) {
-                double s = 0.0;
-#pragma unroll
-                for (int i = 0; i < D; ++i) s += g.K[k][i] * U[L][i];
-                z[k] = s * g.detJ;
-            }
-#pragma unroll
-            for (int M = 0; M <= D; ++M) {
-                const double t = TB::T(I, L, M);
-#pragma unroll
-                for (int k = 0; k < D; ++k) y[M][k] += t * z[k];
-            }
+            for (int b = 0; b < D; ++b) cc.U[L][b] = ustar[(int64_t)D * nd + b];
         }
-        double gM[D + 1][D][D];
-        if (newton) vertex_gradients<D>(g, U, gM);
-        for (int J = 0; J < NL; ++J) {
-            double S = mass_coef * g.detJ * TB::M2(I, J);
-            double v = 0.0;
+        cell_context<D>(cc);
+        for (int b = 0; b < D; ++b) {
+            double Ae[D * NL], Fe;
+            velocity_row<D>(cc, I, b, nullptr, mass_coef, 0.0, cf, fm, newton != 0, true, Ae, Fe);
+            for (int J = 0; J < NL; ++J) {
+                double* dst = vals + base + (int64_t)pair_slots[(int64_t)p * NL + J] * DD;
 #pragma unroll
-            for (int j = 0; j < D; ++j)
-#pragma unroll
-                for (int k = 0; k < D; ++k) v += G[j][k] * TB::D2(I, J, j, k);
-            S += c_visc * v;
-            double cv = 0.0;
-#pragma unroll
-            for (int M = 0; M <= D; ++M)
-#pragma unroll
-                for (int k = 0; k < D; ++k) cv += y[M][k] * TB::DV(J, M, k);
-            S += c_conv * cv;
-            double blk[D][D];
-#pragma unroll
-            for (int b = 0; b < D; ++b)
-#pragma unroll
-                for (int a = 0; a < D; ++a) blk[b][a] = (a == b) ? S : 0.0;
-            if (newton) {
-                const double f = c_conv * g.detJ;
-#pragma unroll
-                for (int M = 0; M <= D; ++M) {
-                    const double t = f * TB::T(I, J, M);
-#pragma unroll
-                    for (int b = 0; b < D; ++b)
-#pragma unroll
-                        for (int a = 0; a < D; ++a) blk[b][a] += t * gM[M][b][a];
-                }
+                for (int a = 0; a < D; ++a) dst[b * D + a] += Ae[a * NL + J];
             }
-            double* dst = vals + base + (int64_t)pair_slots[(int64_t)p * NL + J] * DD;
-#pragma unroll
-            for (int b = 0; b < D; ++b)
-#pragma unroll
-                for (int a = 0; a < D; ++a) dst[b * D + a] += blk[b][a];
         }
     }
 }
@@ -190,7 +137,7 @@ k_momentum_residual(int32_t nrows, const int32_t* __restrict__ pair_ptr,
                     const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
                     const int32_t* __restrict__ cell_verts,
                     const double* __restrict__ ustar, const double* __restrict__ un,
-                    const double* __restrict__ unm1, const double* __restrict__ pn, nsb_coef cf,
+                    const double* __restrict__ unm1, const double* __restrict__ pn, nsb_coef cf, nsb_forms fm,
                     double* __restrict__ b_out) {
     using TB = Tab<D>;
     constexpr int NL = TB::NL2;
@@ -203,68 +150,36 @@ k_momentum_residual(int32_t nrows, const int32_t* __restrict__ pair_ptr,
     for (int32_t p = pair_ptr[row]; p < pair_ptr[row + 1]; ++p) {
         const int32_t c = pair_cell[p];
         const int I = pair_iloc[p];
-        int32_t nodes[NL];
-#pragma unroll
-        for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
         int32_t vtx[D + 1];
 #pragma unroll
         for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
-        Geo<D> g;
-        cell_geometry(coords, vtx, g);
-        double U[NL][D];
-#pragma unroll
-        for (int L = 0; L < NL; ++L)
-#pragma unroll
-            for (int b = 0; b < D; ++b) U[L][b] = ustar[(int64_t)D * nodes[L] + b];
-        double G[D][D];
-        metric<D>(g, G);
-        double gM[D + 1][D][D];
-        vertex_gradients<D>(g, U, gM);
-        double Fe[D];
-#pragma unroll
-        for (int b = 0; b < D; ++b) Fe[b] = 0.0;
+        CellCtx<D> cc;
+        cell_geometry(coords, vtx, cc.g);
+        double acc[D][NL];
         for (int L = 0; L < NL; ++L) {
-            // mass (BDF acceleration) + viscous
-            const double m = inv_k * g.detJ * TB::M2(I, L);
-            double a = 0.0;
-#pragma unroll
-            for (int j = 0; j < D; ++j)
-#pragma unroll
-                for (int k = 0; k < D; ++k) a += G[j][k] * TB::D2(I, L, j, k);
-            a *= cf.c_visc;
+            const int64_t nd = cell_nodes[(int64_t)c * NL + L];
 #pragma unroll
             for (int b = 0; b < D; ++b) {
-                const int64_t dof = (int64_t)D * nodes[L] + b;
-                const double acc = cf.a0 * U[L][b] + cf.a1 * un[dof] + cf.a2 * unm1[dof];
-                Fe[b] += m * acc + a * U[L][b];
+                const int64_t dof = (int64_t)D * nd + b;
+                const double u = ustar[dof];
+                cc.U[L][b] = u;
+                acc[b][L] = cf.a0 * u + cf.a1 * un[dof] + cf.a2 * unm1[dof];
             }
-            // convective
+        }
+        cell_context<D>(cc);
+        for (int b = 0; b < D; ++b) {
+            double Fe;
+            velocity_row<D>(cc, I, b, acc[b], 0.0, inv_k, cf, fm, true, false, nullptr, Fe);
+            // pressure: - c_p int div(w) p^n
 #pragma unroll
             for (int M = 0; M <= D; ++M) {
-                const double t = cf.c_conv * g.detJ * TB::T(I, L, M);
-#pragma unroll
-                for (int b = 0; b < D; ++b) {
-                    double h = 0.0;
-#pragma unroll
-                    for (int j = 0; j < D; ++j) h += U[L][j] * gM[M][b][j];
-                    Fe[b] += t * h;
-                }
-            }
-        }
-        // pressure
-#pragma unroll
-        for (int M = 0; M <= D; ++M) {
-            const double pm = cf.c_p * g.detJ * pn[vtx[M]];
-#pragma unroll
-            for (int b = 0; b < D; ++b) {
                 double s = 0.0;
 #pragma unroll
-                for (int j = 0; j < D; ++j) s += g.K[j][b] * TB::DP(I, j, M);
-                Fe[b] -= pm * s;
+                for (int j = 0; j < D; ++j) s += cc.g.K[j][b] * TB::DP(I, j, M);
+                Fe -= cf.c_p * cc.g.detJ * pn[vtx[M]] * s;
             }
+            F[b] += Fe;
         }
-#pragma unroll
-        for (int b = 0; b < D; ++b) F[b] += Fe[b];
     }
 #pragma unroll
     for (int b = 0; b < D; ++b) b_out[(int64_t)D * row + b] = F[b];
@@ -476,7 +391,7 @@ k_mixed_rows(int32_t nrows, int do_vec, int do_mat, int newton, int bdf, int sym
              const uint8_t* __restrict__ pair_slots, const double* __restrict__ coords,
              const int32_t* __restrict__ cell_verts, const int32_t* __restrict__ cell_dofs,
              const double* __restrict__ w0, const double* __restrict__ w1, const double* __restrict__ w2,
-             const uint8_t* __restrict__ bc_mask, const double* __restrict__ bc_g, nsb_coef cf,
+             const uint8_t* __restrict__ bc_mask, const double* __restrict__ bc_g, nsb_coef cf, nsb_forms fm,
              double* __restrict__ b_out, double* __restrict__ vals) {
     using TB = Tab<D>;
     constexpr int NL = TB::NL2, NV = D + 1, NW = D * NL + NV;
@@ -497,7 +412,9 @@ k_mixed_rows(int32_t nrows, int do_vec, int do_mat, int newton, int bdf, int sym
         for (int M = 0; M < NV; ++M) v[M] = cell_verts[(int64_t)c * NV + M];
         Geo<D> g;
         cell_geometry(coords, v, g);
-        double U[NL][D];
+        CellCtx<D> cc;
+        cc.g = g;
+        double (&U)[NL][D] = cc.U;
 #pragma unroll
         for (int L = 0; L < NL; ++L)
 #pragma unroll
@@ -506,59 +423,15 @@ k_mixed_rows(int32_t nrows, int do_vec, int do_mat, int newton, int bdf, int sym
         double Fe = 0.0;
         if (il < D * NL) {
             const int br = il / NL, I = il % NL;
-            double G[D][D];
-            metric<D>(g, G);
-            double gM[D + 1][D][D];
-            vertex_gradients<D>(g, U, gM);
-            double y[D + 1][D];
-#pragma unroll
-            for (int M = 0; M <= D; ++M)
-#pragma unroll
-                for (int k = 0; k < D; ++k) y[M][k] = 0.0;
-            for (int L = 0; L < NL; ++L) {
-#pragma unroll
-                for (int k = 0; k < D; ++k) {
-                    double s = 0.0;
-#pragma unroll
-                    for (int i = 0; i < D; ++i) s += g.K[k][i] * U[L][i];
-                    s *= g.detJ;
-#pragma unroll
-                    for (int M = 0; M <= D; ++M) y[M][k] += TB::T(I, L, M) * s;
-                }
-            }
-            for (int J = 0; J < NL; ++J) {
-                double vis = 0.0;
-#pragma unroll
-                for (int j = 0; j < D; ++j)
-#pragma unroll
-                    for (int k = 0; k < D; ++k) vis += G[j][k] * TB::D2(I, J, j, k);
-                vis *= cf.c_visc;
-                double cv = 0.0;
-#pragma unroll
-                for (int M = 0; M <= D; ++M)
-#pragma unroll
-                    for (int k = 0; k < D; ++k) cv += y[M][k] * TB::DV(J, M, k);
-                const double mm = g.detJ * TB::M2(I, J);
-                const double S = mass_coef * mm + vis + cf.c_conv * cv;
-                // residual pieces
-                double acc = 0.0;
-                if (bdf) {
+            cell_context<D>(cc);
+            double acc[NL];
+            if (bdf) {
+                for (int J = 0; J < NL; ++J) {
                     const int32_t dof = dofs[br * NL + J];
-                    acc = cf.a0 * U[J][br] + cf.a1 * w1[dof] + cf.a2 * w2[dof];
-                }
-                Fe += inv_k * mm * acc + (vis + cf.c_conv * cv) * U[J][br];
-#pragma unroll
-                for (int a = 0; a < D; ++a) {
-                    double e = (a == br) ? S : 0.0;
-                    if (newton) {
-                        double s = 0.0;
-#pragma unroll
-                        for (int M = 0; M <= D; ++M) s += TB::T(I, J, M) * gM[M][br][a];
-                        e += cf.c_conv * g.detJ * s;
-                    }
-                    Ae[a * NL + J] = e;
+                    acc[J] = cf.a0 * U[J][br] + cf.a1 * w1[dof] + cf.a2 * w2[dof];
                 }
             }
+            velocity_row<D>(cc, I, br, bdf ? acc : nullptr, mass_coef, inv_k, cf, fm, newton != 0, do_mat || symbc, Ae, Fe);
 #pragma unroll
             for (int M = 0; M < NV; ++M) {
                 double s = 0.0;
@@ -623,17 +496,24 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
     cudaStream_t st = (cudaStream_t)stream;
     const int T = 128, B = nsb_blocks(P.nrows, T);
     const nsb_coef cf = ctx->coef;
+    nsb_forms fm;
+    fm.conv = ctx->form_conv; fm.visc = ctx->form_visc;
+    for (int i = 0; i < 3; ++i) fm.cor[i] = ctx->coriolis[i];
+    // the tuned kernels cover the default weak form (standard convection, reduced viscous term, no Coriolis term);
+    // every other variant of the reference runs through the generic row kernels (assemble_forms.cuh)
+    const bool tuned = fm.conv == 0 && fm.visc == 0 && fm.cor[0] == 0.0 && fm.cor[1] == 0.0 && fm.cor[2] == 0.0 &&
+                       !ctx->force_generic_assembly;
     if (flags & NSB_VEC) {
         NSB_REQUIRE(ctx, ustar && un && unm1 && pn && b_out, "null vector argument");
         NSB_TIMED(ctx, NSB_T_ASM_RES, st);
-        const int tp = nsb_launch_residual_cells(ctx, ustar, un, unm1, pn, b_out, st);
+        const int tp = tuned ? nsb_launch_residual_cells(ctx, ustar, un, unm1, pn, b_out, st) : 1;
         if (tp < 0) return -1;
         if (tp == 1) {
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_residual<2><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                                     ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, cf, b_out)),
+                                                     ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, cf, fm, b_out)),
             (k_momentum_residual<3><<<B, T, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, ctx->coords,
-                                                     ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, cf, b_out)));
+                                                     ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn, cf, fm, b_out)));
         NSB_LAUNCH_CHECK(ctx, "k_momentum_residual");
         }
     }
@@ -642,16 +522,16 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
         const int newton = (flags & NSB_PICARD) ? 0 : 1;
         const double mc = cf.a0 / cf.k;
         NSB_TIMED(ctx, NSB_T_ASM_JAC, st);
-        const int rg = nsb_launch_jacobian_rowgroups(ctx, ustar, mc, newton, A_out, st);
+        const int rg = tuned ? nsb_launch_jacobian_rowgroups(ctx, ustar, mc, newton, A_out, st) : 1;
         if (rg < 0) return -1;
         if (rg == 0) return 0;
         NSB_DIM_DISPATCH(ctx,
             (k_momentum_jacobian<2><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
                                                      P.pair_slots, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mc,
-                                                     cf.c_conv, cf.c_visc, newton, A_out)),
+                                                     cf, fm, newton, A_out)),
             (k_momentum_jacobian<3><<<B, T, 0, st>>>(P.nrows, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
                                                      P.pair_slots, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mc,
-                                                     cf.c_conv, cf.c_visc, newton, A_out)));
+                                                     cf, fm, newton, A_out)));
         NSB_LAUNCH_CHECK(ctx, "k_momentum_jacobian");
     }
     return 0;
@@ -762,16 +642,32 @@ extern "C" int nsb_assemble_mixed(nsb_ctx* ctx, int32_t flags, const double* w0,
     NSB_REQUIRE(ctx, !symbc || (ctx->w_bc_mask && ctx->w_bc_g), "symmetric BC elimination needs nsb_set_mixed_bc");
     cudaStream_t st = (cudaStream_t)stream;
     const int T = 128, B = nsb_blocks(P.nrows, T);
+    nsb_forms fm;
+    fm.conv = ctx->form_conv; fm.visc = ctx->form_visc;
+    for (int i = 0; i < 3; ++i) fm.cor[i] = ctx->coriolis[i];
     nsb_timed_region mixed_region(ctx, do_mat ? NSB_T_ASM_JAC : NSB_T_ASM_RES, st);
     NSB_DIM_DISPATCH(ctx,
         (k_mixed_rows<2><<<B, T, 0, st>>>(P.nrows, do_vec, do_mat, newton, bdf, symbc, P.rowptr, P.pair_ptr,
                                           P.pair_cell, P.pair_iloc, P.pair_slots, ctx->coords, ctx->cell_verts,
-                                          ctx->cell_dofs_w, w0, w1, w2, ctx->w_bc_mask, ctx->w_bc_g, ctx->coef,
+                                          ctx->cell_dofs_w, w0, w1, w2, ctx->w_bc_mask, ctx->w_bc_g, ctx->coef, fm,
                                           b_out, A_out)),
         (k_mixed_rows<3><<<B, T, 0, st>>>(P.nrows, do_vec, do_mat, newton, bdf, symbc, P.rowptr, P.pair_ptr,
                                           P.pair_cell, P.pair_iloc, P.pair_slots, ctx->coords, ctx->cell_verts,
-                                          ctx->cell_dofs_w, w0, w1, w2, ctx->w_bc_mask, ctx->w_bc_g, ctx->coef,
+                                          ctx->cell_dofs_w, w0, w1, w2, ctx->w_bc_mask, ctx->w_bc_g, ctx->coef, fm,
                                           b_out, A_out)));
     NSB_LAUNCH_CHECK(ctx, "k_mixed_rows");
+    return 0;
+}
+
+// weak-form variants (source/ns_solver_base.py:78-115 constructor arguments form_convective_term / form_viscous_term,
+// :173-191 Coriolis term): conv 0 standard | 1 rotational | 2 divergence | 3 skew_symmetric; visc 0 reduced | 1 traction;
+// coriolis3 = 2 c_Omega Omega (2D: only [2]); generic != 0 forces the generic row kernels for the default form too
+extern "C" int nsb_set_forms(nsb_ctx* ctx, int32_t conv, int32_t visc, const double* coriolis3, int32_t generic) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, conv >= 0 && conv <= 3 && (visc == 0 || visc == 1), "unknown weak-form variant");
+    ctx->form_conv = conv;
+    ctx->form_visc = visc;
+    for (int i = 0; i < 3; ++i) ctx->coriolis[i] = coriolis3 ? coriolis3[i] : 0.0;
+    ctx->force_generic_assembly = generic != 0;
     return 0;
 }

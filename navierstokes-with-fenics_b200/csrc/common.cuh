@@ -142,6 +142,10 @@ struct nsb_ctx {
     const uint8_t* w_bc_mask = nullptr;
     const double* w_bc_g = nullptr;
     nsb_coef coef = {1.0, 1.0, -1.0, 0.0, 1.0, 1.0, 1.0, 1.0};
+    // weak-form variants (nsb_set_forms): convective form, viscous form, Coriolis vector 2 c_Omega Omega
+    int32_t form_conv = 0, form_visc = 0;
+    double coriolis[3] = {0.0, 0.0, 0.0};
+    bool force_generic_assembly = false;
     // reduction scratch (device) + pinned host mirror
     double* d_partials = nullptr;     // [NSB_MAX_PARTIALS * 8]
     double* d_scalars = nullptr;      // [64] device-resident Krylov scalars

@@ -327,6 +327,14 @@ class Device:
         self.check(self.lib.nsb_set_coefficients(self.ctx, arr))
         self.coef = tuple(arr)
 
+    def set_forms(self, conv=0, visc=0, coriolis=None, generic=False):
+        """weak-form variants (nsb_set_forms): conv 0 standard | 1 rotational | 2 divergence | 3 skew_symmetric,
+        visc 0 reduced | 1 traction, coriolis = 2 c_Omega Omega (3 components; 2D: only the last)"""
+        arr = None
+        if coriolis is not None:
+            arr = (C.c_double * 3)(*[float(v) for v in coriolis])
+        self.check(self.lib.nsb_set_forms(self.ctx, int(conv), int(visc), arr, 1 if generic else 0))
+
     # ---- assembly ---------------------------------------------------------------------------
     def assemble_ipcs_momentum(self, flags, ustar, un=None, unm1=None, pn=None, b=None, A=None):
         self.check(self.lib.nsb_assemble_ipcs_momentum(self.ctx, flags, _ptr(ustar), _ptr(un), _ptr(unm1),
@@ -498,6 +506,20 @@ class Device:
             self._mass_ops[space] = (M, dinv)
         return self._mass_ops[space]
 
+    def cell_rhs(self, fn, space, degree):
+        """b_I = int (I_k fn) phi_I dx over the owned rows of V (interleaved) or Q: right-hand side of a projection,
+        body-force load vector (source/ns_solver_base.py:158-171)"""
+        from . import lagrange
+        d = self.dim
+        ncomp = d if space == "V" else 1
+        which, pname = (L.PAT_P2P2, "P2P2") if space == "V" else (L.PAT_P1P1, "P1P1")
+        pat = self.pattern(pname)
+        F, nk = self._cell_lattice_values(fn, degree, ncomp)
+        R = self.upload(lagrange.cross_mass(d, "P2" if space == "V" else "P1", degree))
+        b = self.empty(pat.nrows * ncomp)
+        self.check(self.lib.nsb_assemble_cell_rhs(self.ctx, which, nk, ncomp, _ptr(R), _ptr(F), _ptr(b), self.stream))
+        return b
+
     def project(self, fn, space, degree, out=None, rtol=1e-14):
         """``dolfin.project(Expression(degree=degree), V|Q)`` (source/ns_solver_base.py:1151,1168): cell-wise P_k
         interpolant of ``fn``, exact right-hand side on the device, mass solve by Jacobi-CG (LU in the
@@ -507,13 +529,9 @@ class Device:
         d = self.dim
         ncomp = d if space == "V" else 1
         which, pname, halo = (L.PAT_P2P2, "P2P2", L.HALO_NODES) if space == "V" else (L.PAT_P1P1, "P1P1", L.HALO_VERTS)
-        self.pattern(pname)
-        F, nk = self._cell_lattice_values(fn, degree, ncomp)
-        R = self.upload(lagrange.cross_mass(d, "P2" if space == "V" else "P1", degree))
+        b = self.cell_rhs(fn, space, degree)
         M, dinv = self.mass_operator(space)
         n_own = M.nrows * M.bs
-        b = self.empty(n_own)
-        self.check(self.lib.nsb_assemble_cell_rhs(self.ctx, which, nk, ncomp, _ptr(R), _ptr(F), _ptr(b), self.stream))
         n_all = (self.spaces.n_nodes * d) if space == "V" else self.spaces.n_vertices
         x = self.zeros(n_all) if out is None else out
         x[:n_own].zero_()

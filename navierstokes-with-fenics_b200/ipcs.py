@@ -46,14 +46,14 @@ class IPCSSolver(SolverBase):
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
                  momentum_preconditioner="chebyshev", chebyshev_degree=8, chebyshev_ratio=30.0, partition=None,
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
-                 pressure_chebyshev_ratio=300.0, pressure_solve="auto"):
+                 pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard"):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
         [owned | ghost] entries, every linear system lives on the owned entries."""
         if partition is not None:
             mesh, boundary_markers = partition.mesh, partition.mesh.bfacet_marker
-        super().__init__(mesh, boundary_markers, form_convective_term)
+        super().__init__(mesh, boundary_markers, form_convective_term, form_viscous_term)
         assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
         assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
         self._time_stepping = time_stepping
@@ -282,6 +282,8 @@ class IPCSSolver(SolverBase):
         if not self._bc_ready:
             self._setup_boundary_conditions()
         self._set_time(self._time_stepping.next_time)
+        self._apply_forms(self.dev)
+        self._load = self._external_load(self.dev)
         self.h2d_bytes = self._update_bc_values(force=upload_bcs)
         self._update_time_stepping_coefficients()
         if not (self._have_constant and self._cache):
@@ -292,6 +294,8 @@ class IPCSSolver(SolverBase):
         dev = self.dev
         dev.assemble_ipcs_momentum(L.VEC, self._intermediate_velocity, self._velocities[1], self._velocities[2],
                                    self._old_pressure, b=self._bV)
+        if getattr(self, "_load", None) is not None:      # F += -c_b int f.w dx + int_Gamma t.w ds
+            dev.axpy(1.0, self._load[:self._nV_own], self._bV)
         dev.bc_apply_vector(L.BC_NEWTON, self._bV, self._vbc_dofs, self._vbc_vals, x=self._intermediate_velocity)
         return dev.norm(self._bV)
 

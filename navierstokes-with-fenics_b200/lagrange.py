@@ -15,7 +15,7 @@ from math import factorial
 
 import numpy as np
 
-UFC_EDGES = {2: ((1, 2), (0, 2), (0, 1)), 3: ((2, 3), (1, 3), (1, 2), (0, 3), (0, 2), (0, 1))}
+UFC_EDGES = {1: ((0, 1),), 2: ((1, 2), (0, 2), (0, 1)), 3: ((2, 3), (1, 3), (1, 2), (0, 3), (0, 2), (0, 1))}
 
 
 # ---- multi-indices / lattice nodes ------------------------------------------------------------

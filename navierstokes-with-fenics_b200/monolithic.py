@@ -14,12 +14,12 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged
 
 class MixedSolverBase(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=1,
-                 linear_solver="auto", linear_rtol=1e-12, gmres_restart=60):
+                 linear_solver="auto", linear_rtol=1e-12, gmres_restart=60, form_viscous_term="standard"):
         """``linear_solver`` (K16, the Newton update the reference hands to sparse LU): "gmres" = hand-written
         flexible GMRES with the block-triangular Cahouet-Chabard preconditioner (csrc/krylov.cu saddle_apply);
         "direct" = cuSOLVER sparse QR (library leg); "auto" = direct below 20 000 dofs and for stationary problems
         (no mass term: the Schur complement approximation degrades with the Reynolds number), gmres otherwise."""
-        super().__init__(mesh, boundary_markers, form_convective_term)
+        super().__init__(mesh, boundary_markers, form_convective_term, form_viscous_term)
         assert linear_solver in ("auto", "gmres", "direct")
         self._linear_solver, self._linear_rtol, self._gmres_restart = linear_solver, linear_rtol, gmres_restart
         self.krylov_iterations, self.inner_iterations = [], 0
@@ -94,6 +94,18 @@ class MixedSolverBase(SolverBase):
         if not converged and error_on_nonconvergence:
             raise NewtonNotConverged("Newton solver did not converge (%d iterations, residual %g)" % (it, r))
         return it
+
+    def _prepare_forms_and_load(self):
+        """weak-form switches to the device; external load (body force, tractions) scattered into W numbering"""
+        dev = self.dev
+        self._apply_forms(dev)
+        load = self._external_load(dev)
+        self._loadW = None
+        if load is not None:
+            if not hasattr(self, "_loadW_buf"):
+                self._loadW_buf = dev.zeros(self._nW)
+            dev.scatter(self._maps()[0], load, self._loadW_buf)
+            self._loadW = self._loadW_buf
 
     # ---- K16: hand-written Krylov solve of the Newton update ---------------------------------------
     _mass_coefficient = 0.0      # alpha0 / k of the Jacobian's mass term; set by the instationary mirror

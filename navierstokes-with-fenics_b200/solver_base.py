@@ -28,12 +28,27 @@ class PressureBCType(Enum):
     mean_value = auto()
 
 
+class TractionBCType(Enum):
+    """source/ns_solver_base.py:32-37"""
+    constant = auto()
+    constant_component = auto()
+    function = auto()
+    function_component = auto()
+    free = auto()
+
+
 class WeakFormConvectiveTerm(Enum):
-    """source/ns_solver_base.py:39-48 (only the standard form is on the GPU path so far)"""
+    """source/ns_solver_base.py:39-48; the enum order is the ``conv`` code of nsb_set_forms"""
     standard_form = auto()
     rotational_form = auto()
     divergence_form = auto()
     skew_symmetric_form = auto()
+
+
+class WeakFormViscousTerm(Enum):
+    """source/ns_solver_base.py:51-56"""
+    reduced_form = auto()
+    traction_form = auto()
 
 
 class Expression:
@@ -61,13 +76,17 @@ class SolverBase:
     """Common part of the three solver mirrors: BC tuples -> (marker, comp, value) tables,
     coefficient dictionary (source/ns_solver_base.py:722-827, :828-857)."""
 
-    def __init__(self, mesh, boundary_markers, form_convective_term="standard"):
+    def __init__(self, mesh, boundary_markers, form_convective_term="standard", form_viscous_term="standard"):
+        """source/ns_solver_base.py:78-115: ``form_convective_term`` in {"standard", "rotational", "divergence",
+        "skew_symmetric"}, ``form_viscous_term`` in {"standard", "reduced", "traction"}"""
         assert isinstance(mesh, SimplexMesh)
         if isinstance(form_convective_term, str):
             form_convective_term = WeakFormConvectiveTerm[form_convective_term.lower() + "_form"] \
                 if not form_convective_term.endswith("_form") else WeakFormConvectiveTerm[form_convective_term]
-        if form_convective_term is not WeakFormConvectiveTerm.standard_form:
-            raise NotImplementedError("only the standard convective form is implemented on the GPU path")
+        if isinstance(form_viscous_term, str):
+            form_viscous_term = WeakFormViscousTerm.traction_form if form_viscous_term.lower().startswith("traction") \
+                else WeakFormViscousTerm.reduced_form
+        self._form_convective_term, self._form_viscous_term = form_convective_term, form_viscous_term
         self._mesh = mesh
         self._boundary_markers = boundary_markers
         self._space_dim = mesh.dim
@@ -82,7 +101,7 @@ class SolverBase:
         assert isinstance(bcs, (list, tuple))
         assert internal_constraints is None, "internal constraints are not on the GPU path"
         ids = self._mesh.boundary_ids()
-        vel, prs = [], []
+        vel, prs, trc = [], [], []
         d = self._space_dim
         for bc in bcs:
             assert isinstance(bc, tuple) and len(bc) in (3, 4)
@@ -114,9 +133,24 @@ class SolverBase:
                 else:
                     assert bid in ids, "unknown boundary id %r" % (bid,)
                     prs.append((bid, "p", bc[2] if callable(bc[2]) else float(bc[2])))
+            elif isinstance(kind, TractionBCType):
+                assert bid in ids, "unknown boundary id %r" % (bid,)
+                if kind is TractionBCType.free:
+                    continue
+                if kind in (TractionBCType.constant, TractionBCType.function):
+                    assert len(bc) == 3
+                    trc.append((bid, None, bc[2] if callable(bc[2]) else tuple(float(v) for v in bc[2])))
+                else:
+                    assert len(bc) == 4 and 0 <= bc[2] < d
+                    trc.append((bid, int(bc[2]), bc[3] if callable(bc[3]) else float(bc[3])))
             else:
-                raise NotImplementedError("traction boundary conditions are not on the GPU path")
+                raise TypeError("unknown boundary condition type %r" % (kind,))
         self._velocity_bcs, self._pressure_bcs = vel, prs
+        if trc:
+            # source/ns_solver_base.py:823-825 (quirk Q12): any traction BC switches the viscous term to its traction form
+            self._traction_bcs = trc
+            self._form_viscous_term = WeakFormViscousTerm.traction_form
+            self._forms_dirty = True
 
     def _planar_normal_axis(self, bid):
         """``boundary_normal`` (source/auxiliary_methods.py:8-53) for axis-aligned planes."""
@@ -129,9 +163,66 @@ class SolverBase:
 
     def _set_time(self, t):
         """source/ns_solver_base.py:1033-1104: every Expression gets time = next_time."""
-        for _, _, v in self._velocity_bcs + self._pressure_bcs:
+        for _, _, v in self._velocity_bcs + self._pressure_bcs + getattr(self, "_traction_bcs", []):
             if isinstance(v, Expression):
                 v.time = t
+        if isinstance(getattr(self, "_body_force", None), Expression):
+            self._body_force.time = t
+        if callable(getattr(self, "_angular_velocity", None)):
+            self._omega_now = self._angular_velocity(t)
+            self._forms_dirty = True
+
+    # ---- body force, Coriolis term, weak-form switches ----------------------------------------------
+    def set_body_force(self, body_force):
+        """source/ns_solver_base.py:711-720: an Expression (vector valued) or a tuple of floats"""
+        assert isinstance(body_force, Expression) or len(body_force) == self._space_dim
+        self._body_force = body_force
+        self._load_vector = None
+
+    def set_angular_velocity(self, omega):
+        """rotating frame (source/ns_solver_base.py:173-191): ``omega`` = Omega_z (2D) or a 3-vector, or a callable
+        of time returning one; the Coriolis term 2 c_Omega Omega x u needs ``coriolis_term`` among the coefficients"""
+        self._angular_velocity = omega
+        self._omega_now = omega(0.0) if callable(omega) else omega
+        self._forms_dirty = True
+
+    def _apply_forms(self, dev):
+        """hand the weak-form switches to the device (nsb_set_forms) when they changed"""
+        if not getattr(self, "_forms_dirty", True):
+            return
+        cor = None
+        c_cor = self._equation_coefficients.get("coriolis_term")
+        if getattr(self, "_omega_now", None) is not None and c_cor is not None:
+            om = np.atleast_1d(np.asarray(self._omega_now, dtype=np.float64))
+            om3 = np.zeros(3)
+            om3[2 if len(om) == 1 else slice(0, 3)] = om
+            cor = 2.0 * c_cor * om3
+        dev.set_forms(self._form_convective_term.value - 1, self._form_viscous_term.value - 1, cor)
+        self._forms_dirty = False
+
+    def _external_load(self, dev):
+        """V-numbered load vector  -c_b int f.w dx + int_Gamma t.w ds  (source/ns_solver_base.py:121-171), or None.
+        The body force is integrated on the device (cell-wise P_k interpolant, csrc/project.cu); boundary tractions
+        live on O(boundary) facets and are integrated on the host like every other boundary datum."""
+        f, trc = getattr(self, "_body_force", None), getattr(self, "_traction_bcs", None)
+        if f is None and not trc:
+            return None
+        timedep = isinstance(f, Expression) or any(isinstance(v, Expression) for _, _, v in (trc or []))
+        if getattr(self, "_load_vector", None) is not None and not timedep:
+            return self._load_vector
+        sp, d = dev.spaces, dev.dim
+        load = dev.zeros(sp.ndofs_V)
+        if f is not None:
+            c_b = self._equation_coefficients["body_force_term"]
+            assert c_b is not None, "set_body_force needs the body_force_term coefficient"
+            fn = f if isinstance(f, Expression) else (lambda x: np.broadcast_to(np.asarray(f, dtype=np.float64), (len(x), d)))
+            rhs = dev.cell_rhs(fn, "V", f.degree if isinstance(f, Expression) else 1)
+            dev.axpy(-c_b, rhs, load[:rhs.numel()])
+        if trc:
+            from .tractions import traction_load
+            load += dev.upload(traction_load(sp, trc))
+        self._load_vector = load
+        return load
 
     # ---- coefficients ---------------------------------------------------------------------------
     def set_equation_coefficients(self, coefficients):
@@ -140,9 +231,11 @@ class SolverBase:
         for key, value in coefficients.items():
             assert key in ("convective_term", "coriolis_term", "euler_term", "pressure_term",
                            "viscous_term", "body_force_term")
-            if key in ("coriolis_term", "euler_term"):
-                assert value is None, "rotating-frame terms are not on the GPU path"
+            if key == "euler_term":
+                assert value is None, "the Euler acceleration (time-dependent Omega) is not on the GPU path"
                 continue
+            if key == "coriolis_term":
+                self._forms_dirty = True
             if value is not None:
                 assert isinstance(value, float) and math.isfinite(value) and value > 0.0
             self._equation_coefficients[key] = value

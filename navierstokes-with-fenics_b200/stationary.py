@@ -13,8 +13,10 @@ from .monolithic import MixedSolverBase
 
 class StationarySolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", tol=1e-10, maxiter=50,
-                 tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12):
-        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol)
+                 tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12,
+                 form_viscous_term="standard"):
+        super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol,
+                         form_viscous_term=form_viscous_term)
         assert isinstance(maxiter, int) and maxiter > 0 and isinstance(tol, float) and tol > 0.0
         assert isinstance(maxiter_picard, int) and maxiter_picard > 0 and isinstance(tol_picard, float)
         self._tol, self._maxiter = tol, maxiter
@@ -29,6 +31,10 @@ class StationarySolver(MixedSolverBase):
         returns ||b||"""
         flags = L.VEC | L.SYMBC | (L.PICARD if picard else 0) | (L.MAT if matrix else 0)
         self.dev.assemble_mixed(flags, self._solution, b=self._b, A=self._A if matrix else None)
+        if self._loadW is not None:
+            # the external load enters b_e linearly and the local elimination overwrites only Dirichlet rows:
+            # adding the global load on all other rows equals assembling it cell by cell
+            self.dev.axpy(1.0, self._loadW, self._b)
         return self.dev.norm(self._b)
 
     def solve(self):
@@ -38,6 +44,10 @@ class StationarySolver(MixedSolverBase):
             self.dev.set_coefficients(1.0, (1.0, -1.0, 0.0), co["convective_term"], co["pressure_term"],
                                       co["viscous_term"])
             self._setup_boundary_conditions()
+        self._prepare_forms_and_load()
+        if self._loadW is not None:
+            self._loadW = self._loadW.clone()
+            self._loadW[self._bc_dofs.long()] = 0.0          # setup-time masking of the Dirichlet rows
         residual = self._system(True, False)
         if residual < self._tol_picard:          # :966-970: lower the Picard tolerance below the start residual
             order = math.floor(math.log10(residual))

@@ -37,6 +37,10 @@ class Assembler:
         self.phi2, self.dphi2 = fem.tabulate_p2(self.qp)
         self.phi1, self.dphi1 = fem.tabulate_p1(self.qp)
         self._patterns = {}
+        # weak-form variants (source/ns_solver_base.py:78-115): restated at the quadrature points, term by term
+        self.conv_form = "standard"      # | "rotational" | "divergence" | "skew_symmetric"   (:370-390, :478-499)
+        self.visc_form = "reduced"       # | "traction"                                        (:662-673)
+        self.coriolis = None             # 2 c_Omega Omega as a 3-vector (2D: only [2]), :173-191
 
     # ---- patterns ---------------------------------------------------------------------------
     def pattern(self, name):
@@ -94,40 +98,102 @@ class Assembler:
         return w[self.sp.cell_dofs_W[s:e, d * nl:]]
 
     # ---- element tensors ------------------------------------------------------------------------
+    @staticmethod
+    def _pad3(x, axis):
+        """embed a 2-vector index into 3D (zero z component)"""
+        if x.shape[axis] == 3:
+            return x
+        pad = [(0, 0)] * x.ndim
+        pad[axis] = (0, 1)
+        return np.pad(x, pad)
+
+    _EPS = np.zeros((3, 3, 3))
+    for _i, _j, _k in ((0, 1, 2), (1, 2, 0), (2, 0, 1)):
+        _EPS[_i, _j, _k], _EPS[_i, _k, _j] = 1.0, -1.0
+
+    def _cross_matrix(self):
+        """X[b,k] with (Omega x u)_b = X[b,k] u_k, restricted to the mesh dimension"""
+        om = np.asarray(self.coriolis, dtype=np.float64)
+        X = np.einsum("bik,i->bk", self._EPS, om)
+        return X[:self.d, :self.d]
+
     def _momentum_residual(self, wdet, G2, G1, U, Uacc, P, c_conv, c_p, c_visc, inv_k):
-        """F[c,I,b] of  (acc.w)/k + c_c (grad(u) u).w - c_p div(w) p + c_nu grad(u):grad(w).
+        """F[c,I,b] of  (acc.w)/k + c_c conv(u).w - c_p div(w) p + c_nu visc(u,w)  [+ 2 c_Om (Om x u).w].
         Uacc = sum_i alpha_i U_i (or None for the stationary form); P[c,M] pressure dofs."""
         phi2, phi1 = self.phi2, self.phi1
+        d = self.d
         uq = np.einsum("qI,cIa->cqa", phi2, U)
         gu = np.einsum("cqIj,cIb->cqbj", G2, U)                            # d_j u_b
-        conv = np.einsum("cqbj,cqj->cqb", gu, uq)
-        pq = np.einsum("qM,cM->cq", phi1, P)
+        conv = np.einsum("cqbj,cqj->cqb", gu, uq)                          # dot(grad(u), u)
+        if self.conv_form == "rotational":                                 # cross(curl(u), u); 2D: (-curl u u_y, curl u u_x)
+            gu3, u3 = self._pad3(self._pad3(gu, 2), 3), self._pad3(uq, 2)
+            curl = np.einsum("imn,cqnm->cqi", self._EPS, gu3)
+            conv = np.einsum("bik,cqi,cqk->cqb", self._EPS, curl, u3)[:, :, :d]
+        elif self.conv_form == "divergence":
+            conv = conv + 0.5 * np.einsum("cqjj,cqb->cqb", gu, uq)
         F = c_conv * np.einsum("cq,cqb,qI->cIb", wdet, conv, phi2)
+        if self.conv_form == "skew_symmetric":                            # 1/2 [conv.w - dot(dot(grad(w), u), u)]
+            F = 0.5 * F - 0.5 * c_conv * np.einsum("cq,cqIj,cqj,cqb->cIb", wdet, G2, uq, uq)
+        pq = np.einsum("qM,cM->cq", phi1, P)
         F -= c_p * np.einsum("cq,cq,cqIb->cIb", wdet, pq, G2)
-        F += c_visc * np.einsum("cq,cqbj,cqIj->cIb", wdet, gu, G2)
+        if self.visc_form == "traction":                                   # (grad u + grad u^T) : 1/2 (grad w + grad w^T)
+            F += c_visc * np.einsum("cq,cqbj,cqIj->cIb", wdet, gu + np.swapaxes(gu, 2, 3), G2)
+        else:
+            F += c_visc * np.einsum("cq,cqbj,cqIj->cIb", wdet, gu, G2)
+        if self.coriolis is not None:
+            F += np.einsum("cq,bk,cqk,qI->cIb", wdet, self._cross_matrix(), uq, phi2)
         if Uacc is not None:
             aq = np.einsum("qI,cIa->cqa", phi2, Uacc)
             F += inv_k * np.einsum("cq,cqb,qI->cIb", wdet, aq, phi2)
         return F
 
     def _momentum_jacobian(self, wdet, G2, U, c_conv, c_visc, mass_coef, newton=True):
-        """A[c,I,b,J,a] = delta_ab (mass_coef phi_I phi_J + c_c (u.grad phi_J) phi_I
-        + c_nu grad phi_I.grad phi_J) + [newton] c_c phi_J (d_a u_b) phi_I."""
+        """A[c,I,b,J,a]: derivative of the residual w.r.t. the coefficient of phi_J e_a (newton) or the reference's
+        Picard linearisation with the convecting velocity frozen (source/ns_solver_base.py:478-499)."""
         phi2 = self.phi2
         d = self.d
+        nl = phi2.shape[1]
+        eye = np.eye(d)
         uq = np.einsum("qI,cIa->cqa", phi2, U)
-        adv = np.einsum("cqJj,cqj->cqJ", G2, uq)                            # u.grad phi_J
-        S = c_conv * np.einsum("cq,qI,cqJ->cIJ", wdet, phi2, adv)
-        S += c_visc * np.einsum("cq,cqIj,cqJj->cIJ", wdet, G2, G2)
+        gu = np.einsum("cqIj,cIb->cqbj", G2, U)                            # d_j u_b
+        adv = np.einsum("cqJj,cqj->cqJ", G2, uq)                           # u . grad phi_J
+        mI_adv = np.einsum("cq,qI,cqJ->cIJ", wdet, phi2, adv)              # int (u.grad phi_J) phi_I
+        mIJ_gu = np.einsum("cq,qI,qJ,cqba->cIbJa", wdet, phi2, phi2, gu)   # int phi_J (d_a u_b) phi_I
+        A = np.zeros((U.shape[0], nl, d, nl, d))
+        form = self.conv_form
+        if form == "standard":
+            A += np.einsum("cIJ,ba->cIbJa", mI_adv, eye)
+            if newton:
+                A += mIJ_gu
+        elif form == "divergence":
+            divu = np.einsum("cqjj->cq", gu)
+            A += np.einsum("cIJ,ba->cIbJa", mI_adv + 0.5 * np.einsum("cq,cq,qI,qJ->cIJ", wdet, divu, phi2, phi2), eye)
+            if newton:
+                A += mIJ_gu + 0.5 * np.einsum("cq,cqJa,cqb,qI->cIbJa", wdet, G2, uq, phi2)
+        elif form == "skew_symmetric":
+            A += 0.5 * np.einsum("cIJ,ba->cIbJa", mI_adv - np.swapaxes(mI_adv, 1, 2), eye)
+            if newton:
+                A += 0.5 * mIJ_gu - 0.5 * np.einsum("cq,cqIa,qJ,cqb->cIbJa", wdet, G2, phi2, uq)
+        elif form == "rotational":
+            gu3, u3 = self._pad3(self._pad3(gu, 2), 3), self._pad3(uq, 2)
+            curl = np.einsum("imn,cqnm->cqi", self._EPS, gu3)
+            # cross(curl(u), v):  eps[b,i,a] curl_i phi_J
+            A += np.einsum("cq,bia,cqi,qI,qJ->cIbJa", wdet, self._EPS, curl, phi2, phi2)[:, :, :d, :, :d]
+            if newton:
+                # cross(curl(v), u), v = phi_J e_a:  curl(v)_i = eps[i,m,a] d_m phi_J
+                G3 = self._pad3(G2, 3)
+                A += np.einsum("cq,bik,ima,cqJm,cqk,qI->cIbJa", wdet, self._EPS, self._EPS, G3, u3, phi2)[:, :, :d, :, :d]
+        else:
+            raise ValueError(form)
+        A *= c_conv
+        S = c_visc * np.einsum("cq,cqIj,cqJj->cIJ", wdet, G2, G2)
         if mass_coef != 0.0:
             S += mass_coef * np.einsum("cq,qI,qJ->cIJ", wdet, phi2, phi2)
-        nl = phi2.shape[1]
-        A = np.zeros((U.shape[0], nl, d, nl, d))
-        for a in range(d):
-            A[:, :, a, :, a] = S
-        if newton:
-            gu = np.einsum("cqIj,cIb->cqbj", G2, U)                        # d_j u_b
-            A += c_conv * np.einsum("cq,qI,qJ,cqba->cIbJa", wdet, phi2, phi2, gu)
+        A += np.einsum("cIJ,ba->cIbJa", S, eye)
+        if self.visc_form == "traction":
+            A += c_visc * np.einsum("cq,cqIa,cqJb->cIbJa", wdet, G2, G2)
+        if self.coriolis is not None:
+            A += np.einsum("cq,ba,qI,qJ->cIbJa", wdet, self._cross_matrix(), phi2, phi2)
         return A
 
     def _div_block(self, wdet, G2, c_p):

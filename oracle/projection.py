@@ -46,6 +46,63 @@ def _physical(mesh, ref_points):
     return np.einsum("km,cmi->cki", lam, mesh.coords[mesh.cells])
 
 
+def rhs_vector(asm, f, space, degree):
+    """b_I = int (I_k f) phi_I dx in V (interleaved) / Q numbering: right-hand side of ``project`` and, with
+    the factor -c_b, the body-force term of source/ns_solver_base.py:158-171"""
+    s, m = asm.sp, asm.sp.mesh
+    d = m.dim
+    el = LagrangeElement(d, degree)
+    ncomp = d if space == "V" else 1
+    F = np.asarray(f(_physical(m, el.nodes).reshape(-1, d)), dtype=np.float64).reshape(m.num_cells, len(el.nodes), ncomp)
+    qp, qw = fem.simplex_quadrature(d, degree + 2)
+    psi = el.tabulate(qp)
+    phi = fem.tabulate_p2(qp)[0] if space == "V" else fem.tabulate_p1(qp)[0]
+    be = np.einsum("c,q,qI,qJ,cJk->cIk", asm.detJ, qw, phi, psi, F)
+    if space == "V":
+        b = np.zeros((s.n_nodes, d))
+        np.add.at(b, s.cell_nodes, be)
+        return b.reshape(-1)
+    b = np.zeros(s.ndofs_Q)
+    np.add.at(b, s.cell_dofs_Q, be[:, :, 0])
+    return b
+
+
+def traction_vector(asm, traction_bcs):
+    """int_Gamma t . w ds (source/ns_solver_base.py:121-156), facet by facet: ``traction_bcs`` = [(marker, comp or
+    None, value, degree)], value a callable x[n,d] -> [n, d] / [n] or a constant (tuple); V numbering"""
+    s, m = asm.sp, asm.sp.mesh
+    d = m.dim
+    verts = np.zeros((d + 1, d))
+    verts[1:, :] = np.eye(d)
+    load = np.zeros((s.n_nodes, d))
+    for marker, comp, value, degree in traction_bcs:
+        el = LagrangeElement(d, degree)                       # the CELL's P_k interpolant, restricted to the facet
+        qp, qw = fem.simplex_quadrature(d - 1, degree + 2)
+        for f in np.nonzero(m.bfacet_marker == int(marker))[0]:
+            c = int(m.bfacet_cell[f])
+            cv = m.cells[c]
+            loc = [int(np.nonzero(cv == v)[0][0]) for v in m.bfacets[f]]
+            X = m.coords[cv]
+            lam_f = np.concatenate([1.0 - qp.sum(axis=1, keepdims=True), qp], axis=1)
+            ref = lam_f @ verts[loc]                           # facet quadrature points in the cell's reference frame
+            E = X[loc][1:] - X[loc][0]
+            meas = np.linalg.norm(E[0]) if d == 2 else np.linalg.norm(np.cross(E[0], E[1]))
+            lamc, _ = fem.barycentric(el.nodes)
+            xn = lamc @ X                                      # physical lattice nodes of the cell
+            ncomp = d if comp is None else 1
+            tn = np.asarray(value(xn), dtype=np.float64).reshape(len(xn), ncomp) if callable(value) else \
+                np.broadcast_to(np.asarray(value, dtype=np.float64).reshape(1, ncomp), (len(xn), ncomp))
+            tq = el.tabulate(ref) @ tn                         # [nq, ncomp]
+            phi = fem.tabulate_p2(ref)[0]                      # cell P2 basis on the facet (zero for off-facet nodes)
+            be = meas * np.einsum("q,qI,qk->Ik", qw, phi, tq)
+            nodes = s.cell_nodes[c]
+            if comp is None:
+                np.add.at(load, nodes, be)
+            else:
+                np.add.at(load[:, comp], nodes, be[:, 0])
+    return load.reshape(-1)
+
+
 def project(asm, f, space, degree):
     """L2 projection of the cell-wise degree-`degree` interpolant of f(x[n,d]) onto V (interleaved) or Q"""
     s, m = asm.sp, asm.sp.mesh

@@ -130,6 +130,7 @@ class IPCSOracle(_Base):
         self.linear_solver = "lu"          # "lu" (reference-faithful) | "krylov" / "krylov-c" (algorithm-matched)
         self.krylov_rtol = 1e-12
         self.krylov_iterations = []
+        self.load = None                   # V-numbered external load  -c_b int f.w + int_Gamma t.w ds, or callable(t)
 
     def _bcs_at(self, t):
         def bind(v):
@@ -160,8 +161,12 @@ class IPCSOracle(_Base):
         un, unm1, pn = self.velocities[1], self.velocities[2], self.old_pressure
 
         # (1) tentative velocity: Newton with NonlinearVariationalSolver BC semantics
+        load = self.load(t_next) if callable(self.load) else self.load
+
         def F(x):
             b = asm.ipcs_momentum_residual(x, un, unm1, pn, alpha, k, self.c_conv, self.c_p, self.c_visc)
+            if load is not None:
+                b = b + load
             return obc.apply_rhs_newton(b, x, vd, vv)
 
         def J(x):
@@ -229,6 +234,7 @@ class BDFOracle(_Base):
         self.solutions = [np.zeros(self.sp.ndofs_W) for _ in range(3)]
         self.velocity_bcs, self.pressure_bcs = list(velocity_bcs), list(pressure_bcs)
         self.tol, self.max_iter = tol, max_iter
+        self.load = None                   # V-numbered external load, or callable(t)
 
     def _bcs_at(self, t):
         def bind(v):
@@ -250,8 +256,12 @@ class BDFOracle(_Base):
         dofs, vals = self._bcs_at(t_next)
         w1, w2 = self.solutions[1], self.solutions[2]
 
+        load = self.load(t_next) if callable(self.load) else self.load
+
         def F(x):
             b = asm.mixed_residual(x, self.c_conv, self.c_p, self.c_visc, bdf=(alpha, k, w1, w2))
+            if load is not None:
+                b[self.sp.V_to_W] += load
             return obc.apply_rhs_newton(b, x, dofs, vals)
 
         def J(x):

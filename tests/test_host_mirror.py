@@ -50,8 +50,17 @@ def test_bc_tuple_translation_matches_reference_format():
     assert base._velocity_bcs[-1] == (1, 0, 0.0)          # planar normal of x = 0 is axis 0
     with pytest.raises(AssertionError):
         base.set_boundary_conditions([(V.no_slip, 9, None)])       # unknown boundary id
-    with pytest.raises(NotImplementedError):
-        nsb200.solver_base.SolverBase(m, markers, "rotational")
+    # every weak-form variant of the reference constructor is accepted (source/ns_solver_base.py:78-115)
+    W, Wv, T = nsb200.WeakFormConvectiveTerm, nsb200.WeakFormViscousTerm, nsb200.TractionBCType
+    for name, form in (("standard", W.standard_form), ("rotational", W.rotational_form), ("divergence", W.divergence_form),
+                       ("skew_symmetric", W.skew_symmetric_form)):
+        assert nsb200.solver_base.SolverBase(m, markers, name)._form_convective_term is form
+    other = nsb200.solver_base.SolverBase(m, markers, "standard", "traction")
+    assert other._form_viscous_term is Wv.traction_form
+    # a traction BC switches the viscous term to the traction form (quirk Q12, source/ns_solver_base.py:823-825)
+    base2 = nsb200.solver_base.SolverBase(m, markers, "standard")
+    base2.set_boundary_conditions([(V.no_slip, 3, None), (T.constant, 2, (1.0, 0.0)), (T.constant_component, 4, 1, 0.5)])
+    assert base2._form_viscous_term is Wv.traction_form and base2._traction_bcs == [(2, None, (1.0, 0.0)), (4, 1, 0.5)]
     base.set_equation_coefficients(dict(convective_term=1.0, viscous_term=0.01))
     with pytest.raises(AssertionError):
         base.set_equation_coefficients(dict(viscous_term=-1.0))
