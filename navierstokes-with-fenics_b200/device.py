@@ -554,8 +554,9 @@ class Device:
         Psi = lagrange.eval_lagrange(d, k, Xq)
         work = self.empty(F.numel())
         out = C.c_double()
-        self.check(self.lib.nsb_cell_error_norm2(self.ctx, which, ncomp, _ptr(uh), nk, _ptr(self.upload(E)), len(Wq),
-                                                 _ptr(self.upload(Psi)), _ptr(self.upload(Wq)), _ptr(F), _ptr(work),
+        tabs = (self.upload(E), self.upload(Psi), self.upload(Wq))       # named: they must outlive the launch
+        self.check(self.lib.nsb_cell_error_norm2(self.ctx, which, ncomp, _ptr(uh), nk, _ptr(tabs[0]), len(Wq),
+                                                 _ptr(tabs[1]), _ptr(tabs[2]), _ptr(F), _ptr(work),
                                                  C.byref(out), self.stream))
         return float(np.sqrt(max(out.value, 0.0)))
 

@@ -253,7 +253,10 @@ def test_ipcs_steps_match_oracle(case, flow):
         o_vel = [(w, None, (0.0,) * d) for w in walls] + [(4, None, lid)]
         o_prs = []
     ts = nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=dt)
-    solver = nsb200.IPCSSolver(m, m.bfacet_marker, "standard", ts, tol=1e-10, max_iter=50)
+    # linear_atol_factor = 0.01: the last Newton update is solved two digits below the default, so that the pressure
+    # (which amplifies the O(1e-12 r0) difference between two converged Newton iterates by alpha0 / k and 1 / h) meets
+    # the same 1e-8 bar as the velocity; tests/test_gpu_scale.py measures both settings side by side
+    solver = nsb200.IPCSSolver(m, m.bfacet_marker, "standard", ts, tol=1e-10, max_iter=50, linear_atol_factor=0.01)
     solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / Re))
     solver.set_boundary_conditions(bcs)
     orc = oracle.solvers.IPCSOracle(om, Re, o_vel, o_prs, tol=1e-10, max_iter=50)
@@ -267,7 +270,7 @@ def test_ipcs_steps_match_oracle(case, flow):
         u, p = solver.velocity.cpu().numpy(), solver.pressure.cpu().numpy()
         assert rel_max_err(u, orc.velocities[0]) < 1e-8, "velocity, step %d" % step
         if flow == "cavity":      # pressure up to a constant (H4): both carry the zero-mean representative
-            assert rel_max_err(p - p.mean(), orc.pressure - orc.pressure.mean()) < 1e-7
+            assert rel_max_err(p - p.mean(), orc.pressure - orc.pressure.mean()) < 1e-8
         else:
             assert rel_max_err(p, orc.pressure) < 1e-8, "pressure, step %d" % step
         assert solver.newton_iterations[-1] == orc.newton_iterations[-1]
