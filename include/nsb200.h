@@ -99,6 +99,10 @@ typedef struct nsb_matrix {
                                 the diagonal of block ij (nsb_bsr_block_scalar_f32).  Read ONLY by the single-
                                 precision Chebyshev polynomial inside the flexible nsb_gmres (nsb_precond.lowp),
                                 in preference to vals32: 8 instead of 40 bytes per block entry */
+    const int16_t* col16;    /* dev [nnz] or NULL: column deltas col - row of a scalar CSR matrix (nsb_csr_compress).
+                                Together with vals32 (here: a float copy of the CSR values) read ONLY by the SpMVs
+                                inside the Chebyshev polynomial of the persistent CG kernel: 6 instead of 12 bytes per
+                                entry, so that the pressure operator stays L2-resident; the CG operator stays FP64 */
 } nsb_matrix;
 
 /* preconditioners of nsb_cg / nsb_gmres (K12) */
@@ -206,10 +210,11 @@ int nsb_sched_build(int32_t nrows, const int32_t* rowptr_host, const int32_t* pa
 int nsb_set_schedule(nsb_ctx* ctx, int32_t which, int32_t ngroups, int32_t group_max_entries,
                      const int32_t* group_row_dev, const int32_t* chunk_first_dev, const int32_t* round_ptr_dev,
                      const uint16_t* sched_dev);
-/* Caller-owned device workspace for the two-phase (element vectors per cell -> gather per row)
- * vector assembly kernels; needs ncells * NL2 * d doubles.  Without it the one-thread-per-row
- * kernels are used.  NULL / 0 unregisters. */
+/* Caller-owned device workspace of the two-phase assembly kernels (per-cell data -> gather per row): the
+ * residual needs ncells * NL2 * d doubles, the Jacobian pre-pass ncells * nsb_scratch_doubles_per_cell(d)
+ * (74 in 3D, 32 in 2D).  Without it the one-thread-per-row kernels are used.  NULL / 0 unregisters. */
 int nsb_set_scratch(nsb_ctx* ctx, double* scratch_dev, int64_t ndoubles);
+int nsb_scratch_doubles_per_cell(int32_t dim);
 /* mixed Taylor-Hood dof map [ncells x (d*NL2 + d+1)] (source/ns_solver_base.py:501-524) */
 int nsb_set_mixed_dofmap(nsb_ctx* ctx, int32_t ndofs, const int32_t* cell_dofs_dev);
 /* scalars: dlfn.Constant.assign of k, alpha_i (source/ns_ipcs_solver.py:210-227,
@@ -262,6 +267,10 @@ int nsb_set_mixed_bc(nsb_ctx* ctx, const uint8_t* bc_mask_dev, const double* bc_
 
 /* ---------------------------------------------------------------- linear algebra (K10-13) */
 int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void* stream);
+/* vals32_out[k] = (float) vals[k], col16_out[k] = col[k] - row(k) for a scalar CSR matrix; *overflow_out != 0 if some
+ * delta does not fit 16 bits (then leave nsb_matrix.col16 NULL) */
+int nsb_csr_compress(nsb_ctx* ctx, const nsb_matrix* A, float* vals32_out, int16_t* col16_out, int32_t* overflow_out,
+                     void* stream);
 /* inv_diag[i] = 1/A_ii (1 on masked rows): Jacobi preconditioner (K12) */
 int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_diag, void* stream);
 int64_t nsb_cg_workspace_doubles(int64_t n);

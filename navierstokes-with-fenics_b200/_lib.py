@@ -13,7 +13,7 @@ CSR, BSR = 0, 1
 BC_LINEAR, BC_NEWTON = 0, 1
 # entries per TMA tile of the bulk-copy SpMV kernels, keyed by (matrix kind, bs) (csrc/spmv_tma.cuh)
 TILE_ENTRIES = {(BSR, 3): 384, (BSR, 2): 768}
-SCHED_MAX_BLOCKS = 160     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
+SCHED_MAX_BLOCKS = 128     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
 TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
                  "krylov_vec", "dirichlet", "vector", "comm", "spmv_bsr_f32", "cg_persistent")
 HALO_NONE, HALO_NODES, HALO_VERTS = 0, 1, 2
@@ -29,7 +29,7 @@ class Matrix(C.Structure):
     """struct nsb_matrix"""
     _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
                 ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp), ("tiles", vp),
-                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp), ("diag32", vp)]
+                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp), ("diag32", vp), ("col16", vp)]
 
 
 class Saddle(C.Structure):
@@ -66,6 +66,7 @@ PROTOTYPES = {
     "nsb_sched_build": (C.c_int, [C.c_int32, vp, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]),
     "nsb_set_schedule": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp]),
     "nsb_set_scratch": (C.c_int, [vp, vp, C.c_int64]),
+    "nsb_scratch_doubles_per_cell": (C.c_int, [C.c_int32]),
     "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),
     "nsb_set_coefficients": (C.c_int, [vp, c_f64p]),
     "nsb_set_forms": (C.c_int, [vp, C.c_int32, C.c_int32, c_f64p, C.c_int32]),
@@ -78,6 +79,7 @@ PROTOTYPES = {
     "nsb_bc_apply_vector": (C.c_int, [vp, C.c_int32, vp, vp, C.c_int32, vp, vp, vp]),
     "nsb_set_mixed_bc": (C.c_int, [vp, vp, vp]),
     "nsb_spmv": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp]),
+    "nsb_csr_compress": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, c_i32p, vp]),
     "nsb_inv_diagonal": (C.c_int, [vp, C.POINTER(Matrix), vp, vp]),
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),

@@ -29,6 +29,8 @@ struct pcg_params {
     const int32_t* rowptr;
     const int32_t* col;
     const double* vals;
+    const float* vals32;       // optional single-precision copy of vals  } read ONLY by the SpMVs inside the Chebyshev
+    const int16_t* col16;      // optional column deltas col - row         } polynomial: 6 instead of 12 bytes per entry
     const uint8_t* mask;
     const double* dinv;
     const double* b;
@@ -80,32 +82,73 @@ __device__ __forceinline__ void grid_reduce(cg::grid_group& grid, double (&v)[NV
     for (int i = 0; i < NV; ++i) v[i] = smem[NV * NW + i];
 }
 
-// (A x)_row by PCG_LANES cooperating lanes; the result is valid in every lane of the group.  Every lane of the
-// warp calls it (row >= hi: contributes nothing) so that the shuffles of the group sum are warp-uniform.
-__device__ __forceinline__ double row_dot(const pcg_params& P, int32_t row, int32_t hi, int lane, const double* x) {
-    double acc = 0.0;
-    if (row < hi) {
-        const int32_t end = __ldg(P.rowptr + row + 1);
-        constexpr int U = 4;
-        for (int32_t s = __ldg(P.rowptr + row) + lane; s < end; s += PCG_LANES * U) {
-            double v[U];
-            int32_t cn[U];
+// One SpMV phase over the CTA's rows [lo, hi): PCG_LANES lanes per row, PCG_THREADS / PCG_LANES rows per pass.
+// The pass is software-pipelined: while the x values of pass k are gathered, the value / column entries of pass
+// k+1 and the row offsets of pass k+2 are already in flight, and so are the vector entries the epilogue of pass k
+// needs (pre()), so that a pass costs ONE memory latency instead of the chain offsets -> entries -> gather ->
+// epilogue operands.  VT = double | float (values), IT = int32_t (absolute columns) | int16_t (col - row).
+// post(row, (A x)_row, pre-loaded operands) runs in lane 0 of the row's group.
+template <typename VT, typename IT>
+struct RowEntries {
+    VT v[4];
+    int32_t c[4];
+};
+
+template <typename VT, typename IT>
+__device__ __forceinline__ void load_entries(const VT* __restrict__ vals, const IT* __restrict__ cols, int32_t row,
+                                             int32_t beg, int32_t end, int lane, RowEntries<VT, IT>& e) {
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int32_t ss = s + u * PCG_LANES;
-                const bool ok = ss < end;
-                v[u] = ok ? __ldg(P.vals + ss) : 0.0;
-                cn[u] = ok ? __ldg(P.col + ss) : row;
-            }
-            double xv[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) xv[u] = ldv(x + cn[u]);
-#pragma unroll
-            for (int u = 0; u < U; ++u) acc += v[u] * xv[u];
-        }
+    for (int u = 0; u < 4; ++u) {
+        const int32_t s = beg + lane + u * PCG_LANES;
+        const bool ok = s < end;
+        e.v[u] = ok ? __ldg(vals + s) : (VT)0;
+        if (sizeof(IT) == 2) e.c[u] = ok ? row + (int32_t)__ldg(cols + s) : row;
+        else e.c[u] = ok ? (int32_t)__ldg(cols + s) : row;
     }
-    __syncwarp();
-    return group_sum<PCG_LANES>(acc);       // one call site for the whole warp
+}
+
+template <typename VT, typename IT, typename Pre, typename Post>
+__device__ __forceinline__ void spmv_phase(const int32_t* __restrict__ rowptr, const VT* __restrict__ vals,
+                                           const IT* __restrict__ cols, const double* x, int32_t lo, int32_t hi, int grp,
+                                           int lane, Pre&& pre, Post&& post) {
+    constexpr int GROUPS = PCG_THREADS / PCG_LANES;
+    const int npass = (hi - lo + GROUPS - 1) / GROUPS;
+    auto offsets = [&](int k, int32_t& b, int32_t& e) {
+        const int32_t row = lo + grp + k * GROUPS;
+        if (k < npass && row < hi) { b = __ldg(rowptr + row); e = __ldg(rowptr + row + 1); }
+        else { b = 0; e = 0; }
+    };
+    int32_t beg_c, end_c, beg_n, end_n;
+    offsets(0, beg_c, end_c);
+    offsets(1, beg_n, end_n);
+    RowEntries<VT, IT> cur, nxt;
+    load_entries<VT, IT>(vals, cols, lo + grp, beg_c, end_c, lane, cur);
+    for (int k = 0; k < npass; ++k) {
+        const int32_t row = lo + grp + k * GROUPS;
+        const bool mine = row < hi && lane == 0;
+        // everything issued here is independent: one round trip per pass
+        double xv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) xv[u] = ldv(x + cur.c[u]);
+        auto operands = pre(row, mine);
+        load_entries<VT, IT>(vals, cols, row + GROUPS, beg_n, end_n, lane, nxt);
+        int32_t beg_nn, end_nn;
+        offsets(k + 2, beg_nn, end_nn);
+        double acc = 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc += (double)cur.v[u] * xv[u];
+        // rows longer than 4 * PCG_LANES entries (never on P1 meshes of bounded valence): plain tail loop
+        for (int32_t s = beg_c + lane + 4 * PCG_LANES; s < end_c; s += PCG_LANES) {
+            const int32_t cn = sizeof(IT) == 2 ? row + (int32_t)__ldg(cols + s) : (int32_t)__ldg(cols + s);
+            acc += (double)__ldg(vals + s) * ldv(x + cn);
+        }
+        __syncwarp();
+        acc = group_sum<PCG_LANES>(acc);
+        if (mine) post(row, acc, operands);
+        cur = nxt;
+        beg_c = beg_n; end_c = end_n;
+        beg_n = beg_nn; end_n = end_nn;
+    }
 }
 
 }  // namespace
@@ -117,7 +160,6 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
     const int32_t per = (n + (int32_t)gridDim.x - 1) / (int32_t)gridDim.x;
     const int32_t lo = min(n, (int32_t)blockIdx.x * per), hi = min(n, lo + per);
     const int lane = threadIdx.x % PCG_LANES, grp = threadIdx.x / PCG_LANES;
-    constexpr int GROUPS = PCG_THREADS / PCG_LANES;
     double* slot_a = P.partials;                       // 3 values
     double* slot_b = P.partials + 3 * (size_t)gridDim.x;   // 3 values (alternates with slot_a)
     const bool cheb = P.degree >= 2;
@@ -132,16 +174,21 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
     }
     // ---- r = (b - shift) - A x ; preconditioner start for the first iteration --------------------------
     double red[3] = {0.0, 0.0, 0.0};                   // rr, bb, rz (Jacobi)
-    for (int32_t row = lo + grp; row - grp < hi; row += GROUPS) {
-        double v = row_dot(P, row, hi, lane, P.x);
-        if (lane == 0 && row < hi) {
-            if (P.mask != nullptr && P.mask[row]) v = ldv(P.x + row);
-            const double bi = __ldg(P.b + row) - shift;
+    struct Op0 { double xi, bi, dinv; };
+    spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, P.x, lo, hi, grp, lane,
+        [&](int32_t row, bool mine) {
+            Op0 o = {0.0, 0.0, 0.0};
+            if (mine) { o.xi = ldv(P.x + row); o.bi = __ldg(P.b + row); o.dinv = __ldg(P.dinv + row); }
+            return o;
+        },
+        [&](int32_t row, double v, const Op0& o) {
+            if (P.mask != nullptr && P.mask[row]) v = o.xi;
+            const double bi = o.bi - shift;
             const double ri = bi - v;
             P.r[row] = ri;
             red[0] += ri * ri;
             red[1] += bi * bi;
-            const double di = __ldg(P.dinv + row) * ri;
+            const double di = o.dinv * ri;
             if (cheb) {
                 P.rc[row] = di;
                 const double d = di * P.inv_theta;
@@ -151,8 +198,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
                 P.z[row] = di;
                 red[2] += ri * di;
             }
-        }
-    }
+        });
     grid_reduce<3>(grid, red, slot_b, smem);
     double rr = red[0];
     const double bb = red[1];
@@ -171,20 +217,29 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
             for (int k = 1; k < P.degree; ++k) {
                 const double a = P.ca[k], bcoef = P.cb[k];
                 const bool last = k == P.degree - 1;
-                for (int32_t row = lo + grp; row - grp < hi; row += GROUPS) {
-                    double v = row_dot(P, row, hi, lane, dold);
-                    if (lane == 0 && row < hi) {
-                        const double dk = ldv(dold + row);
-                        if (P.mask != nullptr && P.mask[row]) v = dk;
-                        const double rci = ldv(P.rc + row) - __ldg(P.dinv + row) * v;
-                        const double dn = a * dk + bcoef * rci;
-                        const double zi = ldv(P.z + row) + dn;
-                        P.rc[row] = rci;
-                        dnew[row] = dn;
-                        P.z[row] = zi;
-                        if (last) s[0] += ldv(P.r + row) * zi;
+                struct OpC { double dk, rc, dinv, z, r; };
+                auto pre = [&](int32_t row, bool mine) {
+                    OpC o = {0.0, 0.0, 0.0, 0.0, 0.0};
+                    if (mine) {
+                        o.dk = ldv(dold + row); o.rc = ldv(P.rc + row); o.dinv = __ldg(P.dinv + row); o.z = ldv(P.z + row);
+                        if (last) o.r = ldv(P.r + row);
                     }
-                }
+                    return o;
+                };
+                auto post = [&](int32_t row, double v, const OpC& o) {
+                    if (P.mask != nullptr && P.mask[row]) v = o.dk;
+                    const double rci = o.rc - o.dinv * v;
+                    const double dn = a * o.dk + bcoef * rci;
+                    const double zi = o.z + dn;
+                    P.rc[row] = rci;
+                    dnew[row] = dn;
+                    P.z[row] = zi;
+                    if (last) s[0] += o.r * zi;
+                };
+                if (P.vals32 != nullptr && P.col16 != nullptr)
+                    spmv_phase<float, int16_t>(P.rowptr, P.vals32, P.col16, dold, lo, hi, grp, lane, pre, post);
+                else
+                    spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, dold, lo, hi, grp, lane, pre, post);
                 if (!last) grid.sync();
                 double* t = dold; dold = dnew; dnew = t;
             }
@@ -202,15 +257,18 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
         grid.sync();
         // q = A p ; p.q
         double s1[1] = {0.0};
-        for (int32_t row = lo + grp; row - grp < hi; row += GROUPS) {
-            double v = row_dot(P, row, hi, lane, P.p);
-            if (lane == 0 && row < hi) {
-                const double pi = ldv(P.p + row);
-                if (P.mask != nullptr && P.mask[row]) v = pi;
+        struct OpQ { double pi; };
+        spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, P.p, lo, hi, grp, lane,
+            [&](int32_t row, bool mine) {
+                OpQ o = {0.0};
+                if (mine) o.pi = ldv(P.p + row);
+                return o;
+            },
+            [&](int32_t row, double v, const OpQ& o) {
+                if (P.mask != nullptr && P.mask[row]) v = o.pi;
                 P.q[row] = v;
-                s1[0] += pi * v;
-            }
-        }
+                s1[0] += o.pi * v;
+            });
         grid_reduce<1>(grid, s1, slot_b, smem);
         const double pq = s1[0];
         const double alpha = pq != 0.0 ? rz / pq : 0.0;
@@ -279,6 +337,7 @@ int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     pcg_params P;
     memset(&P, 0, sizeof P);
     P.nrows = A->nrows; P.rowptr = A->rowptr; P.col = A->col; P.vals = A->vals; P.mask = A->bc_mask;
+    P.vals32 = A->vals32; P.col16 = A->col16;
     P.dinv = M->inv_diag; P.b = b; P.x = x;
     P.r = work; P.z = work + n; P.p = work + 2 * n; P.q = work + 3 * n; P.rc = work + 4 * n; P.d0 = work + 5 * n; P.d1 = work + 6 * n;
     P.partials = ctx->d_partials;
@@ -312,5 +371,36 @@ int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     if (resid_out) *resid_out = rnorm;
     if (!(rnorm == rnorm)) return nsb_fail(ctx, "CG breakdown: residual is NaN%s%s");
     if (rnorm > fmax(rtol * bnorm, atol)) return nsb_fail(ctx, "CG did not converge within the iteration limit%s%s");
+    return 0;
+}
+
+// single-precision values + 16-bit column deltas of a scalar CSR matrix (nsb_matrix.vals32 / col16): what the SpMVs
+// inside the Chebyshev polynomial of the persistent CG read.  flag_out[0] != 0 afterwards: some |col - row| > 32767,
+// the deltas are unusable (leave nsb_matrix.col16 NULL).
+__global__ void k_csr_compress(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                               const double* __restrict__ vals, float* __restrict__ vals32, int16_t* __restrict__ col16,
+                               int* flag) {
+    const int32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    for (int32_t s = rowptr[row]; s < rowptr[row + 1]; ++s) {
+        const int32_t d = col[s] - row;
+        if (d > 32767 || d < -32768) *flag = 1;
+        col16[s] = (int16_t)d;
+        vals32[s] = (float)vals[s];
+    }
+}
+
+extern "C" int nsb_csr_compress(nsb_ctx* ctx, const nsb_matrix* A, float* vals32_out, int16_t* col16_out, int32_t* overflow_out,
+                                void* stream) {
+    NSB_REQUIRE(ctx, ctx && A && A->kind == NSB_CSR && vals32_out && col16_out && overflow_out, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    int* flag = reinterpret_cast<int*>(ctx->d_counter + 1);
+    NSB_CUDA(ctx, cudaMemsetAsync(flag, 0, sizeof(int), st));
+    k_csr_compress<<<nsb_blocks(A->nrows, 256), 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->vals, vals32_out, col16_out, flag);
+    NSB_LAUNCH_CHECK(ctx, "k_csr_compress");
+    int h = 0;
+    NSB_CUDA(ctx, cudaMemcpyAsync(&h, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    NSB_CUDA(ctx, cudaStreamSynchronize(st));
+    *overflow_out = h;
     return 0;
 }

@@ -127,7 +127,7 @@ class Device:
         if patterns is None:
             patterns = ("WW",) if mixed else ("P2P2", "P1P1")
         if "P2P2" in patterns:
-            self.scratch = self.empty(mesh.num_cells * sp.nloc2 * sp.dim)
+            self.scratch = self.empty(mesh.num_cells * self.lib.nsb_scratch_doubles_per_cell(sp.dim))
             self.check(self.lib.nsb_set_scratch(self.ctx, _ptr(self.scratch), self.scratch.numel()))
         self.patterns = {}
         self.coef = None
@@ -306,7 +306,7 @@ class Device:
             self.patterns[name] = pat
         return self.patterns[name]
 
-    def matrix(self, pattern, vals, kind, bs, bc_mask=None, vals32=None, diag32=None):
+    def matrix(self, pattern, vals, kind, bs, bc_mask=None, vals32=None, diag32=None, compress=False):
         """nsb_matrix descriptor (keeps the tensors alive through attributes).  ``vals32``: float32
         copy of the BSR values for the SpMVs inside the Chebyshev preconditioner (``to_f32``);
         ``diag32``: one float per block, its block-scalar approximation (``block_scalar_f32``)."""
@@ -317,8 +317,16 @@ class Device:
                      tiles.data_ptr() if tiles is not None else None, ntiles,
                      getattr(pat, "halo", 0) if self.partition is not None else 0,
                      vals32.data_ptr() if vals32 is not None else None,
-                     diag32.data_ptr() if diag32 is not None else None)
+                     diag32.data_ptr() if diag32 is not None else None, None)
         m._keep = (pat, vals, bc_mask, tiles, vals32, diag32)
+        if compress and kind == L.CSR and bs == 1:
+            # float values + 16-bit column deltas for the polynomial SpMVs of the persistent CG (nsb_csr_compress)
+            v32, c16 = self.empty(pat.nnz, dtype=torch.float32), self.empty(pat.nnz, dtype=torch.int16)
+            over = C.c_int32()
+            self.check(self.lib.nsb_csr_compress(self.ctx, C.byref(m), _ptr(v32), _ptr(c16), C.byref(over), self.stream))
+            if over.value == 0:
+                m.vals32, m.col16 = v32.data_ptr(), c16.data_ptr()
+                m._keep = m._keep + (v32, c16)
         return m
 
     # ---- coefficients -----------------------------------------------------------------------

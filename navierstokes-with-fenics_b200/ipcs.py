@@ -234,13 +234,15 @@ class IPCSSolver(SolverBase):
         dev, d = self.dev, self.dev.dim
         dev.assemble_poisson(L.MAT, A=self._A_lap)
         dev.assemble_correction(L.MAT, A=self._A_mass)
-        self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pressure_dirichlet else None)
+        self._lap = dev.matrix("P1P1", self._A_lap, L.CSR, 1, self._maskQ if self._pressure_dirichlet else None,
+                               compress=dev.partition is None or dev.partition.nranks == 1)
         self._mass = dev.matrix("P2P2", self._A_mass, L.CSR, d, self._maskV)
         self._jac = dev.matrix("P2P2", self._A_mom, L.BSR, d, None, vals32=self._A_mom32, diag32=self._S_mom32)
         if self._p_replicated:          # the whole pressure operator on every rank (its own single-rank context)
             pdev = self._pdev
             pdev.assemble_poisson(L.MAT, A=self._A_lap_g)
-            self._lap_g = pdev.matrix("P1P1", self._A_lap_g, L.CSR, 1, self._maskQ_g if self._pressure_dirichlet else None)
+            self._lap_g = pdev.matrix("P1P1", self._A_lap_g, L.CSR, 1, self._maskQ_g if self._pressure_dirichlet else None,
+                                      compress=True)
             lap, dinvQ, ldev = self._lap_g, self._dinvQ_g, pdev
         else:
             lap, dinvQ, ldev = self._lap, self._dinvQ, dev

@@ -24,7 +24,8 @@ def run(n, repeat, dim):
     pat = dev.patterns["P1P1"]
     A = dev.empty(pat.nnz)
     dev.assemble_poisson(L.MAT, A=A)
-    out = {"mode": os.environ.get("NSB_CG", "persistent"), "n": n, "rows": pat.nrows, "nnz": pat.nnz}
+    out = {"mode": os.environ.get("NSB_CG", "persistent") + ("+f32/i16 polynomial" if os.environ.get("NSB_PCG_LOWP") == "1" else ""),
+           "n": n, "rows": pat.nrows, "nnz": pat.nnz}
     rng = np.random.default_rng(1)
     for name, mask, nullspace in (("neumann", None, True), ("dirichlet", "mask", False)):
         m = None
@@ -32,7 +33,7 @@ def run(n, repeat, dim):
             mm = np.zeros(pat.nrows, dtype=np.uint8)
             mm[rng.choice(pat.nrows, pat.nrows // 50, replace=False)] = 1
             m = dev.upload(mm)
-        lap = dev.matrix("P1P1", A, L.CSR, 1, m)
+        lap = dev.matrix("P1P1", A, L.CSR, 1, m, compress=os.environ.get("NSB_PCG_LOWP", "0") == "1")
         dinv = dev.empty(pat.nrows)
         dev.inv_diagonal(lap, dinv)
         b = rng.uniform(-1, 1, pat.nrows)
@@ -71,8 +72,8 @@ if __name__ == "__main__":
     if a.child:
         print(json.dumps(run(a.n, a.repeat, a.dim)))
     else:
-        for mode in ("persistent", "multi"):
-            env = dict(os.environ, NSB_CG=mode)
+        for mode, lowp in (("persistent", "1"), ("persistent", "0"), ("multi", "0")):
+            env = dict(os.environ, NSB_CG=mode, NSB_PCG_LOWP=lowp)
             r = subprocess.run([sys.executable, __file__, "--child", "--n", str(a.n), "--dim", str(a.dim), "--repeat", str(a.repeat)],
                                env=env, capture_output=True, text=True, timeout=240)
             print(r.stdout.strip() or r.stderr[-2000:])
