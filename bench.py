@@ -81,7 +81,7 @@ def cpu_oracle_steps(n, steps, warmup, keep_fields=False):
     om = oracle.mesh.hyper_rectangle((0.0, 0.0, 0.0), (1.0, 1.0, 1.0), (n, n, n))
     vel = [(w, None, (0.0, 0.0, 0.0)) for w in (1, 2, 3, 5, 6)] + [(4, None, (1.0, 0.0, 0.0))]
     orc = oracle.solvers.IPCSOracle(om, RE, vel, [], assembler="c", threads=threads)
-    orc.linear_solver, orc.krylov_rtol = "krylov-c", 1e-13      # 1e-13: the arm is also the parity checker of same_size
+    orc.linear_solver, orc.krylov_rtol = "krylov-c", 1e-13
     t, times = 0.0, []
     for s in range(warmup + steps):
         alpha = (1.0, -1.0, 0.0) if s == 0 else (1.5, -2.0, 0.5)

@@ -210,9 +210,9 @@ int nsb_sched_build(int32_t nrows, const int32_t* rowptr_host, const int32_t* pa
 int nsb_set_schedule(nsb_ctx* ctx, int32_t which, int32_t ngroups, int32_t group_max_entries,
                      const int32_t* group_row_dev, const int32_t* chunk_first_dev, const int32_t* round_ptr_dev,
                      const uint16_t* sched_dev);
-/* Caller-owned device workspace of the two-phase assembly kernels (per-cell data -> gather per row): the
- * residual needs ncells * NL2 * d doubles, the Jacobian pre-pass ncells * nsb_scratch_doubles_per_cell(d)
- * (74 in 3D, 32 in 2D).  Without it the one-thread-per-row kernels are used.  NULL / 0 unregisters. */
+/* Caller-owned device workspace of the two-phase (element vectors per cell -> gather per row) vector assembly
+ * kernels: ncells * nsb_scratch_doubles_per_cell(d) doubles (= NL2 * d).  Without it the one-thread-per-row
+ * kernels are used.  NULL / 0 unregisters. */
 int nsb_set_scratch(nsb_ctx* ctx, double* scratch_dev, int64_t ndoubles);
 int nsb_scratch_doubles_per_cell(int32_t dim);
 /* mixed Taylor-Hood dof map [ncells x (d*NL2 + d+1)] (source/ns_solver_base.py:501-524) */

@@ -13,7 +13,7 @@ CSR, BSR = 0, 1
 BC_LINEAR, BC_NEWTON = 0, 1
 # entries per TMA tile of the bulk-copy SpMV kernels, keyed by (matrix kind, bs) (csrc/spmv_tma.cuh)
 TILE_ENTRIES = {(BSR, 3): 384, (BSR, 2): 768}
-SCHED_MAX_BLOCKS = 128     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
+SCHED_MAX_BLOCKS = 160     # entries of a row group in shared memory (csrc/assemble_jac.cu JacCfg::MAXB)
 TIMER_CLASSES = ("asm_jacobian", "asm_residual", "asm_constant", "asm_rhs", "spmv_bsr", "spmv_csr",
                  "krylov_vec", "dirichlet", "vector", "comm", "spmv_bsr_f32", "cg_persistent")
 HALO_NONE, HALO_NODES, HALO_VERTS = 0, 1, 2

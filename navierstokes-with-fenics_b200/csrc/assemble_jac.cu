@@ -7,14 +7,9 @@
 //
 // Work unit = a "row group": consecutive rows (scalar P2 nodes) with at most 32 (row, cell)
 // incidence pairs and MAXB entries (nsb_sched_build).  One warp per group, lane = pair:
-//   pre-pass one thread per CELL evaluates what all NL rows of the cell share -- geometry, the scaled vertex
-//            velocity gradients g[b][a][M] = c_c detJ d_a u_b(x_M), the transformed nodal velocities
-//            z_L = detJ K U_L, the metric G and the mass factor -- ONCE and parks it as a 74-double record
-//            (round 1 recomputed all of it for each of the cell's 10 rows: 5x the FP64 work of the whole
-//            kernel and 168 registers per lane).  Rows that share a cell are close in the node numbering, so
-//            the records are re-read out of the 126 MB L2.
-//   phase A  lane = (row, cell) pair: load the cell record, evaluate in closed form the pair's scalar row S_I.
-//            (NL values, parked in shared memory); g stays in REGISTERS.  Loops over the column index
+//   phase A  gather the cell, geometry, u*; evaluate in closed form the pair's scalar row S_I.
+//            (NL values, parked in shared memory) and the scaled vertex velocity gradients
+//            g[b][a][M] = c_c detJ d_a u_b(x_M) (kept in REGISTERS).  Loops over the column index
 //            J and the vertex index M are fully unrolled against constexpr tables, so the zeros
 //            of the reference tensors cost nothing; only the row index I is a run-time index
 //            (tables in shared memory: no constant-cache serialisation).
@@ -54,10 +49,7 @@ template <int D>
 struct JacCfg {
     static constexpr int NL = CT<D>::NL, NV = D + 1, DD = D * D, NS = D * (D + 1) / 2;
     static constexpr int WARPS = 4;
-    // per-cell record of the pre-pass: g[DD][4] | z[NL][D] | G sym [NS] | mass factor, padded to a 16-byte multiple
-    static constexpr int REC_G = 0, REC_Z = DD * 4, REC_GM = REC_Z + NL * D, REC_M = REC_GM + NS;
-    static constexpr int REC = (REC_M + 1 + 1) & ~1;
-    static constexpr int MAXB = 128;                              // entries of one row group held in shared memory
+    static constexpr int MAXB = 160;                              // entries of one row group held in shared memory
     static constexpr int SSTR = NL + 1 - (NL & 1);                // odd stride of the per-lane S rows: conflict-free
     // shared tables indexed by the run-time row index I (T padded to 4 columns for 128-bit loads)
     static constexpr int TAB_T = NL * NL * 4, TAB_M = NL * NL, TAB_D = NL * NL * NS;
@@ -71,84 +63,14 @@ __device__ constexpr int sym_index(int D, int j, int k) { return j * D - j * (j 
 
 }  // namespace
 
-// ---- pre-pass: one thread per cell -> record (see JacCfg::REC_*) -----------------------------------
 template <int D>
-__global__ void __launch_bounds__(128)
-k_jacobian_cells(int32_t ncells, const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
-                 const int32_t* __restrict__ cell_verts, const double* __restrict__ ustar, double mass_coef,
-                 double c_conv, int newton, double* __restrict__ rec_out) {
-    using C = JacCfg<D>;
-    using TB = CT<D>;
-    constexpr int NL = C::NL, NV = C::NV, DD = C::DD;
-    const int32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncells) return;
-    int32_t vtx[D + 1];
-#pragma unroll
-    for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
-    Geo<D> geo;
-    cell_geometry(coords, vtx, geo);
-    double U[NL][D];
-#pragma unroll
-    for (int L = 0; L < NL; ++L) {
-        const int64_t nd = cell_nodes[(int64_t)c * NL + L];
-#pragma unroll
-        for (int b = 0; b < D; ++b) U[L][b] = ustar[(int64_t)D * nd + b];
-    }
-    double* rec = rec_out + (int64_t)c * C::REC;
-    const double f = newton ? c_conv * geo.detJ : 0.0;
-#pragma unroll
-    for (int M = 0; M < 4; ++M) {
-        double ref[D][D];   // ref[b][k] = sum_L U_Lb dhat_k phi_L(x_M)
-#pragma unroll
-        for (int b = 0; b < D; ++b)
-#pragma unroll
-            for (int k = 0; k < D; ++k) ref[b][k] = 0.0;
-        if (M < NV) {
-#pragma unroll
-            for (int L = 0; L < NL; ++L)
-#pragma unroll
-                for (int k = 0; k < D; ++k)
-                    if (TB::DV(L, M < NV ? M : 0, k) != 0.0) {
-#pragma unroll
-                        for (int b = 0; b < D; ++b) ref[b][k] += U[L][b] * TB::DV(L, M < NV ? M : 0, k);
-                    }
-        }
-#pragma unroll
-        for (int b = 0; b < D; ++b)
-#pragma unroll
-            for (int a = 0; a < D; ++a) {
-                double s = 0.0;
-#pragma unroll
-                for (int k = 0; k < D; ++k) s += ref[b][k] * geo.K[k][a];
-                rec[C::REC_G + (b * D + a) * 4 + M] = f * s;
-            }
-    }
-#pragma unroll
-    for (int L = 0; L < NL; ++L)
-#pragma unroll
-        for (int k = 0; k < D; ++k) {
-            double s = 0.0;
-#pragma unroll
-            for (int i = 0; i < D; ++i) s += geo.K[k][i] * U[L][i];
-            rec[C::REC_Z + L * D + k] = s * geo.detJ;
-        }
-    double G[D][D];
-    metric<D>(geo, G);
-#pragma unroll
-    for (int a = 0; a < D; ++a)
-#pragma unroll
-        for (int b = a; b < D; ++b) rec[C::REC_GM + sym_index(D, a, b)] = G[a][b];
-    rec[C::REC_M] = mass_coef * geo.detJ;
-    if (C::REC > C::REC_M + 1) rec[C::REC_M + 1] = 0.0;
-}
-
-template <int D>
-__global__ void __launch_bounds__(JacCfg<D>::WARPS * 32, 4)
+__global__ void __launch_bounds__(JacCfg<D>::WARPS * 32, 3)
 k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, const int32_t* __restrict__ chunk_first,
                      const int32_t* __restrict__ round_ptr, const uint16_t* __restrict__ sched,
                      const int32_t* __restrict__ rowptr, const int32_t* __restrict__ pair_ptr,
                      const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
-                     const double* __restrict__ cell_rec, double c_conv, double c_visc,
+                     const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
+                     const int32_t* __restrict__ cell_verts, const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc, int newton,
                      double* __restrict__ vals) {
     using C = JacCfg<D>;
     using TB = CT<D>;
@@ -194,12 +116,46 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                 const int32_t P = q0 + lane;
                 const int32_t c = pair_cell[P];
                 I = pair_iloc[P];
-                const double2* rec2 = reinterpret_cast<const double2*>(cell_rec + (int64_t)c * C::REC);
-                // g[b*D+a][M] (already scaled by c_c detJ; zero in Picard mode)
+                int32_t nodes[NL];
 #pragma unroll
-                for (int i = 0; i < DD; ++i) {
-                    const double2 g01 = rec2[(C::REC_G + i * 4) / 2], g23 = rec2[(C::REC_G + i * 4) / 2 + 1];
-                    g[i][0] = g01.x; g[i][1] = g01.y; g[i][2] = g23.x; g[i][3] = g23.y;
+                for (int L = 0; L < NL; ++L) nodes[L] = cell_nodes[(int64_t)c * NL + L];
+                int32_t vtx[D + 1];
+#pragma unroll
+                for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[(int64_t)c * (D + 1) + M];
+                Geo<D> geo;
+                cell_geometry(coords, vtx, geo);
+                double U[NL][D];
+#pragma unroll
+                for (int L = 0; L < NL; ++L)
+#pragma unroll
+                    for (int b = 0; b < D; ++b) U[L][b] = ustar[(int64_t)D * nodes[L] + b];
+                if (newton) {
+                    const double f = c_conv * geo.detJ;
+#pragma unroll
+                    for (int M = 0; M < NV; ++M) {
+                        double ref[D][D];   // ref[b][k] = sum_L U_Lb dhat_k phi_L(x_M)
+#pragma unroll
+                        for (int b = 0; b < D; ++b)
+#pragma unroll
+                            for (int k = 0; k < D; ++k) ref[b][k] = 0.0;
+#pragma unroll
+                        for (int L = 0; L < NL; ++L)
+#pragma unroll
+                            for (int k = 0; k < D; ++k)
+                                if (TB::DV(L, M, k) != 0.0) {
+#pragma unroll
+                                    for (int b = 0; b < D; ++b) ref[b][k] += U[L][b] * TB::DV(L, M, k);
+                                }
+#pragma unroll
+                        for (int b = 0; b < D; ++b)
+#pragma unroll
+                            for (int a = 0; a < D; ++a) {
+                                double s = 0.0;
+#pragma unroll
+                                for (int k = 0; k < D; ++k) s += ref[b][k] * geo.K[k][a];
+                                g[b * D + a][M] = f * s;
+                            }
+                    }
                 }
                 // y[M][k] = sum_L T(I,L,M) z_L[k]
                 double y[NV][D];
@@ -208,12 +164,16 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
 #pragma unroll
                     for (int k = 0; k < D; ++k) y[M][k] = 0.0;
                 const double* tI = sT + I * NL * 4;
-                const double* zrec = cell_rec + (int64_t)c * C::REC + C::REC_Z;
 #pragma unroll
                 for (int L = 0; L < NL; ++L) {
                     double z[D];
 #pragma unroll
-                    for (int k = 0; k < D; ++k) z[k] = zrec[L * D + k];
+                    for (int k = 0; k < D; ++k) {
+                        double s = 0.0;
+#pragma unroll
+                        for (int i = 0; i < D; ++i) s += geo.K[k][i] * U[L][i];
+                        z[k] = s * geo.detJ;
+                    }
 #pragma unroll
                     for (int M = 0; M < NV; ++M) {
                         const double t = tI[L * 4 + M];
@@ -221,10 +181,9 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                         for (int k = 0; k < D; ++k) y[M][k] += t * z[k];
                     }
                 }
-                double Gs[NS];
-#pragma unroll
-                for (int i = 0; i < NS; ++i) Gs[i] = zrec[NL * D + i];
-                const double mcd = zrec[NL * D + NS];
+                double G[D][D];
+                metric<D>(geo, G);
+                const double mcd = mass_coef * geo.detJ;
                 const double* mI = sM2 + I * NL;
                 const double* dI = sD2 + I * NL * NS;
                 double* st = sS + lane * SSTR;
@@ -232,7 +191,9 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                 for (int J = 0; J < NL; ++J) {
                     double vis = 0.0;
 #pragma unroll
-                    for (int i = 0; i < NS; ++i) vis += Gs[i] * dI[J * NS + i];
+                    for (int a = 0; a < D; ++a)
+#pragma unroll
+                        for (int b = a; b < D; ++b) vis += G[a][b] * dI[J * NS + sym_index(D, a, b)];
                     double cv = 0.0;
 #pragma unroll
                     for (int M = 0; M < NV; ++M)
@@ -292,22 +253,15 @@ static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double
     int per_sm = 0;
     NSB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_jacobian_rowgroups<D>, C::WARPS * 32, C::SMEM));
     if (per_sm < 1) return 1;
-    if (!ctx->scratch || ctx->scratch_doubles < (int64_t)ctx->ncells * C::REC) return 1;
     int64_t blocks = (int64_t)ctx->sm_count * per_sm;
     const int64_t need = ((int64_t)P.ngroups + C::WARPS - 1) / C::WARPS;
     if (blocks > need) blocks = need;
-    k_jacobian_cells<D><<<nsb_blocks(ctx->ncells, 128), 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar,
-                                                                     mass_coef, ctx->coef.c_conv, newton, ctx->scratch);
-    NSB_LAUNCH_CHECK(ctx, "k_jacobian_cells");
     k_jacobian_rowgroups<D><<<(int)blocks, C::WARPS * 32, C::SMEM, st>>>(
         P.ngroups, P.group_row, P.chunk_first, P.round_ptr, P.sched, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
-        ctx->scratch, ctx->coef.c_conv, ctx->coef.c_visc, A_out);
+        ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
     NSB_LAUNCH_CHECK(ctx, "k_jacobian_rowgroups");
     return 0;
 }
-
-// doubles per cell the Jacobian pre-pass needs in the caller-owned scratch (nsb_set_scratch)
-int nsb_jacobian_scratch_per_cell(int dim) { return dim == 2 ? JacCfg<2>::REC : JacCfg<3>::REC; }
 
 int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass_coef, int newton, double* A_out,
                                   cudaStream_t st) {

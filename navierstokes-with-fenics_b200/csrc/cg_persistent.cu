@@ -11,9 +11,13 @@
 // decision is uniform without a broadcast), the Chebyshev recurrence and all CG vector updates live in the
 // SpMV epilogues.  degree + 2 barriers per iteration, no host round trip before the solve ends.
 //
-// Memory-model notes: vectors written inside the kernel are read with ld.global.cg (L2, never a stale L1
-// line of another SM's data); the matrix, D^-1 and b are read-only for the kernel's lifetime and go through
-// the non-coherent path.
+// Memory-model notes: vectors written inside the kernel are read with ordinary (L1-cacheable) loads: the grid
+// barrier is a gpu-scope release / acquire (thread 0 of every CTA fences after the spin, which invalidates the
+// SM's L1, and the CTA barrier that follows orders the other threads behind it), exactly the guarantee
+// grid.sync() documents.  That matters: a gathered x_j is used by ~15 rows, nearly all of them in the same
+// CTA, so the gathers hit L1 -- with L2-only loads (ld.global.cg, the first version) every 8-byte gather
+// cost a 32-byte sector request and the SM <-> L2 port bounded the SpMV phase at ~15 us (measured: 206 us per
+// iteration).  Only truly read-only data (matrix, D^-1, b) goes through the non-coherent path (__ldg).
 #include <cooperative_groups.h>
 #include <math.h>
 #include "common.cuh"
@@ -44,7 +48,7 @@ struct pcg_params {
 
 namespace {
 
-__device__ __forceinline__ double ldv(const double* p) { return __ldcg(p); }
+__device__ __forceinline__ double ldv(const double* p) { return *p; }
 
 // per-CTA partials -> barrier -> every CTA sums all partials in CTA order
 template <int NV>

@@ -264,8 +264,5 @@ extern "C" int nsb_launch_count(nsb_ctx* ctx, int64_t* count_out) {
     return 0;
 }
 
-int nsb_jacobian_scratch_per_cell(int dim);     // assemble_jac.cu
-extern "C" int nsb_scratch_doubles_per_cell(int32_t dim) {
-    const int res = dim == 2 ? 12 : 30, jac = nsb_jacobian_scratch_per_cell(dim);
-    return res > jac ? res : jac;
-}
+// doubles per cell of the caller-owned scratch of the two-phase residual assembly: NL2 * d
+extern "C" int nsb_scratch_doubles_per_cell(int32_t dim) { return dim == 2 ? 12 : 30; }
