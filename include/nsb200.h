@@ -76,6 +76,22 @@ typedef struct nsb_pattern_builder nsb_pattern_builder;
 #define NSB_HALO_NODES 1     /* scalar P2 nodes (velocity vectors: bs = d)             */
 #define NSB_HALO_VERTS 2     /* vertices (pressure vectors)                            */
 
+/* SELL-C-sigma copy (C = 32, sigma = 1: P1 rows are nearly uniform, 7 .. 15 entries) of a scalar CSR matrix: rows in
+ * slices of 32, a slice padded to its longest row and stored COLUMN-major, so that one thread per row reads the
+ * value / column streams fully coalesced (entry k of row 32 s + l sits at slice_ptr[s] + 32 k + l).  Padding entries
+ * carry value 0 and the row's own index as column.  vals32 / col16 (col - row, when every delta fits 16 bits): the
+ * 6-bytes-per-entry copy read ONLY by the SpMVs inside the Chebyshev polynomial of the persistent CG -- the CG
+ * operator itself stays FP64. */
+typedef struct nsb_sell {
+    int32_t nslices;               /* ceil(nrows / 32)                                   */
+    int32_t reserved;
+    const int32_t* slice_ptr;      /* dev [nslices + 1], entry offsets (multiples of 32) */
+    const int32_t* col;            /* dev [slice_ptr[nslices]]                           */
+    const double* vals;            /* dev [slice_ptr[nslices]]                           */
+    const float* vals32;           /* dev or NULL                                        */
+    const int16_t* col16;          /* dev or NULL                                        */
+} nsb_sell;
+
 typedef struct nsb_matrix {
     int32_t kind;            /* NSB_CSR | NSB_BSR                                        */
     int32_t bs;              /* components (CSR) or block size (BSR)                      */
@@ -99,10 +115,8 @@ typedef struct nsb_matrix {
                                 the diagonal of block ij (nsb_bsr_block_scalar_f32).  Read ONLY by the single-
                                 precision Chebyshev polynomial inside the flexible nsb_gmres (nsb_precond.lowp),
                                 in preference to vals32: 8 instead of 40 bytes per block entry */
-    const int16_t* col16;    /* dev [nnz] or NULL: column deltas col - row of a scalar CSR matrix (nsb_csr_compress).
-                                Together with vals32 (here: a float copy of the CSR values) read ONLY by the SpMVs
-                                inside the Chebyshev polynomial of the persistent CG kernel: 6 instead of 12 bytes per
-                                entry, so that the pressure operator stays L2-resident; the CG operator stays FP64 */
+    const struct nsb_sell* sell;   /* or NULL: SELL-32 copy of a scalar CSR matrix (nsb_sell_fill), the layout the
+                                persistent CG kernel streams */
 } nsb_matrix;
 
 /* preconditioners of nsb_cg / nsb_gmres (K12) */
@@ -267,10 +281,11 @@ int nsb_set_mixed_bc(nsb_ctx* ctx, const uint8_t* bc_mask_dev, const double* bc_
 
 /* ---------------------------------------------------------------- linear algebra (K10-13) */
 int nsb_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* y, void* stream);
-/* vals32_out[k] = (float) vals[k], col16_out[k] = col[k] - row(k) for a scalar CSR matrix; *overflow_out != 0 if some
- * delta does not fit 16 bits (then leave nsb_matrix.col16 NULL) */
-int nsb_csr_compress(nsb_ctx* ctx, const nsb_matrix* A, float* vals32_out, int16_t* col16_out, int32_t* overflow_out,
-                     void* stream);
+/* Fill the arrays of a SELL-32 copy (slice_ptr given, computed by the caller from the row lengths) from the CSR
+ * matrix A; vals32_out / col16_out may be NULL.  *overflow_out != 0: some |col - row| does not fit 16 bits, col16_out
+ * is unusable (leave nsb_sell.col16 NULL). */
+int nsb_sell_fill(nsb_ctx* ctx, const nsb_matrix* A, int32_t nslices, const int32_t* slice_ptr_dev, int32_t* col_out,
+                  double* vals_out, float* vals32_out, int16_t* col16_out, int32_t* overflow_out, void* stream);
 /* inv_diag[i] = 1/A_ii (1 on masked rows): Jacobi preconditioner (K12) */
 int nsb_inv_diagonal(nsb_ctx* ctx, const nsb_matrix* A, double* inv_diag, void* stream);
 int64_t nsb_cg_workspace_doubles(int64_t n);

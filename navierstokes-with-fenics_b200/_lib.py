@@ -25,11 +25,17 @@ c_i64p = C.POINTER(C.c_int64)
 vp = C.c_void_p
 
 
+class Sell(C.Structure):
+    """struct nsb_sell"""
+    _fields_ = [("nslices", C.c_int32), ("reserved", C.c_int32), ("slice_ptr", vp), ("col", vp), ("vals", vp),
+                ("vals32", vp), ("col16", vp)]
+
+
 class Matrix(C.Structure):
     """struct nsb_matrix"""
     _fields_ = [("kind", C.c_int32), ("bs", C.c_int32), ("nrows", C.c_int32), ("nnz", C.c_int32),
                 ("rowptr", vp), ("col", vp), ("vals", vp), ("bc_mask", vp), ("tiles", vp),
-                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp), ("diag32", vp), ("col16", vp)]
+                ("ntiles", C.c_int32), ("halo", C.c_int32), ("vals32", vp), ("diag32", vp), ("sell", C.POINTER(Sell))]
 
 
 class Saddle(C.Structure):
@@ -79,7 +85,7 @@ PROTOTYPES = {
     "nsb_bc_apply_vector": (C.c_int, [vp, C.c_int32, vp, vp, C.c_int32, vp, vp, vp]),
     "nsb_set_mixed_bc": (C.c_int, [vp, vp, vp]),
     "nsb_spmv": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, vp]),
-    "nsb_csr_compress": (C.c_int, [vp, C.POINTER(Matrix), vp, vp, c_i32p, vp]),
+    "nsb_sell_fill": (C.c_int, [vp, C.POINTER(Matrix), C.c_int32, vp, vp, vp, vp, vp, c_i32p, vp]),
     "nsb_inv_diagonal": (C.c_int, [vp, C.POINTER(Matrix), vp, vp]),
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),

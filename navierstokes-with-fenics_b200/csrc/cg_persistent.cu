@@ -33,8 +33,13 @@ struct pcg_params {
     const int32_t* rowptr;
     const int32_t* col;
     const double* vals;
-    const float* vals32;       // optional single-precision copy of vals  } read ONLY by the SpMVs inside the Chebyshev
-    const int16_t* col16;      // optional column deltas col - row         } polynomial: 6 instead of 12 bytes per entry
+    // SELL-32 copy (nsb_sell): one thread per row, coalesced streams.  s_vals32 / s_col16: the 6-bytes-per-entry copy
+    // read ONLY by the SpMVs inside the Chebyshev polynomial
+    const int32_t* s_ptr;
+    const int32_t* s_col;
+    const double* s_vals;
+    const float* s_vals32;
+    const int16_t* s_col16;
     const uint8_t* mask;
     const double* dinv;
     const double* b;
@@ -155,13 +160,52 @@ __device__ __forceinline__ void spmv_phase(const int32_t* __restrict__ rowptr, c
     }
 }
 
+// One SpMV phase in the SELL-32 layout: thread = row, warp = slice, every load of the value / column streams is a
+// fully coalesced 32-lane access; ~6 instructions per entry instead of the ~35 of the 4-lanes-per-row CSR pass
+// (which was ISSUE bound: measured 1 us per 256-row pass).  rows [lo, hi), lo a multiple of 32.
+template <typename VT, typename IT, typename Pre, typename Post>
+__device__ __forceinline__ void sell_phase(const int32_t* __restrict__ sptr, const VT* __restrict__ vals,
+                                           const IT* __restrict__ cols, const double* x, int32_t lo, int32_t hi,
+                                           Pre&& pre, Post&& post) {
+    for (int32_t row = lo + (int32_t)threadIdx.x; row < hi; row += PCG_THREADS) {
+        const int32_t slice = row >> 5, l = row & 31;
+        const int32_t base = __ldg(sptr + slice), width = (__ldg(sptr + slice + 1) - base) >> 5;
+        auto operands = pre(row, true);
+        const VT* v = vals + base + l;
+        const IT* c = cols + base + l;
+        double acc0 = 0.0, acc1 = 0.0;
+        int k = 0;
+        for (; k + 4 <= width; k += 4) {
+            VT vv[4];
+            int32_t cc[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                vv[u] = __ldg(v + (k + u) * 32);
+                cc[u] = sizeof(IT) == 2 ? row + (int32_t)__ldg(c + (k + u) * 32) : (int32_t)__ldg(c + (k + u) * 32);
+            }
+            double xv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) xv[u] = ldv(x + cc[u]);
+            acc0 += (double)vv[0] * xv[0] + (double)vv[2] * xv[2];
+            acc1 += (double)vv[1] * xv[1] + (double)vv[3] * xv[3];
+        }
+        for (; k < width; ++k) {
+            const int32_t cn = sizeof(IT) == 2 ? row + (int32_t)__ldg(c + k * 32) : (int32_t)__ldg(c + k * 32);
+            acc0 += (double)__ldg(v + k * 32) * ldv(x + cn);
+        }
+        post(row, acc0 + acc1, operands);
+    }
+}
+
 }  // namespace
 
 __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_params P) {
     cg::grid_group grid = cg::this_grid();
     __shared__ double smem[3 * (PCG_THREADS / 32) + 4];
     const int32_t n = P.nrows;
-    const int32_t per = (n + (int32_t)gridDim.x - 1) / (int32_t)gridDim.x;
+    const bool sell = P.s_ptr != nullptr;
+    int32_t per = (n + (int32_t)gridDim.x - 1) / (int32_t)gridDim.x;
+    if (sell) per = (per + 31) & ~31;                  // whole slices per CTA
     const int32_t lo = min(n, (int32_t)blockIdx.x * per), hi = min(n, lo + per);
     const int lane = threadIdx.x % PCG_LANES, grp = threadIdx.x / PCG_LANES;
     double* slot_a = P.partials;                       // 3 values
@@ -179,13 +223,13 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
     // ---- r = (b - shift) - A x ; preconditioner start for the first iteration --------------------------
     double red[3] = {0.0, 0.0, 0.0};                   // rr, bb, rz (Jacobi)
     struct Op0 { double xi, bi, dinv; };
-    spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, P.x, lo, hi, grp, lane,
-        [&](int32_t row, bool mine) {
+    {
+        auto pre0 = [&](int32_t row, bool mine) {
             Op0 o = {0.0, 0.0, 0.0};
             if (mine) { o.xi = ldv(P.x + row); o.bi = __ldg(P.b + row); o.dinv = __ldg(P.dinv + row); }
             return o;
-        },
-        [&](int32_t row, double v, const Op0& o) {
+        };
+        auto post0 = [&](int32_t row, double v, const Op0& o) {
             if (P.mask != nullptr && P.mask[row]) v = o.xi;
             const double bi = o.bi - shift;
             const double ri = bi - v;
@@ -202,7 +246,10 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
                 P.z[row] = di;
                 red[2] += ri * di;
             }
-        });
+        };
+        if (sell) sell_phase<double, int32_t>(P.s_ptr, P.s_vals, P.s_col, P.x, lo, hi, pre0, post0);
+        else spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, P.x, lo, hi, grp, lane, pre0, post0);
+    }
     grid_reduce<3>(grid, red, slot_b, smem);
     double rr = red[0];
     const double bb = red[1];
@@ -240,8 +287,12 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
                     P.z[row] = zi;
                     if (last) s[0] += o.r * zi;
                 };
-                if (P.vals32 != nullptr && P.col16 != nullptr)
-                    spmv_phase<float, int16_t>(P.rowptr, P.vals32, P.col16, dold, lo, hi, grp, lane, pre, post);
+                if (sell && P.s_vals32 != nullptr && P.s_col16 != nullptr)
+                    sell_phase<float, int16_t>(P.s_ptr, P.s_vals32, P.s_col16, dold, lo, hi, pre, post);
+                else if (sell && P.s_vals32 != nullptr)
+                    sell_phase<float, int32_t>(P.s_ptr, P.s_vals32, P.s_col, dold, lo, hi, pre, post);
+                else if (sell)
+                    sell_phase<double, int32_t>(P.s_ptr, P.s_vals, P.s_col, dold, lo, hi, pre, post);
                 else
                     spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, dold, lo, hi, grp, lane, pre, post);
                 if (!last) grid.sync();
@@ -262,17 +313,20 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_par
         // q = A p ; p.q
         double s1[1] = {0.0};
         struct OpQ { double pi; };
-        spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, P.p, lo, hi, grp, lane,
-            [&](int32_t row, bool mine) {
+        {
+            auto preq = [&](int32_t row, bool mine) {
                 OpQ o = {0.0};
                 if (mine) o.pi = ldv(P.p + row);
                 return o;
-            },
-            [&](int32_t row, double v, const OpQ& o) {
+            };
+            auto postq = [&](int32_t row, double v, const OpQ& o) {
                 if (P.mask != nullptr && P.mask[row]) v = o.pi;
                 P.q[row] = v;
                 s1[0] += o.pi * v;
-            });
+            };
+            if (sell) sell_phase<double, int32_t>(P.s_ptr, P.s_vals, P.s_col, P.p, lo, hi, preq, postq);
+            else spmv_phase<double, int32_t>(P.rowptr, P.vals, P.col, P.p, lo, hi, grp, lane, preq, postq);
+        }
         grid_reduce<1>(grid, s1, slot_b, smem);
         const double pq = s1[0];
         const double alpha = pq != 0.0 ? rz / pq : 0.0;
@@ -341,7 +395,10 @@ int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     pcg_params P;
     memset(&P, 0, sizeof P);
     P.nrows = A->nrows; P.rowptr = A->rowptr; P.col = A->col; P.vals = A->vals; P.mask = A->bc_mask;
-    P.vals32 = A->vals32; P.col16 = A->col16;
+    if (A->sell && A->sell->slice_ptr && A->sell->col && A->sell->vals && A->sell->nslices == (A->nrows + 31) / 32) {
+        P.s_ptr = A->sell->slice_ptr; P.s_col = A->sell->col; P.s_vals = A->sell->vals;
+        P.s_vals32 = A->sell->vals32; P.s_col16 = A->sell->col16;
+    }
     P.dinv = M->inv_diag; P.b = b; P.x = x;
     P.r = work; P.z = work + n; P.p = work + 2 * n; P.q = work + 3 * n; P.rc = work + 4 * n; P.d0 = work + 5 * n; P.d1 = work + 6 * n;
     P.partials = ctx->d_partials;
@@ -378,30 +435,43 @@ int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     return 0;
 }
 
-// single-precision values + 16-bit column deltas of a scalar CSR matrix (nsb_matrix.vals32 / col16): what the SpMVs
-// inside the Chebyshev polynomial of the persistent CG read.  flag_out[0] != 0 afterwards: some |col - row| > 32767,
-// the deltas are unusable (leave nsb_matrix.col16 NULL).
-__global__ void k_csr_compress(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-                               const double* __restrict__ vals, float* __restrict__ vals32, int16_t* __restrict__ col16,
-                               int* flag) {
+// SELL-32 fill: thread = row; entry k of the row goes to slice_ptr[row / 32] + 32 k + row % 32, padding gets value 0
+// and the row's own index
+__global__ void k_sell_fill(int32_t nrows, int32_t nslices, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                            const double* __restrict__ vals, const int32_t* __restrict__ sptr, int32_t* __restrict__ scol,
+                            double* __restrict__ svals, float* __restrict__ svals32, int16_t* __restrict__ scol16, int* flag) {
     const int32_t row = blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= nrows) return;
-    for (int32_t s = rowptr[row]; s < rowptr[row + 1]; ++s) {
-        const int32_t d = col[s] - row;
-        if (d > 32767 || d < -32768) *flag = 1;
-        col16[s] = (int16_t)d;
-        vals32[s] = (float)vals[s];
+    if (row >= nslices * 32) return;
+    const int32_t slice = row >> 5, l = row & 31;
+    const int32_t base = sptr[slice], width = (sptr[slice + 1] - base) >> 5;
+    const int32_t beg = row < nrows ? rowptr[row] : 0, len = row < nrows ? rowptr[row + 1] - beg : 0;
+    for (int k = 0; k < width; ++k) {
+        const int32_t at = base + k * 32 + l;
+        const bool real = k < len;
+        const int32_t c = real ? col[beg + k] : min(row, nrows - 1);
+        const double v = real ? vals[beg + k] : 0.0;
+        scol[at] = c;
+        svals[at] = v;
+        if (svals32) svals32[at] = (float)v;
+        if (scol16) {
+            const int32_t d = c - row;
+            if (d > 32767 || d < -32768) *flag = 1;
+            scol16[at] = (int16_t)d;
+        }
     }
 }
 
-extern "C" int nsb_csr_compress(nsb_ctx* ctx, const nsb_matrix* A, float* vals32_out, int16_t* col16_out, int32_t* overflow_out,
-                                void* stream) {
-    NSB_REQUIRE(ctx, ctx && A && A->kind == NSB_CSR && vals32_out && col16_out && overflow_out, "bad arguments");
+extern "C" int nsb_sell_fill(nsb_ctx* ctx, const nsb_matrix* A, int32_t nslices, const int32_t* slice_ptr_dev, int32_t* col_out,
+                             double* vals_out, float* vals32_out, int16_t* col16_out, int32_t* overflow_out, void* stream) {
+    NSB_REQUIRE(ctx, ctx && A && A->kind == NSB_CSR && A->bs == 1 && slice_ptr_dev && col_out && vals_out && overflow_out,
+                "bad arguments");
+    NSB_REQUIRE(ctx, nslices == (A->nrows + 31) / 32, "nslices must be ceil(nrows / 32)");
     cudaStream_t st = (cudaStream_t)stream;
     int* flag = reinterpret_cast<int*>(ctx->d_counter + 1);
     NSB_CUDA(ctx, cudaMemsetAsync(flag, 0, sizeof(int), st));
-    k_csr_compress<<<nsb_blocks(A->nrows, 256), 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->vals, vals32_out, col16_out, flag);
-    NSB_LAUNCH_CHECK(ctx, "k_csr_compress");
+    k_sell_fill<<<nsb_blocks((int64_t)nslices * 32, 256), 256, 0, st>>>(A->nrows, nslices, A->rowptr, A->col, A->vals, slice_ptr_dev,
+                                                                       col_out, vals_out, vals32_out, col16_out, flag);
+    NSB_LAUNCH_CHECK(ctx, "k_sell_fill");
     int h = 0;
     NSB_CUDA(ctx, cudaMemcpyAsync(&h, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
     NSB_CUDA(ctx, cudaStreamSynchronize(st));

@@ -320,13 +320,26 @@ class Device:
                      diag32.data_ptr() if diag32 is not None else None, None)
         m._keep = (pat, vals, bc_mask, tiles, vals32, diag32)
         if compress and kind == L.CSR and bs == 1:
-            # float values + 16-bit column deltas for the polynomial SpMVs of the persistent CG (nsb_csr_compress)
-            v32, c16 = self.empty(pat.nnz, dtype=torch.float32), self.empty(pat.nnz, dtype=torch.int16)
-            over = C.c_int32()
-            self.check(self.lib.nsb_csr_compress(self.ctx, C.byref(m), _ptr(v32), _ptr(c16), C.byref(over), self.stream))
-            if over.value == 0:
-                m.vals32, m.col16 = v32.data_ptr(), c16.data_ptr()
-                m._keep = m._keep + (v32, c16)
+            # SELL-32 copy for the persistent CG kernel (+ float values / 16-bit column deltas for its polynomial)
+            rp = pat.rowptr_host.astype(np.int64)
+            nsl = (pat.nrows + 31) // 32
+            lens = np.zeros(nsl * 32, dtype=np.int64)
+            lens[:pat.nrows] = rp[1:] - rp[:-1]
+            width = lens.reshape(nsl, 32).max(axis=1)
+            sp_host = np.zeros(nsl + 1, dtype=np.int64)
+            np.cumsum(32 * width, out=sp_host[1:])
+            if sp_host[-1] < 2 ** 31:
+                tot = int(sp_host[-1])
+                slice_ptr = self.upload(sp_host.astype(np.int32))
+                scol, sval = self.empty(tot, dtype=torch.int32), self.empty(tot)
+                v32, c16 = self.empty(tot, dtype=torch.float32), self.empty(tot, dtype=torch.int16)
+                over = C.c_int32()
+                self.check(self.lib.nsb_sell_fill(self.ctx, C.byref(m), nsl, _ptr(slice_ptr), _ptr(scol), _ptr(sval), _ptr(v32),
+                                                  _ptr(c16), C.byref(over), self.stream))
+                sell = L.Sell(nsl, 0, slice_ptr.data_ptr(), scol.data_ptr(), sval.data_ptr(), v32.data_ptr(),
+                              c16.data_ptr() if over.value == 0 else None)
+                m.sell = C.pointer(sell)
+                m._keep = m._keep + (slice_ptr, scol, sval, v32, c16, sell)
         return m
 
     # ---- coefficients -----------------------------------------------------------------------

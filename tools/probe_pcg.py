@@ -24,7 +24,7 @@ def run(n, repeat, dim):
     pat = dev.patterns["P1P1"]
     A = dev.empty(pat.nnz)
     dev.assemble_poisson(L.MAT, A=A)
-    out = {"mode": os.environ.get("NSB_CG", "persistent") + ("+f32/i16 polynomial" if os.environ.get("NSB_PCG_LOWP") == "1" else ""),
+    out = {"mode": os.environ.get("NSB_CG", "persistent") + ("+SELL-32 (f32/i16 polynomial)" if os.environ.get("NSB_PCG_LOWP") == "1" else ""),
            "n": n, "rows": pat.nrows, "nnz": pat.nnz}
     rng = np.random.default_rng(1)
     for name, mask, nullspace in (("neumann", None, True), ("dirichlet", "mask", False)):
