@@ -46,6 +46,7 @@ struct pcg_params {
     double *x, *r, *z, *p, *q, *rc, *d0, *d1;
     double* partials;          // [6][gridDim.x]
     double* out;               // [4]: iterations, ||r||^2, ||b||^2
+    unsigned int* barrier;     // grid barrier counter, zero on entry
     double rtol, atol, n_all, inv_theta;
     int32_t maxit, nullspace, degree;     // degree 0: Jacobi; >= 2: Chebyshev polynomial with degree terms
     double ca[PCG_MAXDEG], cb[PCG_MAXDEG];
@@ -55,9 +56,33 @@ namespace {
 
 __device__ __forceinline__ double ldv(const double* p) { return *p; }
 
+// Grid-wide barrier on one monotonically increasing counter (zeroed before the launch; all CTAs are co-resident:
+// cooperative launch).  cooperative_groups' grid.sync() measured ~8-10 us per barrier here (1024-thread CTAs on 148
+// SMs) -- with degree + 2 barriers per CG iteration that was most of the solve.  Release: every thread's writes are
+// ordered before thread 0's fence by the CTA barrier; acquire: thread 0 spins with ld.acquire.gpu, fences (which
+// invalidates the SM's L1) and the second CTA barrier orders the other threads' ordinary loads behind it.
+struct GridBarrier {
+    unsigned int* counter;
+    unsigned int target;
+    __device__ __forceinline__ void sync() {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            target += gridDim.x;
+            __threadfence();
+            atomicAdd(counter, 1u);
+            unsigned int v;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+            } while ((int)(v - target) < 0);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+};
+
 // per-CTA partials -> barrier -> every CTA sums all partials in CTA order
 template <int NV>
-__device__ __forceinline__ void grid_reduce(cg::grid_group& grid, double (&v)[NV], double* slots, double* smem) {
+__device__ __forceinline__ void grid_reduce(GridBarrier& grid, double (&v)[NV], double* slots, double* smem) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     constexpr int NW = PCG_THREADS / 32;
 #pragma unroll
@@ -200,7 +225,7 @@ __device__ __forceinline__ void sell_phase(const int32_t* __restrict__ sptr, con
 }  // namespace
 
 __global__ void __launch_bounds__(PCG_THREADS, 1) k_pcg_persistent(const pcg_params P) {
-    cg::grid_group grid = cg::this_grid();
+    GridBarrier grid = {P.barrier, 0u};
     __shared__ double smem[3 * (PCG_THREADS / 32) + 4];
     const int32_t n = P.nrows;
     const bool sell = P.s_ptr != nullptr;
@@ -403,6 +428,8 @@ int nsb_cg_persistent(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     P.r = work; P.z = work + n; P.p = work + 2 * n; P.q = work + 3 * n; P.rc = work + 4 * n; P.d0 = work + 5 * n; P.d1 = work + 6 * n;
     P.partials = ctx->d_partials;
     P.out = ctx->d_scalars;
+    P.barrier = ctx->d_counter + 2;
+    NSB_CUDA(ctx, cudaMemsetAsync(P.barrier, 0, sizeof(unsigned int), st));
     P.rtol = rtol; P.atol = atol; P.maxit = maxit; P.nullspace = nullspace;
     P.n_all = (double)n;
     P.degree = M->kind == NSB_PC_CHEBYSHEV ? M->degree : 0;
