@@ -200,23 +200,35 @@ __device__ __forceinline__ void sell_phase(const int32_t* __restrict__ sptr, con
         const IT* c = cols + base + l;
         double acc0 = 0.0, acc1 = 0.0;
         int k = 0;
-        for (; k + 4 <= width; k += 4) {
-            VT vv[4];
-            int32_t cc[4];
+        // 8 entries in flight per thread: a row of 15 is two dependent round trips (columns -> gathers), not eight
+        for (; k + 8 <= width; k += 8) {
+            VT vv[8];
+            int32_t cc[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < 8; ++u) {
                 vv[u] = __ldg(v + (k + u) * 32);
                 cc[u] = sizeof(IT) == 2 ? row + (int32_t)__ldg(c + (k + u) * 32) : (int32_t)__ldg(c + (k + u) * 32);
             }
-            double xv[4];
+            double xv[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) xv[u] = ldv(x + cc[u]);
-            acc0 += (double)vv[0] * xv[0] + (double)vv[2] * xv[2];
-            acc1 += (double)vv[1] * xv[1] + (double)vv[3] * xv[3];
+            for (int u = 0; u < 8; ++u) xv[u] = ldv(x + cc[u]);
+#pragma unroll
+            for (int u = 0; u < 8; u += 2) { acc0 += (double)vv[u] * xv[u]; acc1 += (double)vv[u + 1] * xv[u + 1]; }
         }
-        for (; k < width; ++k) {
-            const int32_t cn = sizeof(IT) == 2 ? row + (int32_t)__ldg(c + k * 32) : (int32_t)__ldg(c + k * 32);
-            acc0 += (double)__ldg(v + k * 32) * ldv(x + cn);
+        {   // remaining (< 8) entries, still issued together
+            VT vv[8];
+            int32_t cc[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const bool ok = k + u < width;
+                vv[u] = ok ? __ldg(v + (k + u) * 32) : (VT)0;
+                cc[u] = ok ? (sizeof(IT) == 2 ? row + (int32_t)__ldg(c + (k + u) * 32) : (int32_t)__ldg(c + (k + u) * 32)) : row;
+            }
+            double xv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) xv[u] = ldv(x + cc[u]);
+#pragma unroll
+            for (int u = 0; u < 8; u += 2) { acc0 += (double)vv[u] * xv[u]; acc1 += (double)vv[u + 1] * xv[u + 1]; }
         }
         post(row, acc0 + acc1, operands);
     }
