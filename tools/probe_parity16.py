@@ -26,8 +26,8 @@ for _ in range(2):
     ots.advance_time()
     orc.advance_time()
 ou, op = orc.velocities[1], orc.old_pressure - orc.old_pressure.mean()
-for kw in (dict(), dict(linear_atol_factor=0.1), dict(linear_atol_factor=0.01), dict(linear_rtol=1e-13, pressure_rtol=1e-13),
-           dict(linear_rtol=1e-13, pressure_rtol=1e-12), dict(linear_atol_factor=0.01, pressure_rtol=1e-12)):
+for kw in (dict(correction_rtol=1e-12), dict(correction_rtol=1e-12, linear_atol_factor=0.01), dict(),
+           dict(linear_rtol=1e-13), dict(linear_rtol=1e-11, correction_rtol=1e-13)):
     mesh, markers = nsb200.hyper_cube(3, n)
     ts = nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=dt)
     s = nsb200.IPCSSolver(mesh, markers, "standard", ts, **kw)
