@@ -130,14 +130,15 @@ struct RowEntries {
 
 template <typename VT, typename IT>
 __device__ __forceinline__ void load_entries(const VT* __restrict__ vals, const IT* __restrict__ cols, int32_t row,
-                                             int32_t beg, int32_t end, int lane, RowEntries<VT, IT>& e) {
+                                             int32_t safe, int32_t beg, int32_t end, int lane, RowEntries<VT, IT>& e) {
+    // `safe`: a valid column for the lanes without an entry (their gather is issued anyway, with value 0)
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
         const int32_t s = beg + lane + u * PCG_LANES;
         const bool ok = s < end;
         e.v[u] = ok ? __ldg(vals + s) : (VT)0;
-        if (sizeof(IT) == 2) e.c[u] = ok ? row + (int32_t)__ldg(cols + s) : row;
-        else e.c[u] = ok ? (int32_t)__ldg(cols + s) : row;
+        if (sizeof(IT) == 2) e.c[u] = ok ? row + (int32_t)__ldg(cols + s) : safe;
+        else e.c[u] = ok ? (int32_t)__ldg(cols + s) : safe;
     }
 }
 
@@ -156,7 +157,7 @@ __device__ __forceinline__ void spmv_phase(const int32_t* __restrict__ rowptr, c
     offsets(0, beg_c, end_c);
     offsets(1, beg_n, end_n);
     RowEntries<VT, IT> cur, nxt;
-    load_entries<VT, IT>(vals, cols, lo + grp, beg_c, end_c, lane, cur);
+    load_entries<VT, IT>(vals, cols, lo + grp, lo, beg_c, end_c, lane, cur);
     for (int k = 0; k < npass; ++k) {
         const int32_t row = lo + grp + k * GROUPS;
         const bool mine = row < hi && lane == 0;
@@ -165,7 +166,7 @@ __device__ __forceinline__ void spmv_phase(const int32_t* __restrict__ rowptr, c
 #pragma unroll
         for (int u = 0; u < 4; ++u) xv[u] = ldv(x + cur.c[u]);
         auto operands = pre(row, mine);
-        load_entries<VT, IT>(vals, cols, row + GROUPS, beg_n, end_n, lane, nxt);
+        load_entries<VT, IT>(vals, cols, row + GROUPS, lo, beg_n, end_n, lane, nxt);
         int32_t beg_nn, end_nn;
         offsets(k + 2, beg_nn, end_nn);
         double acc = 0.0;
