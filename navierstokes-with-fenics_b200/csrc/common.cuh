@@ -104,7 +104,23 @@ struct nsb_cheb32_epi {
     float *r, *dnew, *z;
     double* zout;
     float a, b;
+    // bf16 shadow of the direction vectors (BS = 3: 4 x bf16 = 8 bytes per node): the SpMV GATHERS from x_h instead of
+    // the float4 vector (half the bytes per gathered node -- the kernel is bound by L1TEX sectors of exactly those
+    // gathers) and writes the shadow of d_new next to d_new; the recurrences themselves stay FP32 on the exact vectors.
+    // nullptr: gather from the float4 vector.
+    const unsigned long long* x_h;
+    unsigned long long* dnew_h;
 };
+__device__ __forceinline__ unsigned long long nsb_pack_bf16x3(float a, float b, float c) {
+    // round-to-nearest-even bf16 = upper 16 bits of the float
+    auto rn = [](float f) -> unsigned int {
+        unsigned int u = __float_as_uint(f);
+        u += 0x7fffu + ((u >> 16) & 1u);
+        return u >> 16;
+    };
+    const unsigned int lo = rn(a) | (rn(b) << 16), hi = rn(c);
+    return ((unsigned long long)hi << 32) | lo;
+}
 
 // the same step in FP64 in the epilogue of the CSR SpMV kernels (pressure Chebyshev-CG): z += d_new in place
 struct nsb_cheb64_epi {

@@ -9,6 +9,8 @@
 // are warp-shuffle + deterministic last-block reductions; vector updates are fused with the
 // reductions that follow them and p.Ap is fused into the SpMV epilogue.
 #include <math.h>
+#include <stdlib.h>
+#include <string.h>
 #include <vector>
 #include "spmv.cuh"
 
@@ -82,7 +84,8 @@ template <> struct Pad32<2> {
 template <int BS>
 __global__ void __launch_bounds__(256)
 k_cheb32_first(int64_t nnodes, const double* __restrict__ dinv, const double* __restrict__ v, float inv_theta,
-               float* __restrict__ r, float* __restrict__ d, float* __restrict__ z, double* __restrict__ zout) {
+               float* __restrict__ r, float* __restrict__ d, float* __restrict__ z, double* __restrict__ zout,
+               unsigned long long* __restrict__ d_h = nullptr) {
     GRID_STRIDE(i, nnodes) {
         float c[BS], di[BS];
 #pragma unroll
@@ -95,6 +98,9 @@ k_cheb32_first(int64_t nnodes, const double* __restrict__ dinv, const double* __
             for (int b = 0; b < BS; ++b) zout[i * BS + b] = (double)di[b];
         } else {
             Pad32<BS>::st(r, i, c); Pad32<BS>::st(d, i, di); Pad32<BS>::st(z, i, di);
+            if constexpr (BS == 3) {
+                if (d_h) d_h[i] = nsb_pack_bf16x3(di[0], di[1], di[2]);
+            }
         }
     }
 }
@@ -233,15 +239,21 @@ static int apply_cheb32(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M,
     const int G = krylov_grid(ctx, nn);
     float* r = reinterpret_cast<float*>(((uintptr_t)scratch + 15) & ~(uintptr_t)15);   // 4 x PB nn floats <= 3 n doubles
     float *d = r + PB * nn, *q = d + PB * nn, *z = q + PB * nn;
+    // bf16 shadows of the two direction buffers (gathered by the block-scalar SpMV); NSB_PC_GATHER=f32 switches them off
+    const bool fused = A->diag32 != nullptr;      // block-scalar matrix: the step runs in the SpMV's epilogue
+    static const bool shadow_on = !(getenv("NSB_PC_GATHER") && !strcmp(getenv("NSB_PC_GATHER"), "f32"));
+    const bool shadow = fused && BS == 3 && shadow_on && M->degree > 1;
+    unsigned long long* dh = reinterpret_cast<unsigned long long*>(z + PB * nn);
+    unsigned long long* qh = dh + nn;
     const double theta = 0.5 * (M->lambda_max + M->lambda_min), delta = 0.5 * (M->lambda_max - M->lambda_min);
     const double sigma1 = theta / delta;
     double rho_old = 1.0 / sigma1;
     {
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
-        k_cheb32_first<BS><<<G, 256, 0, st>>>(nn, M->inv_diag, v, (float)(1.0 / theta), r, d, z, M->degree == 1 ? zout : nullptr);
+        k_cheb32_first<BS><<<G, 256, 0, st>>>(nn, M->inv_diag, v, (float)(1.0 / theta), r, d, z, M->degree == 1 ? zout : nullptr,
+                                              shadow ? dh : nullptr);
         NSB_LAUNCH_CHECK(ctx, "k_cheb32_first");
     }
-    const bool fused = A->diag32 != nullptr;      // block-scalar matrix: the step runs in the SpMV's epilogue
     for (int k = 1; k < M->degree; ++k) {
         const double rho = 1.0 / (2.0 * sigma1 - rho_old);
         if (fused) {                              // d and q alternate as old / new direction
@@ -249,8 +261,10 @@ static int apply_cheb32(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M,
             E.dinv = M->inv_diag; E.r = r; E.dnew = q; E.z = z;
             E.zout = k == M->degree - 1 ? zout : nullptr;
             E.a = (float)(rho * rho_old); E.b = (float)(2.0 * rho / delta);
+            E.x_h = shadow ? dh : nullptr; E.dnew_h = shadow ? qh : nullptr;
             if (nsb_launch_spmv32(ctx, A, d, nullptr, st, &E)) return -1;
             float* tmp = d; d = q; q = tmp;
+            unsigned long long* th = dh; dh = qh; qh = th;
             rho_old = rho;
             continue;
         }
@@ -628,7 +642,7 @@ k_add(int64_t n, const double* __restrict__ t, double* __restrict__ x) {
 // V (restart+1), w, t, Chebyshev scratch (3), and restart more for the preconditioned basis Z of the
 // flexible variant (M->lowp)
 extern "C" int64_t nsb_gmres_workspace_doubles(int64_t n, int32_t restart, int32_t flexible) {
-    return (int64_t)(restart + 6 + (flexible ? restart : 0)) * n;
+    return (int64_t)(restart + 7 + (flexible ? restart : 0)) * n;
 }
 
 extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
@@ -647,12 +661,12 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
     double* V = work;                       // (m+1) x n
     double* w = work + (int64_t)(m + 1) * n;
     double* t = w + n;
-    double* scratch = t + n;                // 3 n (Chebyshev)
+    double* scratch = t + n;                // 4 n (Chebyshev: 3 n of recurrence vectors + the bf16 shadows of the f32 variant)
     // Flexible GMRES (Saad 1993) when the preconditioner runs in single precision: z_j = M^-1 v_j is kept
     // (Z, restart x n behind the scratch) and x += Z y, so the preconditioner need not be a fixed linear
     // operator; Arnoldi, the Hessenberg system and the residual test stay FP64 on the FP64 matrix.
     const bool flex = pc_single_precision(A, M) || M->kind == NSB_PC_SADDLE;
-    double* Z = scratch + 3 * n;
+    double* Z = scratch + 4 * n;
     double* ds = ctx->d_scalars;
     double* hs = ctx->h_scalars;
     const int G = krylov_grid(ctx, n);

@@ -88,11 +88,11 @@ bool nsb_spmv32_available(const nsb_matrix* A) {
 // lower-order Newton coupling, so as a PRECONDITIONER the scalar part does as well as the full blocks
 // (same GMRES iteration counts, tools/probe_scalar_pc.py).  LANES lanes per row, coalesced value / column
 // streams, one 16-byte gather per entry.
-template <int BS, int LANES, int U, bool CHEB>
+template <int BS, int LANES, int U, bool CHEB, bool H16 = false>
 __global__ void __launch_bounds__(256)
 k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
               const float* __restrict__ s, const float* __restrict__ x, int32_t nown, const float* __restrict__ xg,
-              float* __restrict__ y, nsb_cheb32_epi E) {
+              float* __restrict__ y, nsb_cheb32_epi E, const unsigned long long* __restrict__ xgh = nullptr) {
     constexpr int PB = NSB_PAD32(BS);
     const int lane = threadIdx.x % LANES;
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
@@ -113,7 +113,19 @@ k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* 
             cn[u] = ok ? col[kk] : (int32_t)row;
             v[u] = ok ? s[kk] : 0.0f;
         }
-        if constexpr (BS == 3) {
+        if constexpr (BS == 3 && H16) {
+            // bf16 shadow: one 8-byte gather per entry (ghost columns: the shadow's ghost block, E.x_h is [owned | ghost])
+            unsigned long long t[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) t[u] = __ldg((cn[u] < nown ? E.x_h : xgh) + cn[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const unsigned int lo = (unsigned int)t[u], hi = (unsigned int)(t[u] >> 32);
+                acc[0] += v[u] * __uint_as_float(lo << 16);
+                acc[1] += v[u] * __uint_as_float(lo & 0xffff0000u);
+                acc[2] += v[u] * __uint_as_float(hi << 16);
+            }
+        } else if constexpr (BS == 3) {
             float4 t[U];
 #pragma unroll
             for (int u = 0; u < U; ++u)
@@ -158,6 +170,7 @@ k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* 
             } else if constexpr (BS == 3) {
                 reinterpret_cast<float4*>(E.r)[row] = make_float4(ri[0], ri[1], ri[2], 0.0f);
                 reinterpret_cast<float4*>(E.dnew)[row] = make_float4(acc[0], acc[1], acc[2], 0.0f);
+                if constexpr (H16) E.dnew_h[row] = nsb_pack_bf16x3(acc[0], acc[1], acc[2]);
                 reinterpret_cast<float4*>(E.z)[row] = make_float4(zi[0], zi[1], zi[2], 0.0f);
             } else {
                 reinterpret_cast<float2*>(E.r)[row] = make_float2(ri[0], ri[1]);
@@ -173,7 +186,7 @@ k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* 
 
 template <int BS>
 static int launch_spmv_kron32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, int32_t nown, const float* xg, float* y,
-                              const nsb_cheb32_epi* epi, cudaStream_t st) {
+                              const nsb_cheb32_epi* epi, cudaStream_t st, const unsigned long long* xgh = nullptr) {
     const double per_row = (double)A->nnz / (double)A->nrows;
     // measured on B200 at C5 (28 entries per row), preconditioner SpMV ms per step: 4 lanes x 4 gathers 34.0,
     // 8 x 4 38.7, 2 x 4 39.1, 4 x 8 39.5, 8 x 8 56.5, 16 x 2 66.8, 32 x 2 121
@@ -185,6 +198,14 @@ static int launch_spmv_kron32(nsb_ctx* ctx, const nsb_matrix* A, const float* x,
         if (epi) k_spmv_kron32<BS, LANES, U, true><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E);  \
         else k_spmv_kron32<BS, LANES, U, false><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E); \
     } while (0)
+    if constexpr (BS == 3) {
+        if (epi && epi->x_h) {        // bf16 shadow gathers (fused Chebyshev step only)
+            if (lanes == 4) k_spmv_kron32<3, 4, 4, true, true><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E, xgh);
+            else k_spmv_kron32<3, 8, 4, true, true><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E, xgh);
+            NSB_LAUNCH_CHECK(ctx, "k_spmv_kron32(bf16)");
+            return 0;
+        }
+    }
     if (lanes == 4) NSB_KRON(4, 4);
     else NSB_KRON(8, 4);
 #undef NSB_KRON
@@ -219,16 +240,23 @@ int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* 
     const int pb = NSB_PAD32(A->bs);
     int32_t nown = INT32_MAX;
     const float* xg = x;
+    const bool shadow = epi && epi->x_h && A->bs == 3 && A->diag32;
+    const unsigned long long* xgh = shadow ? epi->x_h : nullptr;
     if (ctx->nranks > 1) {
         NSB_REQUIRE(ctx, A->halo == NSB_HALO_NODES || A->halo == NSB_HALO_VERTS, "matrix of a partitioned run needs a halo index space");
         const nsb_halo& H = ctx->halo[A->halo];
         NSB_REQUIRE(ctx, H.n_owned == A->nrows, "matrix rows are not the owned prefix of the halo plan");
-        if (nsb_halo_exchange(ctx, A->halo, pb / 2, reinterpret_cast<const double*>(x), nullptr, st)) return -1;
         nown = H.n_owned;
-        xg = reinterpret_cast<const float*>(H.ghostbuf) - (int64_t)nown * pb;
+        if (shadow) {     // only the gathered copy travels: 8 bytes per node instead of 16
+            if (nsb_halo_exchange(ctx, A->halo, 1, reinterpret_cast<const double*>(epi->x_h), nullptr, st)) return -1;
+            xgh = reinterpret_cast<const unsigned long long*>(H.ghostbuf) - (int64_t)nown;
+        } else {
+            if (nsb_halo_exchange(ctx, A->halo, pb / 2, reinterpret_cast<const double*>(x), nullptr, st)) return -1;
+            xg = reinterpret_cast<const float*>(H.ghostbuf) - (int64_t)nown * pb;
+        }
     }
     NSB_TIMED(ctx, NSB_T_SPMV_BSR32, st);
-    if (A->diag32) return A->bs == 3 ? launch_spmv_kron32<3>(ctx, A, x, nown, xg, y, epi, st) : launch_spmv_kron32<2>(ctx, A, x, nown, xg, y, epi, st);
+    if (A->diag32) return A->bs == 3 ? launch_spmv_kron32<3>(ctx, A, x, nown, xg, y, epi, st, xgh) : launch_spmv_kron32<2>(ctx, A, x, nown, xg, y, epi, st);
     NSB_COUNT(ctx, 1);
     if (A->bs == 3) return launch_spmv_bsr_tma<3, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);
     return launch_spmv_bsr_tma<2, float, float>(ctx, A, A->vals32, x, nown, xg, y, st);

@@ -22,6 +22,9 @@ class MixedSolverBase(SolverBase):
         super().__init__(mesh, boundary_markers, form_convective_term, form_viscous_term)
         assert linear_solver in ("auto", "gmres", "direct")
         self._linear_solver, self._linear_rtol, self._gmres_restart = linear_solver, linear_rtol, gmres_restart
+        # knobs of the block-triangular preconditioner (nsb_saddle): inner CG tolerance, velocity-block Chebyshev
+        # degree and the ratio lambda_max / lambda_min of its interval
+        self.saddle_options = dict(inner_rtol=1e-2, vel_degree=8, vel_ratio=30.0, lp_degree=8, lp_ratio=300.0)
         self.krylov_iterations, self.inner_iterations = [], 0
         self.dev = dev = Device(mesh, device_index, mixed=True)
         self._nW = dev.spaces.ndofs_W
@@ -152,6 +155,7 @@ class MixedSolverBase(SolverBase):
         dev.inv_diagonal(self._Mp, self._Mp_dinv)
         dev.inv_diagonal(self._Lp, self._Lp_dinv)
         lmax = 1.1 * dev.lambda_max(self._Lp, self._Lp_dinv, iters=30)
+        so = self.saddle_options
         self._saddle_work = dev.empty(nu + 11 * npr)
         self._Amat = dev.matrix("WW", self._A, L.CSR, 1)
         self._A_dinv = dev.empty(self._nW)
@@ -160,8 +164,9 @@ class MixedSolverBase(SolverBase):
         cp2 = co["pressure_term"] ** 2
         self._saddle = L.Saddle(nu, npr, self._Mp, self._Lp, self._Mp_dinv.data_ptr(), self._Lp_dinv.data_ptr(),
                                 self._p_ident.data_ptr() if self._p_ident is not None else None,
-                                co["viscous_term"] / cp2, 0.0, 0 if lmask.any() else 1, 8, 0.0, 0.0,
-                                8, lmax / 300.0, lmax, 1e-2, 2000, 0, self._saddle_work.data_ptr(), 0)
+                                co["viscous_term"] / cp2, 0.0, 0 if lmask.any() else 1, int(so["vel_degree"]), 0.0, 0.0,
+                                int(so["lp_degree"]), lmax / so["lp_ratio"], lmax, float(so["inner_rtol"]), 5000, 0,
+                                self._saddle_work.data_ptr(), 0)
         self._vel_lmax = None
         del C
 
@@ -177,7 +182,7 @@ class MixedSolverBase(SolverBase):
         dev.inv_diagonal(self._Amat, self._A_dinv)
         if self._vel_lmax is None:
             self._vel_lmax = 1.1 * dev.saddle_lambda_max(self._Amat, self._A_dinv, S.n_u, iters=12, work=self._gmres_work)
-        S.vel_lambda_max, S.vel_lambda_min = self._vel_lmax, self._vel_lmax / 30.0
+        S.vel_lambda_max, S.vel_lambda_min = self._vel_lmax, self._vel_lmax / self.saddle_options["vel_ratio"]
         pc = L.Precond(L.PC_SADDLE, 1, self._A_dinv.data_ptr(), 0.0, 0.0, 0, 0, C.pointer(S))
         self._dx.zero_()
         t0 = S.inner_iterations
