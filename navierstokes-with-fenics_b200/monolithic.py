@@ -24,7 +24,7 @@ class MixedSolverBase(SolverBase):
         self._linear_solver, self._linear_rtol, self._gmres_restart = linear_solver, linear_rtol, gmres_restart
         # knobs of the block-triangular preconditioner (nsb_saddle): inner CG tolerance, velocity-block Chebyshev
         # degree and the ratio lambda_max / lambda_min of its interval
-        self.saddle_options = dict(inner_rtol=1e-2, vel_degree=8, vel_ratio=30.0, lp_degree=8, lp_ratio=300.0)
+        self.saddle_options = dict(inner_rtol=1e-2, vel_degree=8, vel_ratio=8.0, lp_degree=8, lp_ratio=300.0)
         self.krylov_iterations, self.inner_iterations = [], 0
         self.dev = dev = Device(mesh, device_index, mixed=True)
         self._nW = dev.spaces.ndofs_W
