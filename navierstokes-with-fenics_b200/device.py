@@ -267,6 +267,11 @@ class Device:
     def upload(self, array):
         return torch.from_numpy(np.ascontiguousarray(array)).to(self.torch_device)
 
+    def host_buffer(self, n):
+        """pinned host staging buffer (plain host memory when the device is not a CUDA device: CPU test doubles)"""
+        t = torch.empty(int(n), dtype=torch.float64)
+        return t.pin_memory() if self.torch_device.type == "cuda" else t
+
     def zeros(self, n, dtype=torch.float64):
         return torch.zeros(int(n), dtype=dtype, device=self.torch_device)
 

@@ -94,6 +94,11 @@ class SimplexMesh:
             ok &= inside_fn(X[:, j, :])
         self.bfacet_marker[ok] = int(marker)
 
+    def _unmarked(self):
+        """all facet markers back to 0 (the dolfin-named compat layer lets the caller's SubDomains mark them)"""
+        self.bfacet_marker[:] = 0
+        return self
+
     def boundary_ids(self):
         """``extract_all_boundary_markers`` (source/auxiliary_methods.py:56-67)"""
         if getattr(self, "global_boundary_ids", None) is not None:   # local mesh of a partition

@@ -47,7 +47,7 @@ class IPCSSolver(SolverBase):
                  momentum_preconditioner="chebyshev", chebyshev_degree=8, chebyshev_ratio=30.0, partition=None,
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard",
-                 linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True):
+                 linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True, device=None):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -82,7 +82,8 @@ class IPCSSolver(SolverBase):
         # that bound the partitioned runs -- and fewer launches on one GPU
         self._p_pc = (pressure_preconditioner, pressure_chebyshev_degree, pressure_chebyshev_ratio)
         self._mom_pc, self._cheb_degree, self._cheb_ratio = momentum_preconditioner, chebyshev_degree, chebyshev_ratio
-        self.dev = dev = Device(mesh, device_index, partition=partition)
+        # ``device``: an existing Device of this mesh (the dolfin-named compatibility layer shares one per mesh)
+        self.dev = dev = device if device is not None else Device(mesh, device_index, partition=partition)
         sp = dev.spaces
         nV, nQ = sp.ndofs_V, sp.ndofs_Q                      # local: owned + ghost
         self._nV_own, self._nQ_own = sp.dim * dev.n_owned_nodes, dev.n_owned_verts
@@ -97,7 +98,7 @@ class IPCSSolver(SolverBase):
         self._extrapolate_p = extrapolate_pressure_guess
         self._p_hist, self._p_hist_steps, self._prev_k = None, 0, None
         # work space
-        p22, p11 = dev.patterns["P2P2"], dev.patterns["P1P1"]
+        p22, p11 = dev.pattern("P2P2"), dev.pattern("P1P1")
         d = sp.dim
         self._A_mom = dev.empty(p22.nnz * d * d)
         # single-precision copy of the Jacobian values, read only by the SpMVs INSIDE the Chebyshev
@@ -189,8 +190,8 @@ class IPCSSolver(SolverBase):
             return 0
         sp = self.dev.spaces
         if not hasattr(self, "_vbc_host"):
-            self._vbc_host = torch.empty(self._vbc_vals.numel(), dtype=torch.float64).pin_memory()
-            self._pbc_host = torch.empty(self._pbc_vals.numel(), dtype=torch.float64).pin_memory()
+            self._vbc_host = self.dev.host_buffer(self._vbc_vals.numel())
+            self._pbc_host = self.dev.host_buffer(self._pbc_vals.numel())
             self._vbc_host.copy_(self._vbc_vals)
             self._pbc_host.copy_(self._pbc_vals)
         if self._time_dependent_bcs:
@@ -239,7 +240,7 @@ class IPCSSolver(SolverBase):
         w = self.solution
         if out is None:
             if not hasattr(self, "_w_host"):
-                self._w_host = torch.empty(w.numel(), dtype=torch.float64).pin_memory()
+                self._w_host = self.dev.host_buffer(w.numel())
             out = self._w_host
         out.copy_(w, non_blocking=True)
         torch.cuda.current_stream(self.dev.torch_device).synchronize()
@@ -325,7 +326,13 @@ class IPCSSolver(SolverBase):
         return dev.norm(self._bV)
 
     def _solve_time_step(self):
-        """source/ns_ipcs_solver.py:198-208"""
+        """source/ns_ipcs_solver.py:198-208: the three sub-step solvers in sequence"""
+        self._solve_diffusion_step()
+        self._solve_projection_step()
+        self._solve_correction_step()
+
+    def _solve_diffusion_step(self):
+        """``self._diffusion_solver.solve()`` (source/ns_ipcs_solver.py:202; forms :106-147)"""
         dev, d = self.dev, self.dev.dim
         ustar = self._intermediate_velocity
         # (1) tentative velocity: dolfin NewtonSolver semantics (atol = tol, rtol = 10 tol)
@@ -383,8 +390,12 @@ class IPCSSolver(SolverBase):
         self.newton_residual = r
         if not converged:
             raise NewtonNotConverged("Newton solver did not converge (%d iterations, residual %g)" % (it, r))
-        # (2) pressure Poisson
-        a0 = self._alpha[0]
+        self._kry_momentum = kry
+
+    def _solve_projection_step(self):
+        """``self._projection_solver.solve()`` (source/ns_ipcs_solver.py:205; forms :149-171)"""
+        dev = self.dev
+        ustar = self._intermediate_velocity
         dev.assemble_poisson(L.VEC, pn=self._old_pressure, ustar=ustar, b=self._bQ)
         self._extrapolate_pressure_guess()
         if self._p_replicated:
@@ -398,7 +409,12 @@ class IPCSSolver(SolverBase):
             n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol,
                             nullspace=True, work=self._work)
             dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
-        # (3) velocity correction
+        self._kry_pressure = n_p
+
+    def _solve_correction_step(self):
+        """``self._velocity_correction_solver.solve()`` (source/ns_ipcs_solver.py:208; forms :173-196)"""
+        dev, d = self.dev, self.dev.dim
+        ustar = self._intermediate_velocity
         dev.assemble_correction(L.VEC, ustar=ustar, pnew=self._pressure, pold=self._old_pressure, b=self._bV)
         dev.bc_apply_vector(L.BC_LINEAR, self._bV, self._vbc_dofs, self._vbc_vals)
         dev.copy(ustar, self._velocities[0])
@@ -407,8 +423,7 @@ class IPCSSolver(SolverBase):
                         work=self._work)
         dev.halo_exchange(L.HALO_NODES, d, self._velocities[0])
         dev.halo_status()
-        self.krylov_iterations.append(dict(momentum=kry, pressure=n_p, correction=n_c))
-        del a0
+        self.krylov_iterations.append(dict(momentum=self._kry_momentum, pressure=self._kry_pressure, correction=n_c))
 
     def _extrapolate_pressure_guess(self):
         """x0 of the pressure CG: ``_pressure`` holds p^n on entry; with the history vector p^{n-1} it becomes
