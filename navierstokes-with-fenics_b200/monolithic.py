@@ -14,7 +14,7 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged
 
 class MixedSolverBase(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=1,
-                 linear_solver="auto", linear_rtol=1e-12, gmres_restart=60, form_viscous_term="standard"):
+                 linear_solver="auto", linear_rtol=1e-13, gmres_restart=60, form_viscous_term="standard"):
         """``linear_solver`` (K16, the Newton update the reference hands to sparse LU): "gmres" = hand-written
         flexible GMRES with the block-triangular Cahouet-Chabard preconditioner (csrc/krylov.cu saddle_apply);
         "direct" = cuSOLVER sparse QR (library leg); "auto" = direct below 20 000 dofs and for stationary problems

@@ -13,7 +13,7 @@ from .monolithic import MixedSolverBase
 
 class StationarySolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", tol=1e-10, maxiter=50,
-                 tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-12,
+                 tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-13,
                  form_viscous_term="standard"):
         super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol,
                          form_viscous_term=form_viscous_term)
