@@ -213,8 +213,10 @@ def algorithmic_bytes(solver):
         "spmv_bsr": 8 * 9 * nnz22 + 4 * nnz22 + 16 * nV + 4 * nnodes,
         # single-precision SpMV of the preconditioner on the block-scalar part of J: one float + one column
         # index per block entry, x and y as one float4 per node, row offsets
-        # + the Chebyshev step fused into its epilogue: r and z read + written, d_new written (float4 each), D^-1
-        "spmv_bsr_f32": 4 * nnz22 + 4 * nnz22 + 4 * nnodes + (16 + 32 + 32 + 16 + 24) * nnodes,
+        # + the Chebyshev step fused into its epilogue: r and z read + written, d_new written (float4 each), D^-1;
+        # the gathered copy of x is its bf16 shadow (8 B per node read, 8 B written for d_new), x itself is read once
+        # (own row, float4)
+        "spmv_bsr_f32": 4 * nnz22 + 4 * nnz22 + 4 * nnodes + (16 + 8 + 8 + 32 + 32 + 16 + 24) * nnodes,
         "spmv_csr": None,                                       # two different matrices share the class
         "asm_jacobian": 8 * 9 * nnz22 + geo + 8 * nV,
         "asm_residual": 8 * nV + geo + 8 * (3 * nV + nQ),
@@ -392,7 +394,7 @@ def run_nsb200(args):
     traffic = None
     if n == 73 and world == 1:
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_x_ncu_full_summary.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r2_ncu_full_summary.json")) as f:
                 traffic = json.load(f)[dom]["traffic_bytes"]
         except (OSError, ValueError, KeyError):
             traffic = None
