@@ -179,3 +179,71 @@ def test_partitioned_ipcs_matches_single_gpu(cfg, transport):
     assert rep["halo_transport"] == transport
     assert rep["ok"] and rep["rel_err_velocity"] < 1e-8 and rep["rel_err_pressure"] < 1e-8
     assert rep["newton"]["partitioned"] == rep["newton"]["single"]
+
+
+# ---- replicated pressure solve (ipcs.py::_solve_pressure_replicated): host logic over gloo --------
+def _p1_stiffness_apply(coords, cells, p):
+    """y = K p for the P1 Laplacian, cell by cell (plain numpy; rows of vertices whose cells are all present are complete)"""
+    d = coords.shape[1]
+    X = coords[cells]
+    J = X[:, 1:, :] - X[:, :1, :]                                  # rows = edge vectors
+    det = np.abs(np.linalg.det(J))
+    fact = {2: 2.0, 3: 6.0}[d]
+    Gref = np.concatenate([-np.ones((1, d)), np.eye(d)], axis=0)   # reference gradients of the barycentric functions
+    G = np.einsum("ak,cki->cai", Gref, np.linalg.inv(J).transpose(0, 2, 1))
+    Ke = np.einsum("c,cai,cbi->cab", det / fact, G, G)
+    y = np.zeros(len(coords))
+    np.add.at(y, cells, np.einsum("cab,cb->ca", Ke, p[cells]))
+    return y
+
+
+def _replicated_worker(rank, world, port, dim, n, out):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, ROOT)
+    import nsb200
+    from nsb200 import partition as P
+    mesh = _mesh(dim, n)
+    part = P.build_partition(mesh, rank, world)
+    nQo, gid = part.verts.n_owned, part.vert_gid
+    p_glob = _field(np.arange(mesh.num_vertices) * 1.0)
+    # owned rows of the LOCAL operator applied to the local [owned | ghost] view of a global field ...
+    y_loc = _p1_stiffness_apply(part.mesh.coords, part.mesh.cells, p_glob[gid])
+    # ... scattered into a zeroed global vector and summed over ranks (one contributor per entry) ...
+    b_g = np.zeros(mesh.num_vertices)
+    b_g[gid[:nQo]] = y_loc[:nQo]
+    t = torch.from_numpy(b_g)
+    dist.all_reduce(t)
+    # ... equal the global operator applied to the global field; every rank holds the same bits afterwards
+    y_ref = _p1_stiffness_apply(part.global_mesh.coords, part.global_mesh.cells, p_glob)
+    ok = bool(np.allclose(t.numpy(), y_ref, rtol=0, atol=1e-12 * np.abs(y_ref).max()))
+    same = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(same, t)
+    ok &= all(bool(torch.equal(same[0], s)) for s in same)
+    # gather back: local [owned | ghost] entries of the global solution
+    ok &= bool(np.array_equal(p_glob[gid], _field(gid * 1.0)))
+    ok &= len(np.unique(gid)) == len(gid)
+    cnt = torch.zeros(mesh.num_vertices, dtype=torch.float64)
+    cnt[torch.from_numpy(gid[:nQo].astype(np.int64))] = 1.0
+    dist.all_reduce(cnt)
+    ok &= bool((cnt == 1.0).all())                                  # each global vertex is owned exactly once
+    flag = torch.tensor([1.0 if ok else 0.0])
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        with open(out, "w") as f:
+            json.dump({"ok": bool(flag.item() == 1.0)}, f)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("dim,n", [(2, (5, 6)), (3, (3, 3, 4))])
+def test_replicated_pressure_rhs_over_gloo_world_size_2(tmp_path, dim, n):
+    """scatter of the owned right-hand-side rows + one all-reduce reproduces the global right-hand side bit-identically
+    on every rank, and the global solution gathers back to the local numbering"""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "result.json")
+    port = 29900 + (os.getpid() + dim) % 90
+    mp.spawn(_replicated_worker, args=(2, port, dim, n, out), nprocs=2, join=True)
+    with open(out) as f:
+        assert json.load(f)["ok"]
