@@ -195,7 +195,10 @@ class SolverBase:
         if getattr(self, "_omega_now", None) is not None and c_cor is not None:
             om = np.atleast_1d(np.asarray(self._omega_now, dtype=np.float64))
             om3 = np.zeros(3)
-            om3[2 if len(om) == 1 else slice(0, 3)] = om
+            if len(om) == 1:
+                om3[2] = om[0]
+            else:
+                om3[:] = om
             cor = 2.0 * c_cor * om3
         dev.set_forms(self._form_convective_term.value - 1, self._form_viscous_term.value - 1, cor)
         self._forms_dirty = False
