@@ -223,7 +223,7 @@ def algorithmic_bytes(solver):
     }, dict(nV=nV, nQ=nQ, nnz22=nnz22, nnz11=nnz11)
 
 
-def make_cavity_solver(n, rank=0, world=1, local=0):
+def make_cavity_solver(n, rank=0, world=1, local=0, **solver_options):
     """the C5 problem on the n^3 x 6 unit cube: lid (1,0,0) on y = 1, no-slip elsewhere, from rest"""
     import nsb200
     V = nsb200.VelocityBCType
@@ -234,7 +234,7 @@ def make_cavity_solver(n, rank=0, world=1, local=0):
         from nsb200 import partition as npart
         part = npart.connect_distributed(npart.build_partition(mesh, rank, world))
     ts = nsb200.BDFTimeStepping(0.0, 1.0e6, order=2, desired_start_time_step=DT)
-    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=local, partition=part)
+    solver = nsb200.IPCSSolver(mesh, markers, "standard", ts, device_index=local, partition=part, **solver_options)
     solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / RE))
     solver.set_boundary_conditions([(V.no_slip, w, None) for w in (1, 2, 3, 5, 6)] + [(V.constant, 4, (1.0, 0.0, 0.0))])
     return solver, ts

@@ -211,19 +211,22 @@ int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows,
                     const int32_t* pair_ptr_dev, const int32_t* pair_cell_dev,
                     const uint8_t* pair_iloc_dev, const uint8_t* pair_slots_dev);
 /* Conflict-free scatter schedule of the warp-cooperative matrix assembly (csrc/assemble_jac.cu):
- * rows grouped (<= 32 incidence pairs, <= max_blocks entries), and per chunk of 32 pairs a proper
- * edge colouring of the (pair, entry) graph so that all lanes of a warp add into distinct entries
- * in every round.  nsb_sched_build is host-only; call it with group_row_host == NULL to obtain
- * counts3 = {groups, chunks, rounds}, then with buffers group_row[groups+1], chunk_first[groups+1],
- * round_ptr[chunks+1], sched[32*rounds].  nsb_set_schedule registers the device copies
- * (group_max_entries = the max_blocks used).  Without a schedule the generic kernels are used. */
+ * rows grouped (<= 32 incidence pairs, <= max_blocks slots), and per chunk of 32 pairs a proper
+ * edge colouring of the (pair, slot) graph so that all lanes of a warp add into distinct slots
+ * in every round, preferring rounds without shared-memory bank conflicts.  Entries with many
+ * contributions (the diagonal of a vertex row) get shadow slots behind the group's real entries; the
+ * fold list (real entry << 16 | shadow slot) says which copies are added up before the rows are written.
+ * nsb_sched_build is host-only; call it with group_row_host == NULL to obtain
+ * counts4 = {groups, chunks, rounds, folds}, then with buffers group_row[groups+1], chunk_first[groups+1],
+ * round_ptr[chunks+1], sched[32*rounds], fold_ptr[groups+1], fold[folds].  nsb_set_schedule registers the
+ * device copies (group_max_entries = the max_blocks used).  Without a schedule the generic kernels are used. */
 int nsb_sched_build(int32_t nrows, const int32_t* rowptr_host, const int32_t* pair_ptr_host,
-                    const uint8_t* pair_slots_host, int32_t nloc, int32_t max_blocks, int64_t* counts3,
+                    const uint8_t* pair_slots_host, int32_t nloc, int32_t max_blocks, int64_t* counts4,
                     int32_t* group_row_host, int32_t* chunk_first_host, int32_t* round_ptr_host,
-                    uint16_t* sched_host);
+                    uint16_t* sched_host, int32_t* fold_ptr_host, uint32_t* fold_host);
 int nsb_set_schedule(nsb_ctx* ctx, int32_t which, int32_t ngroups, int32_t group_max_entries,
                      const int32_t* group_row_dev, const int32_t* chunk_first_dev, const int32_t* round_ptr_dev,
-                     const uint16_t* sched_dev);
+                     const uint16_t* sched_dev, const int32_t* fold_ptr_dev, const uint32_t* fold_dev);
 /* Caller-owned device workspace of the two-phase (element vectors per cell -> gather per row) vector assembly
  * kernels: ncells * nsb_scratch_doubles_per_cell(d) doubles (= NL2 * d).  Without it the one-thread-per-row
  * kernels are used.  NULL / 0 unregisters. */

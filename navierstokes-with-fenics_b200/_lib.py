@@ -69,8 +69,8 @@ PROTOTYPES = {
     "nsb_tiles_build": (C.c_int, [C.c_int32, vp, C.c_int32, c_i32p, vp]),
     "nsb_set_mesh": (C.c_int, [vp, C.c_int32, C.c_int32, vp, C.c_int32, vp, C.c_int32, vp]),
     "nsb_set_pattern": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
-    "nsb_sched_build": (C.c_int, [C.c_int32, vp, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]),
-    "nsb_set_schedule": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp]),
+    "nsb_sched_build": (C.c_int, [C.c_int32, vp, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp, vp]),
+    "nsb_set_schedule": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "nsb_set_scratch": (C.c_int, [vp, vp, C.c_int64]),
     "nsb_scratch_doubles_per_cell": (C.c_int, [C.c_int32]),
     "nsb_set_mixed_dofmap": (C.c_int, [vp, C.c_int32, vp]),

@@ -18,8 +18,10 @@
 //            group's rows held in shared memory.  The host-built schedule is a proper edge
 //            colouring of the pair/entry graph: within a round all lanes hit distinct entries,
 //            so the shared-memory read-modify-writes need no atomics and the summation order
-//            is fixed.  Finally the group's rows -- one contiguous range of the BSR value
-//            array -- are written with fully coalesced stores.
+//            is fixed; it prefers rounds without bank conflicts, and entries with many contributions
+//            (diagonal of a vertex row) are spread over shadow slots that are folded at the end.
+//            Finally the group's rows -- one contiguous range of the BSR value array -- are written
+//            with fully coalesced stores.
 // Every value is written to global memory exactly once, by one warp, in a fixed order:
 // bit-reproducible, no atomics, no colouring of cells, no read-modify-write traffic on HBM.
 #define NSB_TABLE static __device__ constexpr
@@ -54,7 +56,8 @@ struct JacCfg {
     // shared tables indexed by the run-time row index I (T padded to 4 columns for 128-bit loads)
     static constexpr int TAB_T = NL * NL * 4, TAB_M = NL * NL, TAB_D = NL * NL * NS;
     static constexpr int TAB = TAB_T + TAB_M + TAB_D;
-    static constexpr int PER_WARP = MAXB * DD + 32 * SSTR + ((MAXB * DD + 32 * SSTR) & 1);   // doubles
+    static constexpr int SROUNDS = 32;                            // rounds of one chunk staged in shared memory (64 B each)
+    static constexpr int PER_WARP = MAXB * DD + 32 * SSTR + ((MAXB * DD + 32 * SSTR) & 1) + SROUNDS * 8;   // doubles
     static constexpr size_t SMEM = sizeof(double) * (TAB + WARPS * PER_WARP);
 };
 
@@ -67,6 +70,7 @@ template <int D>
 __global__ void __launch_bounds__(JacCfg<D>::WARPS * 32, 3)
 k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, const int32_t* __restrict__ chunk_first,
                      const int32_t* __restrict__ round_ptr, const uint16_t* __restrict__ sched,
+                     const int32_t* __restrict__ fold_ptr, const uint32_t* __restrict__ fold,
                      const int32_t* __restrict__ rowptr, const int32_t* __restrict__ pair_ptr,
                      const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
                      const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
@@ -82,6 +86,8 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     double* rowbuf = sD2 + C::TAB_D + (size_t)w * C::PER_WARP;
     double* sS = rowbuf + C::MAXB * DD;
+    // the chunk's schedule, copied asynchronously while phase A runs (16-byte aligned: every part above is even)
+    uint16_t* ssched = reinterpret_cast<uint16_t*>(rowbuf + C::PER_WARP - C::SROUNDS * 8);
 
     // tables indexed by the run-time row index I -> shared memory
     for (int e = threadIdx.x; e < NL * NL; e += blockDim.x) {
@@ -99,12 +105,21 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
         const int32_t e_lo = rowptr[row_lo], nval = (rowptr[row_hi] - e_lo) * DD;
         const int32_t p_lo = pair_ptr[row_lo], p_hi = pair_ptr[row_hi];
         const int32_t c_lo = chunk_first[grp], c_hi = chunk_first[grp + 1];
-        for (int e = lane; e < nval; e += 32) rowbuf[e] = 0.0;
+        const int32_t f_lo = fold_ptr[grp], f_hi = fold_ptr[grp + 1];
+        for (int e = lane; e < nval + (f_hi - f_lo) * DD; e += 32) rowbuf[e] = 0.0;   // real entries, then shadow slots
         for (int32_t ch = c_lo; ch < c_hi; ++ch) {
             const int32_t q0 = p_lo + 32 * (ch - c_lo);
             const int npc = min(32, p_hi - q0);
             const int32_t r_lo = round_ptr[ch], r_hi = round_ptr[ch + 1];
-            unsigned e_next = r_lo < r_hi ? sched[(int64_t)r_lo * 32 + lane] : 0xFFFFu;
+            const int nstaged = min(r_hi - r_lo, C::SROUNDS);
+            {   // rounds x 64 B -> 16-byte granules, lane-strided: coalesced, no register staging
+                const uint16_t* src = sched + (int64_t)r_lo * 32;
+                for (int gidx = lane; gidx < nstaged * 4; gidx += 32) {
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(ssched + gidx * 8);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + gidx * 8) : "memory");
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
             int I = 0;
             double g[DD][4];      // g[b*D+a][M] = c_c detJ d_a u_b (x_M), registers
 #pragma unroll
@@ -203,13 +218,13 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                     st[J] = mcd * mI[J] + c_visc * vis + c_conv * cv;
                 }
             }
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
             __syncwarp();
             // ---------------------------------------------------------------- phase B: scheduled scatter
             const double* myS = sS + lane * SSTR;
             const double* myT = sT + I * NL * 4;
             for (int32_t t = r_lo; t < r_hi; ++t) {
-                const unsigned e = e_next;
-                if (t + 1 < r_hi) e_next = sched[(int64_t)(t + 1) * 32 + lane];
+                const unsigned e = t - r_lo < nstaged ? ssched[(t - r_lo) * 32 + lane] : sched[(int64_t)t * 32 + lane];
                 if (e != 0xFFFFu) {
                     const int J = e & 15u;
                     double* dst = rowbuf + (e >> 4) * DD;
@@ -229,6 +244,12 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                 __syncwarp();
             }
         }
+        // shadow copies of the hot entries -> their real entry, in list order (copies of one entry are consecutive)
+        for (int32_t f = f_lo; f < f_hi; ++f) {
+            const uint32_t it = fold[f];
+            if (lane < DD) rowbuf[(it >> 16) * DD + lane] += rowbuf[(it & 0xFFFFu) * DD + lane];
+            __syncwarp();
+        }
         // the group's rows: one contiguous range of the value array, written once, coalesced
         double* out = vals + (int64_t)e_lo * DD;
         for (int e = lane; e < nval; e += 32) out[e] = rowbuf[e];
@@ -242,7 +263,7 @@ template <int D>
 static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double* ustar, double mass_coef,
                             int newton, double* A_out, cudaStream_t st) {
     using C = JacCfg<D>;
-    if (!P.group_row || !P.chunk_first || !P.round_ptr || !P.sched || P.ngroups <= 0 || P.group_max_entries > C::MAXB)
+    if (!P.group_row || !P.chunk_first || !P.round_ptr || !P.sched || !P.fold_ptr || P.ngroups <= 0 || P.group_max_entries > C::MAXB)
         return 1;
     static bool configured = false;
     if (!configured) {
@@ -257,7 +278,7 @@ static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double
     const int64_t need = ((int64_t)P.ngroups + C::WARPS - 1) / C::WARPS;
     if (blocks > need) blocks = need;
     k_jacobian_rowgroups<D><<<(int)blocks, C::WARPS * 32, C::SMEM, st>>>(
-        P.ngroups, P.group_row, P.chunk_first, P.round_ptr, P.sched, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
+        P.ngroups, P.group_row, P.chunk_first, P.round_ptr, P.sched, P.fold_ptr, P.fold, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
         ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
     NSB_LAUNCH_CHECK(ctx, "k_jacobian_rowgroups");
     return 0;

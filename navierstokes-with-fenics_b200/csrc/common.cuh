@@ -26,6 +26,8 @@ struct nsb_pattern_dev {
     const int32_t* chunk_first = nullptr;   // [ngroups+1]
     const int32_t* round_ptr = nullptr;     // [nchunks+1]
     const uint16_t* sched = nullptr;        // [32 * nrounds]
+    const int32_t* fold_ptr = nullptr;      // [ngroups+1]
+    const uint32_t* fold = nullptr;         // [nfold] real entry << 16 | shadow slot
 };
 
 struct nsb_coef {

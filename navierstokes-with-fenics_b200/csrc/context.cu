@@ -80,15 +80,16 @@ extern "C" int nsb_set_pattern(nsb_ctx* ctx, int32_t which, int32_t nrows, const
 
 extern "C" int nsb_set_schedule(nsb_ctx* ctx, int32_t which, int32_t ngroups, int32_t group_max_entries,
                                 const int32_t* group_row, const int32_t* chunk_first, const int32_t* round_ptr,
-                                const uint16_t* sched) {
+                                const uint16_t* sched, const int32_t* fold_ptr, const uint32_t* fold) {
     NSB_REQUIRE(ctx, ctx != nullptr, "null context");
     NSB_REQUIRE(ctx, which >= 0 && which < 3, "unknown pattern id");
-    NSB_REQUIRE(ctx, ngroups > 0 && group_max_entries > 0 && group_row && chunk_first && round_ptr && sched,
+    NSB_REQUIRE(ctx, ngroups > 0 && group_max_entries > 0 && group_row && chunk_first && round_ptr && sched && fold_ptr,
                 "bad schedule arrays");
     nsb_pattern_dev& P = ctx->pat[which];
     NSB_REQUIRE(ctx, P.nrows > 0, "set the pattern before its schedule");
     P.ngroups = ngroups; P.group_max_entries = group_max_entries; P.group_row = group_row;
     P.chunk_first = chunk_first; P.round_ptr = round_ptr; P.sched = sched;
+    P.fold_ptr = fold_ptr; P.fold = fold;
     return 0;
 }
 

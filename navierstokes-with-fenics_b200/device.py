@@ -55,16 +55,17 @@ class Pattern:
         self.sched = None
         if nlc <= 15 and nlr == nlc:
             # conflict-free scatter schedule of the warp-cooperative matrix assembly
-            cnt = (C.c_int64 * 3)()
+            cnt = (C.c_int64 * 4)()
             a_ = (nrows, rowptr.ctypes.data, pair_ptr.ctypes.data, pair_slots.ctypes.data, nlc, L.SCHED_MAX_BLOCKS)
-            if lib.nsb_sched_build(*a_, cnt, None, None, None, None) == 0:
+            if lib.nsb_sched_build(*a_, cnt, None, None, None, None, None, None) == 0:
                 g_row, c_first = np.empty(cnt[0] + 1, np.int32), np.empty(cnt[0] + 1, np.int32)
                 r_ptr, sched = np.empty(cnt[1] + 1, np.int32), np.empty(32 * cnt[2], np.uint16)
+                f_ptr, fold = np.empty(cnt[0] + 1, np.int32), np.empty(max(int(cnt[3]), 1), np.uint32)
                 L.check(lib.nsb_sched_build(*a_, cnt, g_row.ctypes.data, c_first.ctypes.data, r_ptr.ctypes.data,
-                                            sched.ctypes.data))
-                # uint16 travels as int16 bit patterns (torch has no uint16 arithmetic, none is needed)
+                                            sched.ctypes.data, f_ptr.ctypes.data, fold.ctypes.data))
+                # unsigned words travel as signed bit patterns (torch has no unsigned arithmetic, none is needed)
                 self.sched = (int(cnt[0]), dev.upload(g_row), dev.upload(c_first), dev.upload(r_ptr),
-                              dev.upload(sched.view(np.int16)))
+                              dev.upload(sched.view(np.int16)), dev.upload(f_ptr), dev.upload(fold.view(np.int32)))
         up = dev.upload
         self.rowptr, self.col = up(rowptr), up(col)
         self.pair_ptr, self.pair_cell = up(pair_ptr), up(pair_cell)
@@ -305,9 +306,9 @@ class Device:
                                                 _ptr(pat.pair_ptr), _ptr(pat.pair_cell), _ptr(pat.pair_iloc),
                                                 _ptr(pat.pair_slots)))
             if pat.sched is not None:
-                ng, g_row, c_first, r_ptr, sched = pat.sched
+                ng, g_row, c_first, r_ptr, sched, f_ptr, fold = pat.sched
                 self.check(self.lib.nsb_set_schedule(self.ctx, which, ng, L.SCHED_MAX_BLOCKS, _ptr(g_row),
-                                                     _ptr(c_first), _ptr(r_ptr), _ptr(sched)))
+                                                     _ptr(c_first), _ptr(r_ptr), _ptr(sched), _ptr(f_ptr), _ptr(fold)))
             self.patterns[name] = pat
         return self.patterns[name]
 
