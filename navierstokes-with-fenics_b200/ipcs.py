@@ -44,7 +44,7 @@ def initial_fields(dev, initial_conditions):
 class IPCSSolver(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
                  device_index=0, linear_rtol=1e-12, gmres_restart=40, cache_constant_matrices=True,
-                 momentum_preconditioner="chebyshev", chebyshev_degree=8, chebyshev_ratio=30.0, partition=None,
+                 momentum_preconditioner="chebyshev", chebyshev_degree=10, chebyshev_ratio=30.0, partition=None,
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard",
                  linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True, device=None,
