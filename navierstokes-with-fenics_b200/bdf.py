@@ -13,9 +13,10 @@ from .monolithic import MixedSolverBase
 
 class ImplicitBDFSolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term, time_stepping, tol=1e-10, max_iter=50,
-                 device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-13, form_viscous_term="standard"):
+                 device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-13, form_viscous_term="standard",
+                 device=None):
         super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol,
-                         form_viscous_term=form_viscous_term)
+                         form_viscous_term=form_viscous_term, device=device)
         assert isinstance(max_iter, int) and max_iter > 0 and isinstance(tol, float) and tol > 0.0
         assert hasattr(time_stepping, "n_levels") and hasattr(time_stepping, "coefficients")
         self._time_stepping = time_stepping

@@ -220,7 +220,7 @@ def _cpp_to_python(code):
 
 
 _MATH = {"sin": np.sin, "cos": np.cos, "tan": np.tan, "exp": np.exp, "sqrt": np.sqrt, "pow": np.power, "log": np.log,
-         "abs": np.abs, "pi": math.pi, "DOLFIN_EPS": DOLFIN_EPS, "DOLFIN_PI": math.pi, "atan2": np.arctan2,
+         "abs": np.abs, "pi": math.pi, "DOLFIN_EPS": DOLFIN_EPS, "DOLFIN_PI": math.pi, "M_PI": math.pi, "atan2": np.arctan2,
          "tanh": np.tanh, "cosh": np.cosh, "sinh": np.sinh, "near": lambda a, b, eps=DOLFIN_EPS: abs(a - b) < eps}
 
 
@@ -430,6 +430,19 @@ class _Vector:
 
     def __getitem__(self, i):
         return self.get_local()[i]
+
+
+class _RawVectorOwner:
+    """owner of a bare device tensor that lives on the space of ``like`` (the residual vector of a NewtonSolver)"""
+
+    def __init__(self, tensor, like):
+        self._tensor, self._like = tensor, like
+
+    def _dev(self):
+        return self._like._dev()
+
+    def function_space(self):
+        return self._like.function_space()
 
 
 def Vector(v):
@@ -697,17 +710,38 @@ class NonlinearProblem:
 
 
 class SystemAssembler:
-    def __init__(self, *a, **k):
-        raise NotImplementedError("the stationary Picard / Newton path (SystemAssembler) runs through the nsb200 mirror "
-                                  "class StationarySolver; the compat layer covers the instationary IPCS path")
+    """``SystemAssembler(J, F, bcs)`` of source/auxiliary_classes.py:141: bound to the stationary mixed problem"""
+
+    def __init__(self, J, F, bcs):
+        from .backend import StationaryBinding
+        self._binding = StationaryBinding(J, F, bcs)
+
+    def assemble(self, *args):
+        from .backend import _MatrixHandle
+        if len(args) == 2 and all(isinstance(a, _Vector) for a in args):
+            b, x = args
+            self._binding.assemble_vector(b._f._tensor, x._f._tensor)
+        elif len(args) == 1 and isinstance(args[0], _MatrixHandle):
+            self._binding.assemble_matrix()
+        else:
+            raise NotImplementedError("SystemAssembler.assemble(b, x) and .assemble(A) are the calls of this path")
 
 
 class NewtonSolver:
+    """``dlfn.NewtonSolver(comm, linear_solver, factory)`` with a ``NonlinearProblem`` (source/ns_solver_base.py:938-983):
+    dolfin's loop (residual criterion), the problem's ``F(b, x)`` / ``J(A, x)`` called back every iteration, the update
+    solved on the device (K16)"""
+
     def __init__(self, *a, **k):
         self.parameters = _Parameters()
+        self.parameters.update(absolute_tolerance=1e-10, relative_tolerance=1e-9, maximum_iterations=50,
+                               error_on_nonconvergence=True)
 
     def solve(self, problem, x):
-        raise NotImplementedError("NewtonSolver with a NonlinearProblem callback: use nsb200.StationarySolver")
+        binding = getattr(getattr(problem, "assembler", None), "_binding", None)
+        if binding is None or not isinstance(x, _Vector):
+            raise NotImplementedError("NewtonSolver.solve: the problem must assemble through a SystemAssembler")
+        return binding.newton(problem, x, self.parameters)
 
 
 class PETScLUSolver:

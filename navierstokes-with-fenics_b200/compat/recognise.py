@@ -129,3 +129,92 @@ def recognise_ipcs_correction(a, L, u):
     if out["c_u"] is None or len(out["grads"]) != 2:
         raise Unrecognised("velocity correction: a right-hand-side term is missing")
     return out
+
+
+# ---- monolithic problems on the mixed space W (source/ns_bdf_solver.py:36-100, source/ns_solver_base.py:894-949) -----
+#   F = -c_p div(u) q + sum_i alpha_i / k (u_i . w) + c_c (grad(u) u) . w - c_p div(w) p + c_nu grad(u) : grad(w)
+#   J_newton = derivative(F, w_h) ;  J_picard = -c_p div(v) q + c_c (grad(v) u) . w - c_p div(w) r + c_nu grad(v) : grad(w)
+def _sig_mixed(m, roles):
+    """signature of a monomial whose leaves are parts of ``dlfn.split`` (ListTensor with split_of / index): the parts of
+    the test function are w / q, of the trial function v / r, of the functions in ``roles`` <name>u / <name>p"""
+    def names(leaf):
+        from .dolfin import Argument
+        parent = getattr(leaf, "split_of", None)
+        if parent is None:
+            return "?%s" % type(leaf).__name__
+        if isinstance(parent, Argument):
+            return (("w", "q") if parent.number == 0 else ("v", "r"))[leaf.index]
+        for name, obj in roles.items():
+            if obj is parent:
+                return name + ("u", "p")[leaf.index]
+        return "?Function"
+    return X.atom_signature(m.atom, names)
+
+
+def _split_parents(monos):
+    from .dolfin import Function
+    seen = []
+    for m in monos:
+        for leaf in X.atom_leaves(m.atom):
+            parent = getattr(leaf, "split_of", None)
+            if isinstance(parent, Function) and all(parent is not s for s in seen):
+                seen.append(parent)
+    return seen
+
+
+def recognise_mixed_residual(F, w):
+    """returns dict(solution, history {h1: Function, ...}, acc {"s" | "h<i>": [monomials alpha_i / k]} (empty for the
+    stationary problem), c_div, c_conv, c_p, c_visc as monomials)"""
+    monos = _monomials(F)
+    parents = _split_parents(monos)
+    if all(p is not w for p in parents):
+        raise Unrecognised("mixed residual: the unknown does not appear in the form")
+    roles = {"s": w}
+    for i, f in enumerate(p for p in parents if p is not w):
+        roles["h%d" % (i + 1)] = f
+    out = dict(solution=w, acc={}, c_div=None, c_conv=None, c_p=None, c_visc=None)
+    for m in monos:
+        s = _sig_mixed(m, roles)
+        if s.startswith("dot(") and s.endswith("u,w)") and s.count("(") == 1:
+            out["acc"].setdefault(s[4:-4], []).append(m)
+        elif s in ("mul(div(su),q)", "mul(q,div(su))") and out["c_div"] is None:
+            out["c_div"] = m
+        elif s == "dot(dot(grad(su),su),w)" and out["c_conv"] is None:
+            out["c_conv"] = m
+        elif s in ("mul(div(w),sp)", "mul(sp,div(w))") and out["c_p"] is None:
+            out["c_p"] = m
+        elif s == "inner(grad(su),grad(w))" and out["c_visc"] is None:
+            out["c_visc"] = m
+        else:
+            raise Unrecognised("term %s of the mixed residual is not in the compat vocabulary (standard convective form, "
+                               "reduced viscous form, no body force / tractions); the nsb200 mirror classes cover the "
+                               "other weak-form variants" % s)
+    if None in (out["c_div"], out["c_conv"], out["c_p"], out["c_visc"]):
+        raise Unrecognised("mixed residual: a term of the mass / momentum balance is missing")
+    if out["acc"] and "s" not in out["acc"]:
+        raise Unrecognised("mixed residual: the acceleration term does not contain the unknown velocity")
+    out["history"] = {k: roles[k] for k in out["acc"] if k != "s"}
+    return out
+
+
+def recognise_mixed_jacobian(J, F, w):
+    """"newton" for dlfn.derivative(F, w), "picard" for the frozen-convection bilinear form of
+    source/ns_solver_base.py:929-934 (its coefficients must be the residual's)"""
+    if isinstance(J, X.Derivative):
+        if J.form is not F or J.u is not w:
+            raise Unrecognised("the Newton Jacobian must be dlfn.derivative(F, w) of the same residual")
+        return "newton"
+    res = recognise_mixed_residual(F, w)
+    roles = {"s": w}
+    seen = dict(c_div=None, c_conv=None, c_p=None, c_visc=None)
+    for m in _monomials(J):
+        s = _sig_mixed(m, roles)
+        key = {"mul(div(v),q)": "c_div", "mul(q,div(v))": "c_div", "dot(dot(grad(v),su),w)": "c_conv",
+               "mul(div(w),r)": "c_p", "mul(r,div(w))": "c_p", "inner(grad(v),grad(w))": "c_visc"}.get(s)
+        if key is None or seen[key] is not None:
+            raise Unrecognised("term %s of the Picard Jacobian is not in the compat vocabulary" % s)
+        seen[key] = m
+    for key, m in seen.items():
+        if m is None or abs(m.value() - res[key].value()) > 1e-14 * abs(res[key].value()):
+            raise Unrecognised("the Picard Jacobian's %s does not match the residual's" % key)
+    return "picard"

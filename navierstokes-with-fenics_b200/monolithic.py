@@ -14,7 +14,7 @@ from .solver_base import SolverBase, Expression, NewtonNotConverged
 
 class MixedSolverBase(SolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", device_index=0, reorder=1,
-                 linear_solver="auto", linear_rtol=1e-13, gmres_restart=60, form_viscous_term="standard"):
+                 linear_solver="auto", linear_rtol=1e-13, gmres_restart=60, form_viscous_term="standard", device=None):
         """``linear_solver`` (K16, the Newton update the reference hands to sparse LU): "gmres" = hand-written
         flexible GMRES with the block-triangular Cahouet-Chabard preconditioner (csrc/krylov.cu saddle_apply);
         "direct" = cuSOLVER sparse QR (library leg); "auto" = direct below 20 000 dofs and for stationary problems
@@ -26,9 +26,10 @@ class MixedSolverBase(SolverBase):
         # degree and the ratio lambda_max / lambda_min of its interval
         self.saddle_options = dict(inner_rtol=1e-2, vel_degree=8, vel_ratio=8.0, lp_degree=8, lp_ratio=300.0)
         self.krylov_iterations, self.inner_iterations = [], 0
-        self.dev = dev = Device(mesh, device_index, mixed=True)
+        # ``device``: an existing Device of this mesh (the dolfin-named compat layer shares one per mesh)
+        self.dev = dev = Device(mesh, device_index, mixed=True) if device is None else device
         self._nW = dev.spaces.ndofs_W
-        self._pat = dev.patterns["WW"]
+        self._pat = dev.pattern("WW")
         self._A = dev.empty(self._pat.nnz)
         self._b, self._dx = dev.empty(self._nW), dev.empty(self._nW)
         self._reorder = reorder

@@ -14,9 +14,9 @@ from .monolithic import MixedSolverBase
 class StationarySolver(MixedSolverBase):
     def __init__(self, mesh, boundary_markers, form_convective_term="standard", tol=1e-10, maxiter=50,
                  tol_picard=1e-2, maxiter_picard=10, device_index=0, reorder=1, linear_solver="auto", linear_rtol=1e-13,
-                 form_viscous_term="standard"):
+                 form_viscous_term="standard", device=None):
         super().__init__(mesh, boundary_markers, form_convective_term, device_index, reorder, linear_solver, linear_rtol,
-                         form_viscous_term=form_viscous_term)
+                         form_viscous_term=form_viscous_term, device=device)
         assert isinstance(maxiter, int) and maxiter > 0 and isinstance(tol, float) and tol > 0.0
         assert isinstance(maxiter_picard, int) and maxiter_picard > 0 and isinstance(tol_picard, float)
         self._tol, self._maxiter = tol, maxiter
@@ -29,13 +29,16 @@ class StationarySolver(MixedSolverBase):
     def _system(self, picard, matrix):
         """SystemAssembler(J, F, bcs).assemble(...): b (and A) with the symmetric elimination;
         returns ||b||"""
+        self._assemble_system(picard, matrix)
+        return self.dev.norm(self._b)
+
+    def _assemble_system(self, picard, matrix):
         flags = L.VEC | L.SYMBC | (L.PICARD if picard else 0) | (L.MAT if matrix else 0)
         self.dev.assemble_mixed(flags, self._solution, b=self._b, A=self._A if matrix else None)
         if self._loadW is not None:
             # the external load enters b_e linearly and the local elimination overwrites only Dirichlet rows:
             # adding the global load on all other rows equals assembling it cell by cell
             self.dev.axpy(1.0, self._loadW, self._b)
-        return self.dev.norm(self._b)
 
     def solve(self):
         """source/ns_solver_base.py:951-988"""
@@ -52,11 +55,11 @@ class StationarySolver(MixedSolverBase):
         if residual < self._tol_picard:          # :966-970: lower the Picard tolerance below the start residual
             order = math.floor(math.log10(residual))
             self._tol_picard = (residual / 10.0 ** order - 1.0) * 10.0 ** order
-        it_p = self._newton(lambda: self._system(True, False), lambda: self._system(True, True), self._solution,
+        it_p = self._newton(lambda: self._system(True, False), lambda: self._assemble_system(True, True), self._solution,
                             atol=self._tol_picard, rtol=1e-9, maxit=self._maxiter_picard,
                             error_on_nonconvergence=self._error_on_nonconvergence)
         self._error_on_nonconvergence = False
-        it_n = self._newton(lambda: self._system(False, False), lambda: self._system(False, True), self._solution,
+        it_n = self._newton(lambda: self._system(False, False), lambda: self._assemble_system(False, True), self._solution,
                             atol=self._tol, rtol=1e-9, maxit=self._maxiter, error_on_nonconvergence=False)
         self.newton_iterations = [it_p, it_n]
         residual = self._system(False, False)

@@ -84,6 +84,17 @@ class RecordingDevice(Device):
     def assemble_correction(self, flags, ustar=None, pnew=None, pold=None, b=None, A=None):
         self._rec("assemble_correction", flags, ustar, pnew, pold, b, A)
 
+    def assemble_mixed(self, flags, w0, w1=None, w2=None, b=None, A=None):
+        self._rec("assemble_mixed", flags, w0, w1, w2, b, A)
+
+    def set_mixed_bc(self, mask, g):
+        self._mixed_bc = (mask, g)
+        self._rec("set_mixed_bc", mask, g)
+
+    def direct_solve(self, pattern, vals, b, x, reorder=1):
+        self._rec("direct_solve", pattern, vals, b, x, reorder)
+        x.zero_()
+
     def assemble_p1_mass(self, flags, w=None, A=None):
         self._rec("assemble_p1_mass", flags, w, A)
 
