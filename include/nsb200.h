@@ -313,6 +313,19 @@ int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const dou
  * three iterations then track the slowly moving spectrum. */
 int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, int32_t warm_start,
                    double* work, double* lambda_out_host, void* stream);
+/* Successive right-hand sides (Fischer 1998) for a solve that is repeated with the same SPD operator every time
+ * step -- the pressure projection, source/ns_ipcs_solver.py:149-171, 205.  X / AX: caller-owned lmax x n arrays
+ * (lmax <= 16) holding an A-orthonormal basis of the previous solutions and its image; l = the number of vectors in
+ * use (host integer owned by the caller, start at 0).  nsb_rhs_guess: x = sum_k (X_k . b) X_k (x untouched when
+ * l == 0).  nsb_rhs_update (after the solve): appends the A-orthogonal part of x; a full basis first drops its
+ * older half (lmax / 2 vectors stay); work: 2 n doubles.  The solve itself keeps its tolerance: only its iteration count changes. */
+int nsb_rhs_guess(nsb_ctx* ctx, int64_t n, int32_t l, const double* X_dev, const double* b_dev, double* x_dev, void* stream);
+int nsb_rhs_update(nsb_ctx* ctx, const nsb_matrix* A, int32_t* l_inout_host, int32_t lmax, double* X_dev, double* AX_dev,
+                   const double* x_dev, double* work_dev, void* stream);
+/* The same power iteration on the single-precision block-scalar copy A->diag32 (the operator the f32 Chebyshev
+ * preconditioner of nsb_gmres is a polynomial of): one f32 SpMV per iteration.  work: 2 x 16/12 x n bytes <= 2 n doubles. */
+int nsb_lambda_max32(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, int32_t warm_start,
+                   double* work, double* lambda_out_host, void* stream);
 
 /* Function.assign / Vector ops (source/ns_ipcs_solver.py:41-43, source/ns_solver_base.py:1015-1016) */
 int nsb_vec_copy(nsb_ctx* ctx, int64_t n, const double* x, double* y, void* stream);

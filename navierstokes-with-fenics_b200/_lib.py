@@ -90,6 +90,9 @@ PROTOTYPES = {
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
+    "nsb_rhs_guess": (C.c_int, [vp, C.c_int64, C.c_int32, vp, vp, vp, vp]),
+    "nsb_rhs_update": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(C.c_int32), C.c_int32, vp, vp, vp, vp, vp]),
+    "nsb_lambda_max32": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
     "nsb_saddle_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
     "nsb_cg": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(Precond), vp, vp, C.c_double, C.c_double, C.c_int32, C.c_int32,
                          vp, c_i32p, c_f64p, vp]),

@@ -400,6 +400,83 @@ extern "C" int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* i
     return 0;
 }
 
+// ---- the same on the single-precision block-scalar operator the polynomial preconditioner is built from ------
+// The Chebyshev iteration of apply_cheb32 runs on S (x) I (nsb_matrix.diag32), so the interval it needs is the
+// spectrum of D^-1 (S (x) I), and a power iteration with the 0.27 ms f32 SpMV costs a fifth of the FP64 one.
+// work: 2 x PAD32(bs) x nrows floats (<= 2 n doubles); the iterate stays there for warm starts.
+template <int BS>
+__global__ void k_pi32_init(int64_t nnodes, float* __restrict__ x) {
+    GRID_STRIDE(i, nnodes) {
+        float c[BS];
+#pragma unroll
+        for (int b = 0; b < BS; ++b) {
+            uint32_t h = (uint32_t)(i * BS + b) * 2654435761u;
+            h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+            c[b] = 0.5f + (float)(h & 0xffffu) / 65536.0f;
+        }
+        Pad32<BS>::st(x, i, c);
+    }
+}
+// x = (D^-1 q) / sqrt(prev) ; out = sum x^2 (accumulated in FP64)
+template <int BS>
+__global__ void __launch_bounds__(256)
+k_pi32_step(int64_t nnodes, const double* __restrict__ dinv, const float* __restrict__ q, const double* prev2,
+            float* __restrict__ x, double* partials, unsigned int* counter, double* out) {
+    const double sc = prev2 ? 1.0 / sqrt(*prev2) : 1.0;
+    double s[1] = {0.0};
+    GRID_STRIDE(i, nnodes) {
+        float qi[BS], c[BS];
+        Pad32<BS>::ld(q, i, qi);
+#pragma unroll
+        for (int b = 0; b < BS; ++b) {
+            const double vi = dinv[i * BS + b] * (double)qi[b] * sc;
+            c[b] = (float)vi;
+            s[0] += vi * vi;
+        }
+        Pad32<BS>::st(x, i, c);
+    }
+    __shared__ double red[8];
+    grid_sum<1, 256>(s, partials, counter, out, red);
+}
+
+template <int BS>
+static int lambda_max32(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, int32_t warm_start,
+                        double* work, double* lambda_out, cudaStream_t st) {
+    constexpr int PB = BS == 3 ? 4 : BS;
+    const int64_t nn = A->nrows;
+    const int G = krylov_grid(ctx, nn);
+    float* x = reinterpret_cast<float*>(((uintptr_t)work + 15) & ~(uintptr_t)15);
+    float* q = x + PB * nn;
+    double* ds = ctx->d_scalars;
+    if (!warm_start) {
+        k_pi32_init<BS><<<G, 256, 0, st>>>(nn, x);
+        NSB_LAUNCH_CHECK(ctx, "k_pi32_init");
+    }
+    for (int k = 0; k <= iters; ++k) {
+        if (nsb_launch_spmv32(ctx, A, x, q, st)) return -1;
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_pi32_step<BS><<<G, 256, 0, st>>>(nn, inv_diag, q, k == 0 ? nullptr : ds + S_H1 + ((k - 1) & 1), x, ctx->d_partials,
+                                               ctx->d_counter, ds + S_H1 + (k & 1));
+        }
+        NSB_LAUNCH_CHECK(ctx, "k_pi32_step");
+        if (nsb_allreduce_sum(ctx, ds + S_H1 + (k & 1), 1, st)) return -1;
+    }
+    if (fetch(ctx, S_H1, 2, st)) return -1;
+    *lambda_out = sqrt(ctx->h_scalars[S_H1 + (iters & 1)]);
+    return 0;
+}
+
+extern "C" int nsb_lambda_max32(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters,
+                                int32_t warm_start, double* work, double* lambda_out, void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, A && inv_diag && work && lambda_out && iters >= 1, "bad arguments");
+    NSB_REQUIRE(ctx, A->diag32 && nsb_spmv32_available(A), "nsb_lambda_max32 needs the block-scalar single-precision copy (diag32)");
+    cudaStream_t st = (cudaStream_t)stream;
+    return A->bs == 3 ? lambda_max32<3>(ctx, A, inv_diag, iters, warm_start, work, lambda_out, st)
+                      : lambda_max32<2>(ctx, A, inv_diag, iters, warm_start, work, lambda_out, st);
+}
+
 // ---------------------------------------------------------------------------------------------
 // CG
 // ---------------------------------------------------------------------------------------------
@@ -635,6 +712,102 @@ k_combine(int64_t n, int nk, const double* __restrict__ V, const double* __restr
 __global__ void __launch_bounds__(256)
 k_add(int64_t n, const double* __restrict__ t, double* __restrict__ x) {
     GRID_STRIDE(i, n) x[i] += t[i];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Successive right-hand sides (Fischer, Comput. Methods Appl. Mech. Engrg. 163, 1998): the pressure Poisson
+// problem of source/ns_ipcs_solver.py:149-171 is solved with the SAME operator at every time step.  X holds up to
+// lmax A-orthonormal vectors spanning the previous solutions, AX their images.  nsb_rhs_guess gives the best
+// approximation of A^-1 b in span(X) in the energy norm, x = sum_k (X_k . b) X_k, as the initial guess of the CG
+// (the solve itself still runs to its tolerance: only the iteration count changes); nsb_rhs_update adds the part
+// of the new solution that is A-orthogonal to the basis (one SpMV, one Gram-Schmidt pass) and, when the basis is
+// full, drops its older half.
+// ---------------------------------------------------------------------------------------------
+#define NSB_RHS_MAX_BASIS 16
+
+extern "C" int nsb_rhs_guess(nsb_ctx* ctx, int64_t n, int32_t l, const double* X, const double* b, double* x,
+                             void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, n > 0 && l >= 0 && l <= NSB_RHS_MAX_BASIS && X && b && x, "bad arguments");
+    if (l == 0) return 0;                                   // no history: the caller's x stays the guess
+    cudaStream_t st = (cudaStream_t)stream;
+    const int G = krylov_grid(ctx, n);
+    double* ds = ctx->d_scalars;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_multi_dot<16><<<G, 256, 0, st>>>(n, 0, l, X, b, ctx->d_partials, ctx->d_counter, ds + S_H1);
+    }
+    NSB_LAUNCH_CHECK(ctx, "nsb_rhs_guess dots");
+    if (nsb_allreduce_sum(ctx, ds + S_H1, l, st)) return -1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_combine<<<G, 256, 0, st>>>(n, l, X, ds + S_H1, x);
+    }
+    NSB_LAUNCH_CHECK(ctx, "nsb_rhs_guess combine");
+    NSB_COUNT(ctx, 2);
+    return 0;
+}
+
+extern "C" int nsb_rhs_update(nsb_ctx* ctx, const nsb_matrix* A, int32_t* l_inout, int32_t lmax, double* X, double* AX,
+                              const double* x, double* work, void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, A && l_inout && X && AX && x && work && lmax >= 1 && lmax <= NSB_RHS_MAX_BASIS &&
+                *l_inout >= 0 && *l_inout <= lmax, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = (int64_t)A->nrows * A->bs;
+    const int G = krylov_grid(ctx, n);
+    double* ds = ctx->d_scalars;
+    int l = *l_inout;
+    if (l == lmax) {
+        // full: drop the OLDER half.  A subset of an A-orthonormal set is A-orthonormal, so the newer half moves to
+        // the front as it is (lmax == 1: plain restart from the current solution)
+        const int keep = lmax / 2;
+        for (int k = 0; k < keep; ++k) {
+            NSB_CUDA(ctx, cudaMemcpyAsync(X + (int64_t)k * n, X + (int64_t)(lmax - keep + k) * n, sizeof(double) * n,
+                                          cudaMemcpyDeviceToDevice, st));
+            NSB_CUDA(ctx, cudaMemcpyAsync(AX + (int64_t)k * n, AX + (int64_t)(lmax - keep + k) * n, sizeof(double) * n,
+                                          cudaMemcpyDeviceToDevice, st));
+        }
+        l = keep;
+    }
+    double *w = work, *aw = work + n;
+    NSB_CUDA(ctx, cudaMemcpyAsync(w, x, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
+    if (nsb_launch_spmv(ctx, A, w, aw, nullptr, nullptr, st)) return -1;
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_reduce<true><<<G, 256, 0, st>>>(n, w, aw, ctx->d_partials, ctx->d_counter, ds + S_TMP);      // x . A x
+    }
+    if (nsb_allreduce_sum(ctx, ds + S_TMP, 1, st)) return -1;
+    if (l > 0) {
+        {
+            NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+            k_multi_dot<16><<<G, 256, 0, st>>>(n, 0, l, AX, w, ctx->d_partials, ctx->d_counter, ds + S_H1);
+        }
+        if (nsb_allreduce_sum(ctx, ds + S_H1, l, st)) return -1;
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_multi_axpy<<<G, 256, 0, st>>>(n, l, X, ds + S_H1, w, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+        k_multi_axpy<<<G, 256, 0, st>>>(n, l, AX, ds + S_H1, aw, ctx->d_partials, ctx->d_counter, ds + S_NRM);
+    }
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_reduce<true><<<G, 256, 0, st>>>(n, w, aw, ctx->d_partials, ctx->d_counter, ds + S_OUT);      // delta . A delta
+    }
+    NSB_LAUNCH_CHECK(ctx, "nsb_rhs_update");
+    if (nsb_allreduce_sum(ctx, ds + S_OUT, 1, st)) return -1;
+    NSB_CUDA(ctx, cudaMemcpyAsync(ctx->h_scalars + S_OUT, ds + S_OUT, sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (fetch(ctx, S_TMP, 1, st)) return -1;
+    const double s = ctx->h_scalars[S_OUT], xAx = ctx->h_scalars[S_TMP];
+    NSB_COUNT(ctx, 6);
+    // nothing new (the guess was already the solution), or a direction lost to round-off: keep the basis as it is
+    if (!(s > 1e-24 * xAx) || !(xAx > 0.0)) { *l_inout = l; return 0; }
+    {
+        NSB_TIMED(ctx, NSB_T_KRYLOV, st);
+        k_normalize<<<G, 256, 0, st>>>(n, w, ds + S_OUT, X + (int64_t)l * n);
+        k_normalize<<<G, 256, 0, st>>>(n, aw, ds + S_OUT, AX + (int64_t)l * n);
+    }
+    NSB_LAUNCH_CHECK(ctx, "nsb_rhs_update normalize");
+    *l_inout = l + 1;
+    return 0;
 }
 
 #define NSB_GMRES_MAX_RESTART 60

@@ -418,16 +418,32 @@ class Device:
     def _pc(self, M):
         return M if isinstance(M, L.Precond) else self.precond(M)
 
-    def lambda_max(self, A, inv_diag, iters=12, work=None, warm_start=False):
-        """``warm_start``: ``work`` (kept by the caller between calls) still holds the previous iterate"""
+    def lambda_max(self, A, inv_diag, iters=12, work=None, warm_start=False, lowp=False):
+        """``warm_start``: ``work`` (kept by the caller between calls) still holds the previous iterate;
+        ``lowp``: power iteration on the single-precision block-scalar copy (nsb_lambda_max32)"""
         n = A.nrows * A.bs
         if work is None or work.numel() < 2 * n:
             assert not warm_start, "a warm start needs the work vector of the previous call"
             work = self.empty(2 * n)
         out = C.c_double()
-        self.check(self.lib.nsb_lambda_max(self.ctx, C.byref(A), _ptr(inv_diag), iters, 1 if warm_start else 0,
-                                           _ptr(work), C.byref(out), self.stream))
+        fn = self.lib.nsb_lambda_max32 if lowp else self.lib.nsb_lambda_max
+        self.check(fn(self.ctx, C.byref(A), _ptr(inv_diag), iters, 1 if warm_start else 0, _ptr(work), C.byref(out),
+                      self.stream))
         return out.value
+
+    def rhs_basis(self, n, lmax=10):
+        """state of the successive-right-hand-side projection (nsb_rhs_guess / nsb_rhs_update) for a system of size n"""
+        return dict(n=n, lmax=lmax, l=C.c_int32(0), X=self.empty(lmax * n), AX=self.empty(lmax * n), work=self.empty(2 * n))
+
+    def rhs_guess(self, basis, b, x):
+        self.check(self.lib.nsb_rhs_guess(self.ctx, basis["n"], basis["l"].value, _ptr(basis["X"]), _ptr(b), _ptr(x),
+                                          self.stream))
+        return basis["l"].value
+
+    def rhs_update(self, basis, A, x):
+        self.check(self.lib.nsb_rhs_update(self.ctx, C.byref(A), C.byref(basis["l"]), basis["lmax"], _ptr(basis["X"]),
+                                           _ptr(basis["AX"]), _ptr(x), _ptr(basis["work"]), self.stream))
+        return basis["l"].value
 
     def saddle_lambda_max(self, A, inv_diag, n_u, iters=12, work=None):
         """largest eigenvalue of D^-1 F, F = velocity block of the mixed matrix ``A``"""

@@ -48,7 +48,7 @@ class IPCSSolver(SolverBase):
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard",
                  linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True, device=None,
-                 newton_forcing=0.003):
+                 newton_forcing=0.003, pressure_rhs_projection=10):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -84,6 +84,11 @@ class IPCSSolver(SolverBase):
         # ten times above Newton's own tolerance, i.e. when a second, exact update is certain to follow.  0 switches it
         # off (every update to linear_rtol * r0); the first step of a run has no history and is solved exactly.
         self._newton_forcing, self._newton_rho = float(newton_forcing), None
+        # Pressure projection: the same SPD operator every step -> initial guess = energy-norm best approximation of the
+        # new solution in the span of the last `pressure_rhs_projection` solutions (Fischer 1998; nsb_rhs_guess /
+        # nsb_rhs_update).  Used for the all-Neumann problem on one GPU and in the replicated solve; 0 = off (then the
+        # guess is the linear extrapolation of the last two pressures).  The CG tolerance is unchanged.
+        self._p_basis_size, self._p_basis = int(pressure_rhs_projection), None
         self._cache = cache_constant_matrices
         assert momentum_preconditioner in ("jacobi", "chebyshev")
         assert pressure_preconditioner in ("jacobi", "chebyshev")
@@ -366,8 +371,10 @@ class IPCSSolver(SolverBase):
                     warm = self._pi_work is not None
                     if not warm:
                         self._pi_work = dev.empty(2 * self._nV_own)
+                    # on the block-scalar f32 operator when that is what the polynomial is built from
                     self._lmax = 1.1 * dev.lambda_max(self._jac, self._dinvV, iters=1 if warm else 8,
-                                                      work=self._pi_work, warm_start=warm)
+                                                      work=self._pi_work, warm_start=warm,
+                                                      lowp=self._S_mom32 is not None)
                 pc = dev.precond(self._dinvV, L.PC_CHEBYSHEV, self._cheb_degree, self._lmax / self._cheb_ratio,
                                  self._lmax, lowp=self._pc_lowp)
             else:
@@ -426,10 +433,23 @@ class IPCSSolver(SolverBase):
             n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol, work=self._work)
             dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
         else:
+            basis = self._pressure_basis(dev, self._pressure.numel()) if dev.partition is None else None
+            if basis is not None:
+                dev.rhs_guess(basis, self._bQ, self._pressure)
             n_p, _ = dev.cg(self._lap, self._pcQ, self._bQ, self._pressure, rtol=self._linear_rtol,
                             nullspace=True, work=self._work)
+            if basis is not None:
+                dev.rhs_update(basis, self._lap, self._pressure)
             dev.halo_exchange(L.HALO_VERTS, 1, self._pressure)
         self._kry_pressure = n_p
+
+    def _pressure_basis(self, dev, n):
+        """the successive-right-hand-side basis of the all-Neumann pressure problem (None: switched off)"""
+        if self._p_basis_size <= 0 or self._pressure_dirichlet:
+            return None
+        if self._p_basis is None or self._p_basis["n"] != n:
+            self._p_basis = dev.rhs_basis(n, min(self._p_basis_size, 16))
+        return self._p_basis
 
     def _solve_correction_step(self):
         """``self._velocity_correction_solver.solve()`` (source/ns_ipcs_solver.py:208; forms :173-196)"""
@@ -494,8 +514,13 @@ class IPCSSolver(SolverBase):
         if self._pressure_dirichlet:
             pdev.bc_apply_vector(L.BC_LINEAR, self._bQ_g, self._pbc_dofs_g, self._pbc_vals_g)
             pdev.bc_apply_vector(L.BC_LINEAR, self._p_g, self._pbc_dofs_g, self._pbc_vals_g)
+        basis = self._pressure_basis(pdev, self._p_g.numel())
+        if basis is not None:
+            pdev.rhs_guess(basis, self._bQ_g, self._p_g)
         n_p, _ = pdev.cg(self._lap_g, self._pcQ, self._bQ_g, self._p_g, rtol=self._linear_rtol,
                          nullspace=not self._pressure_dirichlet, work=self._work_g)
+        if basis is not None:
+            pdev.rhs_update(basis, self._lap_g, self._p_g)
         dev.gather(self._loc_gid, self._p_g, self._pressure)
         return n_p
 

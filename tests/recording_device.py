@@ -107,9 +107,21 @@ class RecordingDevice(Device):
     def inv_diagonal(self, A, out):
         self._rec("inv_diagonal", out)
 
-    def lambda_max(self, A, inv_diag, iters=12, work=None, warm_start=False):
+    def lambda_max(self, A, inv_diag, iters=12, work=None, warm_start=False, lowp=False):
         self._rec("lambda_max", iters, bool(warm_start))
         return 2.0
+
+    def rhs_basis(self, n, lmax=10):
+        return dict(n=n, lmax=lmax, l=0)
+
+    def rhs_guess(self, basis, b, x):
+        self._rec("rhs_guess", basis["l"], b, x)
+        return basis["l"]
+
+    def rhs_update(self, basis, A, x):
+        basis["l"] = min(basis["l"] + 1, basis["lmax"])
+        self._rec("rhs_update", basis["l"], x)
+        return basis["l"]
 
     def block_scalar_f32(self, vals, bs, out):
         self._rec("block_scalar_f32", vals, bs, out)

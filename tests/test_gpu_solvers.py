@@ -217,6 +217,85 @@ def test_gmres_chebyshev_precisions(case):
     assert its["f32-scalar", 4, 40] <= 1.5 * its["f64", 4, 40] + 3, its
 
 
+def test_successive_rhs_projection(case):
+    """nsb_rhs_guess / nsb_rhs_update (Fischer 1998) on the all-Neumann P1 Laplacian: the basis is A-orthonormal, its
+    image is A X, the guess for a right-hand side whose solution lies in the span is that solution, and a basis that
+    is full drops its older half"""
+    import nsb200._lib as L
+    dev = case["dev"]
+    pat = dev.patterns["P1P1"]
+    n = pat.nrows
+    A = dev.empty(pat.nnz)
+    dev.assemble_poisson(L.MAT, A=A)
+    Ah = sp.csr_matrix((A.cpu().numpy(), pat.col_host, pat.rowptr_host), shape=(n, n))
+    mat = dev.matrix("P1P1", A, L.CSR, 1)
+    rng = np.random.default_rng(23)
+    sols = [rng.uniform(-1, 1, n) for _ in range(5)]
+    sols = [x - x.mean() for x in sols]
+    lmax = 4
+    basis = dev.rhs_basis(n, lmax)
+    for k, x in enumerate(sols[:lmax]):
+        assert dev.rhs_update(basis, mat, up(dev, x)) == k + 1
+    X = basis["X"].cpu().numpy().reshape(lmax, n)
+    AX = basis["AX"].cpu().numpy().reshape(lmax, n)
+    assert np.abs(X @ (Ah @ X.T) - np.eye(lmax)).max() < 1e-10
+    assert rel_max_err(AX, (Ah @ X.T).T) < 1e-11
+    # span(X) = span(sols[:4]): the guess for b = A (combination of them) is that combination
+    target = 0.3 * sols[0] - 1.2 * sols[2] + 0.5 * sols[3]
+    g = dev.zeros(n)
+    assert dev.rhs_guess(basis, up(dev, Ah @ target), g) == lmax
+    assert rel_max_err(g.cpu().numpy(), target) < 1e-9
+    # a full basis drops its older half (the newer half stays A-orthonormal as it is), then takes the new direction
+    assert dev.rhs_update(basis, mat, up(dev, sols[4])) == lmax // 2 + 1
+    X2 = basis["X"].cpu().numpy().reshape(lmax, n)[:lmax // 2 + 1]
+    assert np.array_equal(X2[:lmax // 2], X[lmax - lmax // 2:]) and np.abs(X2 @ (Ah @ X2.T) - np.eye(len(X2))).max() < 1e-10
+    basis2 = dev.rhs_basis(n, lmax)
+    dev.rhs_update(basis2, mat, up(dev, sols[0]))
+    assert dev.rhs_update(basis2, mat, up(dev, 2.5 * sols[0])) == 1      # parallel to the basis: not added
+    for x in sols[1:4]:
+        dev.rhs_update(basis2, mat, up(dev, x))
+    assert basis2["l"].value == lmax
+    dev.rhs_update(basis2, mat, up(dev, sols[4]))
+    # the guess shortens the solve, the answer stays the CG's
+    dinv = dev.empty(n)
+    dev.inv_diagonal(mat, dinv)
+    b = Ah @ (sols[4] + 1e-3 * sols[1])
+    xa, xb = dev.zeros(n), dev.zeros(n)
+    it_cold, _ = dev.cg(mat, dinv, up(dev, b), xa, rtol=1e-12, nullspace=True)
+    dev.rhs_guess(basis2, up(dev, b), xb)
+    it_warm, _ = dev.cg(mat, dinv, up(dev, b), xb, rtol=1e-12, nullspace=True)
+    assert it_warm < it_cold and rel_max_err(xb.cpu().numpy(), xa.cpu().numpy()) < 1e-9
+
+
+def test_lambda_max_on_the_block_scalar_copy(case):
+    """nsb_lambda_max32: power iteration on the f32 block-scalar copy S (x) I of the momentum Jacobian, against the
+    largest eigenvalue of D^-1 (S (x) I) computed on the host"""
+    import torch
+    import nsb200._lib as L
+    dev, d = case["dev"], case["d"]
+    us = case["fields"][0]
+    pat = dev.patterns["P2P2"]
+    A = dev.empty(pat.nnz * d * d)
+    dev.assemble_ipcs_momentum(L.MAT, up(dev, 0.1 * us), A=A)
+    S32 = dev.empty(pat.nnz, dtype=torch.float32)
+    dev.block_scalar_f32(A, d, S32)
+    mat = dev.matrix("P2P2", A, L.BSR, d, None, diag32=S32)
+    n = pat.nrows * d
+    dinv = dev.empty(n)
+    dev.inv_diagonal(mat, dinv)
+    work = dev.empty(2 * n)
+    lam32 = dev.lambda_max(mat, dinv, iters=60, work=work, lowp=True)
+    Sh = sp.csr_matrix((S32.cpu().numpy().astype(np.float64), pat.col_host, pat.rowptr_host), shape=(pat.nrows, pat.nrows))
+    K = sp.kron(Sh, sp.identity(d)).tocsr()
+    M = sp.diags(dinv.cpu().numpy()) @ K
+    lam_ref = float(np.abs(spla.eigs(M, k=1, which="LM", return_eigenvectors=False, tol=1e-10)[0]))
+    assert abs(lam32 - lam_ref) < 2e-2 * lam_ref, (lam32, lam_ref)
+    lam_warm = dev.lambda_max(mat, dinv, iters=1, work=work, warm_start=True, lowp=True)
+    assert abs(lam_warm - lam_ref) < 2e-2 * lam_ref
+    lam64 = dev.lambda_max(mat, dinv, iters=60)
+    assert abs(lam64 - lam32) < 0.2 * lam64          # S (x) I is the dominant part of J
+
+
 def _channel_bcs(d):
     import nsb200
     V, P = nsb200.VelocityBCType, nsb200.PressureBCType
