@@ -984,8 +984,8 @@ extern "C" int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M
         }
         NSB_LAUNCH_CHECK(ctx, "k_add");
         NSB_CUDA(ctx, cudaStreamSynchronize(st));   // hs[S_Y..] is reused next cycle
-        // Converged by the Arnoldi residual norm |g_{j+1}|: done, as PETSc's KSPGMRES (the reference's Krylov
-        // library) does -- with CGS-2 the recurrence tracks ||b - A x|| to round-off, and in the flexible variant
+        // Converged by the Arnoldi residual norm |g_{j+1}|: done, as library GMRES implementations (PETSc KSPGMRES)
+        // do; the reference itself solves with sparse LU -- with CGS-2 the recurrence tracks ||b - A x|| to round-off, and in the flexible variant
         // w = A z_j makes it exact by construction.  Only a restart recomputes the true residual.
         if (rnorm <= tol) break;
     }

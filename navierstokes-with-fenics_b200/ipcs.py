@@ -48,7 +48,7 @@ class IPCSSolver(SolverBase):
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard",
                  linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True, device=None,
-                 newton_forcing=0.003, pressure_rhs_projection=10):
+                 newton_forcing=0.003, pressure_rhs_projection=0):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -86,8 +86,11 @@ class IPCSSolver(SolverBase):
         self._newton_forcing, self._newton_rho = float(newton_forcing), None
         # Pressure projection: the same SPD operator every step -> initial guess = energy-norm best approximation of the
         # new solution in the span of the last `pressure_rhs_projection` solutions (Fischer 1998; nsb_rhs_guess /
-        # nsb_rhs_update).  Used for the all-Neumann problem on one GPU and in the replicated solve; 0 = off (then the
-        # guess is the linear extrapolation of the last two pressures).  The CG tolerance is unchanged.
+        # nsb_rhs_update).  For the all-Neumann problem on one GPU and in the replicated solve; 0 = off (default: the
+        # guess is then the linear extrapolation of the last two pressures).  The CG tolerance is unchanged.  Measured
+        # on the C5 start-up transient (profiles/r2_pressure_projection_probe.jsonl): 54 iterations instead of 73 once
+        # ten solutions are in the basis, but 70-79 again after the basis is thinned out -- on average no better than
+        # the extrapolation (72), hence not the default.
         self._p_basis_size, self._p_basis = int(pressure_rhs_projection), None
         self._cache = cache_constant_matrices
         assert momentum_preconditioner in ("jacobi", "chebyshev")

@@ -145,6 +145,27 @@ def test_c3_taylor_green_ipcs_matches_oracle_and_converges(built_library):
     assert e16 < 2e-3 and e8 / e16 > 2.5, (e8, e16)
 
 
+def test_c3_ipcs_temporal_order_dt_sweep(built_library):
+    """the dt sweep of convergence_test/taylor_green_vortex.py: IPCS + BDF-2 on a fixed 16^2 mesh to T = 0.16 with
+    dt = 0.04, 0.02, 0.01 against a dt = 0.0025 run on the same mesh (the spatial error cancels): the velocity error
+    falls with order ~2 (BDF-2 with a BDF-1 start-up step), the pressure error with order >= 1 (incremental pressure
+    correction); errors in the dolfin ``errornorm`` sense are not needed here -- both fields live on the same mesh"""
+    T = 0.16
+    ref, _, _ = _run_tgv(16, 64, T / 64)
+    u_ref, p_ref = ref._velocities[1].cpu().numpy(), ref._old_pressure.cpu().numpy()
+    p_ref = p_ref - p_ref.mean()
+    eu, ep = [], []
+    for nsteps in (4, 8, 16):
+        s, _, _ = _run_tgv(16, nsteps, T / nsteps)
+        u, p = s._velocities[1].cpu().numpy(), s._old_pressure.cpu().numpy()
+        eu.append(np.linalg.norm(u - u_ref) / np.linalg.norm(u_ref))
+        ep.append(np.linalg.norm((p - p.mean()) - p_ref) / np.linalg.norm(p_ref))
+    orders_u = [np.log2(eu[i] / eu[i + 1]) for i in range(2)]
+    orders_p = [np.log2(ep[i] / ep[i + 1]) for i in range(2)]
+    assert eu[-1] < eu[0] and min(orders_u) > 1.6 and max(orders_u) < 2.6, (eu, orders_u)
+    assert min(orders_p) > 0.9, (ep, orders_p)
+
+
 @pytest.mark.parametrize("linear_solver", ["direct", "gmres"])
 def test_c4_dfg_cylinder_drag_lift(built_library, linear_solver):
     """configs[3]: DFG 2D-2 (Re = 100, BDF-2, dt = 0.005, inlet 6 y/h (1 - y/h), demo/dfg_benchmark.py) on the
@@ -194,3 +215,29 @@ def test_c4_dfg_cylinder_drag_lift(built_library, linear_solver):
     assert abs(cd - 2.0 * Fo[0]) <= 1e-8 * abs(2.0 * Fo[0])
     assert abs(cl - 2.0 * Fo[1]) <= 1e-8 * max(abs(2.0 * Fo[1]), abs(2.0 * Fo[0]) * 1e-3)
     assert cd > 0.0
+
+
+def test_dfg_2d1_steady_drag_in_the_published_range(built_library):
+    """An EXTERNAL known answer (not the builder's oracle): the steady DFG 2D-1 benchmark (Schaefer & Turek 1996, Re = 20,
+    same geometry scaled by 10 as gmsh-collection/meshes/DFGBenchmark.geo) has c_D = 5.5795, c_L = 0.0106.  Stationary
+    Picard -> Newton solver on the synthetic cylinder mesh (14 235 DOF): the drag from the PHYSICAL traction (twice the
+    viscous part of the reference's functional, see ``boundary_force``) lies within 1.5 % of the published value, the
+    lift has the right sign and size; the reference's own functional gives the smaller 4.59 on the same field."""
+    import nsb200
+    V = nsb200.VelocityBCType
+    Re, h = 20.0, 4.1
+    mesh, markers, ids = nsb200.channel_with_cylinder(16)
+
+    def inlet(x, t=0.0):
+        return np.stack([6.0 * x[:, 1] / h * (1.0 - x[:, 1] / h), 0.0 * x[:, 0]], axis=1)
+    solver = nsb200.StationarySolver(mesh, markers, "standard")
+    solver.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=1.0 / Re))
+    solver.set_boundary_conditions([(V.function, ids["inlet"], inlet), (V.no_slip, ids["cylinder"], None),
+                                    (V.no_slip, ids["upper wall"], None), (V.no_slip, ids["lower wall"], None)])
+    assert solver.solve() <= 1e-10
+    F_phys = solver.boundary_force(solver.solution, ids["cylinder"], viscous_factor=2.0)
+    F_ref = solver.boundary_force(solver.solution, ids["cylinder"])
+    cd, cl = 2.0 * F_phys[0], 2.0 * F_phys[1]
+    assert abs(cd - 5.5795) < 0.015 * 5.5795, cd
+    assert 0.005 < cl < 0.02, cl
+    assert abs(2.0 * F_ref[0] - 4.587) < 0.02          # what demo/dfg_benchmark.py's functional reports for this flow

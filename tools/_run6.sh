@@ -1,6 +1,6 @@
 set -u
-python -m pytest tests -m gpu -q -x --timeout 1500 > gpurun_out/t6.log 2>&1; echo "tests rc=$?"; tail -3 gpurun_out/t6.log
-for proj in 0 6 10 16; do
+python -m pytest tests/test_gpu_solvers.py -m gpu -q -x --timeout 1500 > gpurun_out/t6.log 2>&1; echo "tests rc=$?"; tail -3 gpurun_out/t6.log
+for proj in 8 10 16; do
 python - <<PY
 import sys, json, time, torch
 sys.path.insert(0,'.')
