@@ -313,6 +313,13 @@ int nsb_gmres(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const dou
  * three iterations then track the slowly moving spectrum. */
 int nsb_lambda_max(nsb_ctx* ctx, const nsb_matrix* A, const double* inv_diag, int32_t iters, int32_t warm_start,
                    double* work, double* lambda_out_host, void* stream);
+/* DG post-processing fields of source/ns_problem.py:55-102.  dolfin.project(curl(u), DG_1) and
+ * dolfin.project(grad(p), [DG_0]^d) are cell-wise L2 projections of a field that already lies in the target space
+ * (curl of P2 is P1 per cell, gradient of P1 is constant per cell): the dofs are its vertex values / its value.
+ * nsb_cell_vorticity: out[cell][local vertex][nc], nc = 1 (2D, d_x u_y - d_y u_x) or 3; nsb_cell_pressure_gradient:
+ * out[cell][d].  u in V numbering (interleaved), p in Q numbering. */
+int nsb_cell_vorticity(nsb_ctx* ctx, const double* u_dev, double* out_dev, void* stream);
+int nsb_cell_pressure_gradient(nsb_ctx* ctx, const double* p_dev, double* out_dev, void* stream);
 /* Successive right-hand sides (Fischer 1998) for a solve that is repeated with the same SPD operator every time
  * step -- the pressure projection, source/ns_ipcs_solver.py:149-171, 205.  X / AX: caller-owned lmax x n arrays
  * (lmax <= 16) holding an A-orthonormal basis of the previous solutions and its image; l = the number of vectors in

@@ -90,6 +90,8 @@ PROTOTYPES = {
     "nsb_cg_workspace_doubles": (C.c_int64, [C.c_int64]),
     "nsb_gmres_workspace_doubles": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "nsb_lambda_max": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),
+    "nsb_cell_vorticity": (C.c_int, [vp, vp, vp, vp]),
+    "nsb_cell_pressure_gradient": (C.c_int, [vp, vp, vp, vp]),
     "nsb_rhs_guess": (C.c_int, [vp, C.c_int64, C.c_int32, vp, vp, vp, vp]),
     "nsb_rhs_update": (C.c_int, [vp, C.POINTER(Matrix), C.POINTER(C.c_int32), C.c_int32, vp, vp, vp, vp, vp]),
     "nsb_lambda_max32": (C.c_int, [vp, C.POINTER(Matrix), vp, C.c_int32, C.c_int32, vp, c_f64p, vp]),

@@ -9,7 +9,12 @@
 //     k |u| dt / h_T (quadrature degree 2k), then the max-norm of the dof vector.  Per cell that projection
 //     is ONE fixed matrix (nodes x quadrature points) applied to the integrand's point values.
 //   * x -= s (mean-pressure shift, source/ns_solver_base.py:1190-1203).
+//   * the DG post-processing fields of source/ns_problem.py:55-102: dolfin.project(curl(u), DG_1) and
+//     dolfin.project(grad(p), [DG_0]^d).  The curl of a P2 field is linear and the gradient of a P1 field is
+//     constant on every cell, so the cell-wise L2 projection reproduces them: the DG dofs are the vertex values
+//     of curl(u_h) / the constant grad(p_h), in closed form from the vertex gradients of the P2 basis.
 #include "common.cuh"
+#include "tables.h"
 #include "fe_geometry.cuh"
 
 #define GRID_STRIDE(i, n) \
@@ -254,6 +259,121 @@ extern "C" int nsb_cfl_max(nsb_ctx* ctx, const double* u, double scale, int32_t 
         for (int r = 0; r < ctx->nranks; ++r) m = fmax(m, ctx->h_scalars[64 + r]);
         *out_host = m;
     }
+    return 0;
+}
+
+// ---- DG post-processing fields --------------------------------------------------------------------------
+namespace {
+template <int D> struct PT;
+template <> struct PT<2> {
+    static constexpr int NL = 6, NC = 1;
+    __device__ static __forceinline__ double DV(int j, int m, int k) { return DV_2D[j][m][k]; }
+};
+template <> struct PT<3> {
+    static constexpr int NL = 10, NC = 3;
+    __device__ static __forceinline__ double DV(int j, int m, int k) { return DV_3D[j][m][k]; }
+};
+
+// out[cell][M][c]: curl(u_h) at the cell's vertex M (2D: the scalar d_x u_y - d_y u_x)
+template <int D>
+__global__ void __launch_bounds__(128)
+k_cell_vorticity(int32_t ncells, const double* __restrict__ coords, const int32_t* __restrict__ cell_verts,
+                 const int32_t* __restrict__ cell_nodes, const double* __restrict__ u, double* __restrict__ out) {
+    using T = PT<D>;
+    constexpr int NL = T::NL, NC = T::NC;
+    GRID_STRIDE(c, ncells) {
+        int32_t vtx[D + 1];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[c * (D + 1) + M];
+        Geo<D> g;
+        cell_geometry(coords, vtx, g);
+        double U[NL][D];
+#pragma unroll
+        for (int L = 0; L < NL; ++L)
+#pragma unroll
+            for (int i = 0; i < D; ++i) U[L][i] = u[(int64_t)D * cell_nodes[c * NL + L] + i];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) {
+            double ref[D][D], gr[D][D];      // gr[b][j] = d_j u_b (x_M)
+#pragma unroll
+            for (int b = 0; b < D; ++b)
+#pragma unroll
+                for (int k = 0; k < D; ++k) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int L = 0; L < NL; ++L) s += U[L][b] * T::DV(L, M, k);
+                    ref[b][k] = s;
+                }
+#pragma unroll
+            for (int b = 0; b < D; ++b)
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int k = 0; k < D; ++k) s += ref[b][k] * g.K[k][j];
+                    gr[b][j] = s;
+                }
+            double* o = out + ((int64_t)c * (D + 1) + M) * NC;
+            if (D == 2) {
+                o[0] = gr[1][0] - gr[0][1];
+            } else {
+                o[0] = gr[2 % D][1] - gr[1][2 % D];
+                o[1 % NC] = gr[0][2 % D] - gr[2 % D][0];
+                o[2 % NC] = gr[1][0] - gr[0][1];
+            }
+        }
+    }
+}
+
+// out[cell][j] = d_j p_h on the cell (P1: constant)
+template <int D>
+__global__ void __launch_bounds__(128)
+k_cell_pressure_gradient(int32_t ncells, const double* __restrict__ coords, const int32_t* __restrict__ cell_verts,
+                         const double* __restrict__ p, double* __restrict__ out) {
+    GRID_STRIDE(c, ncells) {
+        int32_t vtx[D + 1];
+#pragma unroll
+        for (int M = 0; M <= D; ++M) vtx[M] = cell_verts[c * (D + 1) + M];
+        Geo<D> g;
+        cell_geometry(coords, vtx, g);
+        const double p0 = p[vtx[0]];
+        double dp[D];
+#pragma unroll
+        for (int k = 0; k < D; ++k) dp[k] = p[vtx[k + 1]] - p0;     // reference gradient: lambda_k = xi_k, lambda_0 = 1 - sum
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < D; ++k) s += dp[k] * g.K[k][j];
+            out[(int64_t)c * D + j] = s;
+        }
+    }
+}
+}  // namespace
+
+extern "C" int nsb_cell_vorticity(nsb_ctx* ctx, const double* u, double* out, void* stream) {
+    NSB_REQUIRE(ctx, ctx && u && out, "bad arguments");
+    NSB_REQUIRE(ctx, ctx->ncells > 0 && ctx->cell_nodes, "set the mesh first");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int G = nsb_blocks(ctx->ncells, 128);
+    NSB_TIMED(ctx, NSB_T_VEC, st);
+    if (ctx->dim == 2) k_cell_vorticity<2><<<G, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_verts, ctx->cell_nodes, u, out);
+    else k_cell_vorticity<3><<<G, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_verts, ctx->cell_nodes, u, out);
+    NSB_LAUNCH_CHECK(ctx, "k_cell_vorticity");
+    NSB_COUNT(ctx, 1);
+    return 0;
+}
+
+extern "C" int nsb_cell_pressure_gradient(nsb_ctx* ctx, const double* p, double* out, void* stream) {
+    NSB_REQUIRE(ctx, ctx && p && out, "bad arguments");
+    NSB_REQUIRE(ctx, ctx->ncells > 0, "set the mesh first");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int G = nsb_blocks(ctx->ncells, 128);
+    NSB_TIMED(ctx, NSB_T_VEC, st);
+    if (ctx->dim == 2) k_cell_pressure_gradient<2><<<G, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_verts, p, out);
+    else k_cell_pressure_gradient<3><<<G, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_verts, p, out);
+    NSB_LAUNCH_CHECK(ctx, "k_cell_pressure_gradient");
+    NSB_COUNT(ctx, 1);
     return 0;
 }
 

@@ -431,6 +431,20 @@ class Device:
                       self.stream))
         return out.value
 
+    def vorticity(self, u):
+        """``dolfin.project(curl(u), DG_1)`` (source/ns_problem.py:55-81): [ncells, d + 1] in 2D, [ncells, 4, 3] in 3D --
+        the DG-1 dofs of a cell are its vertex values, in the cell's local vertex order"""
+        d, nc = self.dim, self.mesh.num_cells
+        out = self.empty(nc * (d + 1) * (1 if d == 2 else 3))
+        self.check(self.lib.nsb_cell_vorticity(self.ctx, _ptr(u), _ptr(out), self.stream))
+        return out.view(nc, d + 1) if d == 2 else out.view(nc, d + 1, 3)
+
+    def pressure_gradient(self, p):
+        """``dolfin.project(grad(p), [DG_0]^d)`` (source/ns_problem.py:83-101): [ncells, d]"""
+        out = self.empty(self.mesh.num_cells * self.dim)
+        self.check(self.lib.nsb_cell_pressure_gradient(self.ctx, _ptr(p), _ptr(out), self.stream))
+        return out.view(self.mesh.num_cells, self.dim)
+
     def rhs_basis(self, n, lmax=10):
         """state of the successive-right-hand-side projection (nsb_rhs_guess / nsb_rhs_update) for a system of size n"""
         return dict(n=n, lmax=lmax, l=C.c_int32(0), X=self.empty(lmax * n), AX=self.empty(lmax * n), work=self.empty(2 * n))

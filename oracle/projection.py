@@ -5,6 +5,8 @@
 * ``mean_pressure_shift``       source/ns_solver_base.py:1190-1203
 * ``errornorm``                 convergence_test/taylor_green_vortex.py:101-119 (dolfin default degree_rise = 3)
 * ``cfl_number``                source/ns_problem.py:554-587: DG-k LocalSolver projection of k |u| dt / h, linf of the dofs
+* ``vorticity_dg`` / ``pressure_gradient_dg``   source/ns_problem.py:55-101: dolfin.project onto DG_1 / [DG_0]^d, done
+  here as a genuine cell-wise L2 projection by quadrature (the device code uses that it is the identity)
 
 Written independently of navierstokes-with-fenics_b200/lagrange.py: Lagrange bases here come from inverting the
 monomial Vandermonde matrix at an equispaced lattice, integrals from the Gauss-Jacobi rules of oracle/fem.py, the
@@ -193,4 +195,48 @@ def cfl_number(asm, u, step_size, degree=2):
     return best
 
 
-__all__ = ["project", "mean_pressure_shift", "errornorm", "cfl_number", "LagrangeElement", "sp"]
+def _dg_project(asm, fq, qp, qw, degree):
+    """cell-wise L2 projection onto DG-`degree` (dolfin.project onto a discontinuous space is block diagonal): fq
+    [nc, nq, ncomp] are the integrand's values at the quadrature points; returns the dofs [nc, ndof, ncomp], dofs =
+    the Lagrange nodes of the cell (vertices for degree 1, the single constant for degree 0)"""
+    d = asm.sp.mesh.dim
+    assert degree in (0, 1)
+    psi = np.ones((len(qw), 1)) if degree == 0 else fem.tabulate_p1(qp)[0]     # DG-1 dofs in the cell's vertex order
+    Mloc = psi.T @ (qw[:, None] * psi)
+    rhs = np.einsum("q,qI,cqk->cIk", qw, psi, fq)               # detJ cancels between the two sides
+    return np.linalg.solve(Mloc[None, :, :], rhs)
+
+
+def vorticity_dg(asm, u):
+    """``_compute_vorticity`` source/ns_problem.py:55-81: dolfin.project(curl(u), DG_1) -> [nc, d+1] (2D) / [nc, 4, 3]"""
+    s, m = asm.sp, asm.sp.mesh
+    d = m.dim
+    qp, qw = fem.simplex_quadrature(d, 4)
+    dphi = fem.tabulate_p2(qp)[1]                                # [nq, nl, d] reference gradients
+    K, _ = fem.geometry(m.coords, m.cells)
+    Uc = u.reshape(-1, d)[s.cell_nodes]                          # [nc, nl, d]
+    # grad[c, q, b, j] = d_j u_b = sum_L U_Lb sum_k dphi[q, L, k] K[c, k, j]
+    grad = np.einsum("cLb,qLk,ckj->cqbj", Uc, dphi, K)
+    if d == 2:
+        curl = (grad[:, :, 1, 0] - grad[:, :, 0, 1])[:, :, None]
+    else:
+        curl = np.stack([grad[:, :, 2, 1] - grad[:, :, 1, 2], grad[:, :, 0, 2] - grad[:, :, 2, 0],
+                         grad[:, :, 1, 0] - grad[:, :, 0, 1]], axis=2)
+    out = _dg_project(asm, curl, qp, qw, 1)
+    return out[:, :, 0] if d == 2 else out
+
+
+def pressure_gradient_dg(asm, p):
+    """``_compute_pressure_gradient`` source/ns_problem.py:83-101: dolfin.project(grad(p), [DG_0]^d) -> [nc, d]"""
+    s, m = asm.sp, asm.sp.mesh
+    d = m.dim
+    qp, qw = fem.simplex_quadrature(d, 2)
+    dphi = fem.tabulate_p1(qp)[1]
+    K, _ = fem.geometry(m.coords, m.cells)
+    Pc = p[s.cell_dofs_Q]
+    grad = np.einsum("cL,qLk,ckj->cqj", Pc, dphi, K)
+    return _dg_project(asm, grad, qp, qw, 0)[:, 0, :]
+
+
+__all__ = ["project", "mean_pressure_shift", "errornorm", "cfl_number", "vorticity_dg", "pressure_gradient_dg",
+           "LagrangeElement", "sp"]

@@ -1,7 +1,7 @@
 """SURVEY.md 8f rows 1-3 on the device against their oracle restatements (oracle/projection.py): dolfin.project
 of degree-k Expressions (initial conditions, source/ns_solver_base.py:1123-1171), the mean-pressure shift
-(:1190-1203), dolfin.errornorm (convergence_test/taylor_green_vortex.py:101-119) and the CFL diagnostic
-(source/ns_problem.py:554-587)."""
+(:1190-1203), dolfin.errornorm (convergence_test/taylor_green_vortex.py:101-119), the CFL diagnostic
+(source/ns_problem.py:554-587) and the DG post-processing fields (vorticity, pressure gradient, :55-101)."""
 import numpy as np
 import pytest
 
@@ -58,6 +58,19 @@ def test_errornorm_and_cfl_match_oracle(case):
         got = dev.cfl(dev.upload(us), dt)
         ref = opj.cfl_number(asm, us, dt)
         assert abs(got - ref) < 1e-12 * ref
+
+
+def test_dg_postprocessing_fields_match_oracle(case):
+    """vorticity and pressure gradient of source/ns_problem.py:55-101 (dolfin.project onto DG_1 / [DG_0]^d): the device
+    evaluates them in closed form per cell, the oracle by a genuine cell-wise L2 projection with quadrature"""
+    from oracle import projection as opj
+    dev, asm, d = case["dev"], case["asm"], case["d"]
+    us, _, _, p = random_fields(dev.spaces)
+    w = dev.vorticity(dev.upload(us)).cpu().numpy()
+    assert w.shape == ((asm.sp.mesh.num_cells, d + 1) if d == 2 else (asm.sp.mesh.num_cells, d + 1, 3))
+    assert rel_max_err(w, opj.vorticity_dg(asm, us)) < 1e-12
+    g = dev.pressure_gradient(dev.upload(p)).cpu().numpy()
+    assert rel_max_err(g, opj.pressure_gradient_dg(asm, p)) < 1e-12
 
 
 def test_initial_conditions_are_projected(built_library):

@@ -242,3 +242,25 @@ def test_lagrange_tables_of_the_product_against_oracle_elements():
         # degree-4 exactness of the FIAT default rule: x0^2 x1^2
         ex = np.einsum("q,q->", W, X[:, 0] ** 2 * X[:, 1] ** 2)
         assert abs(np.einsum("q,q->", Wf, Xf[:, 0] ** 2 * Xf[:, 1] ** 2) - ex) < 1e-12
+
+
+def test_dg_postprocessing_known_answers():
+    """oracle/projection.py vorticity_dg / pressure_gradient_dg (source/ns_problem.py:55-101) on fields whose curl /
+    gradient is known in closed form: quadratic velocities (curl linear: reproduced exactly by DG_1), linear pressure"""
+    import oracle
+    from oracle import projection as P
+    for dim, n in ((2, (3, 2)), (3, (2, 2, 2))):
+        om = oracle.mesh.hyper_rectangle((0.0,) * dim, (1.5, 1.0, 0.5)[:dim], n)
+        asm = oracle.forms.Assembler(oracle.dofmap.Spaces(om))
+        x = asm.sp.node_coords()
+        X = om.coords[om.cells]
+        if dim == 2:
+            u = np.stack([x[:, 1] ** 2, x[:, 0] * x[:, 1]], axis=1).reshape(-1)
+            ref = -X[:, :, 1]                                                   # d_x (x y) - d_y (y^2)
+        else:
+            u = np.stack([x[:, 1] ** 2, x[:, 0] * x[:, 2], x[:, 0] * x[:, 1]], axis=1).reshape(-1)
+            ref = np.stack([0.0 * X[:, :, 0], -X[:, :, 1], X[:, :, 2] - 2.0 * X[:, :, 1]], axis=2)
+        assert np.abs(P.vorticity_dg(asm, u) - ref).max() < 1e-13
+        p = 2.0 * x[:asm.sp.N0, 0] - 3.0 * x[:asm.sp.N0, 1]
+        g = P.pressure_gradient_dg(asm, p)
+        assert np.abs(g[:, 0] - 2.0).max() < 1e-13 and np.abs(g[:, 1] + 3.0).max() < 1e-13
