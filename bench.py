@@ -145,7 +145,7 @@ def workload_config(n, gpus):
                            "[NCCL with NSB_HALO=nccl]); roofline and breakdown are rank 0's share" % gpus,
             "l2_policy": "inputs larger than L2 (Jacobian 6.5 GB, Krylov basis 3.3 GB per GPU at n=73)",
             "linear_solvers": "FP64 flexible GMRES(40), every Newton update to 1e-12 of the step's first residual except the "
-                              "first update of a step (forcing term 0.003 x the Newton contraction observed at the previous "
+                              "first update of a step (forcing term 0.001 x the Newton contraction observed at the previous "
                               "step, only when a second update is certain to follow: same Newton counts, same fields), "
                               "right-preconditioned by a degree-10 Chebyshev polynomial "
                               "in D^-1 J that runs in single precision on the block-scalar part of J (mean block diagonals as "

@@ -455,6 +455,13 @@ int nsb_allreduce(nsb_ctx* ctx, double* buf_dev, int64_t count, void* stream);
  * nsb_comm_finalize unmaps and frees the blocks (call it after a host barrier). */
 /* out[k] = (float) mean of the diagonal of block k of a BSR value array (nsb_matrix.diag32) */
 int nsb_bsr_block_scalar_f32(nsb_ctx* ctx, int64_t nnz, int32_t bs, const double* vals_dev, float* out_dev, void* stream);
+/* The same fused into the assembly: while out_dev is registered (NULL unregisters), nsb_assemble_ipcs_momentum(NSB_MAT)
+ * writes the block-scalar copy of the Jacobian it assembles alongside A_out (in the row-group kernel, from shared
+ * memory: the 6.5 GB re-read at C5 goes away).  nnz_blocks = entries of the P2 x P2 pattern.  After
+ * nsb_bc_apply_matrix changed Dirichlet rows, nsb_bsr_block_scalar_rows_f32 refreshes the listed block rows only. */
+int nsb_set_block_scalar_out(nsb_ctx* ctx, float* out_dev, int64_t nnz_blocks);
+int nsb_bsr_block_scalar_rows_f32(nsb_ctx* ctx, int32_t nlisted, const int32_t* block_rows_dev, const int32_t* rowptr_dev,
+                                  int32_t bs, const double* vals_dev, float* out_dev, void* stream);
 
 int nsb_p2p_export(nsb_ctx* ctx, int32_t which, uint8_t* handle_out64);
 int nsb_p2p_connect(nsb_ctx* ctx, int32_t which, int32_t npeers, const uint8_t* handles64,

@@ -122,6 +122,8 @@ PROTOTYPES = {
     "nsb_comm_finalize": (C.c_int, [vp]),
     "nsb_set_halo": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, vp, vp, vp, vp, vp, vp]),
     "nsb_bsr_block_scalar_f32": (C.c_int, [vp, C.c_int64, C.c_int32, vp, vp, vp]),
+    "nsb_set_block_scalar_out": (C.c_int, [vp, vp, C.c_int64]),
+    "nsb_bsr_block_scalar_rows_f32": (C.c_int, [vp, C.c_int32, vp, vp, C.c_int32, vp, vp, vp]),
     "nsb_p2p_export": (C.c_int, [vp, C.c_int32, vp]),
     "nsb_p2p_connect": (C.c_int, [vp, C.c_int32, C.c_int32, vp, vp, vp, vp]),
     "nsb_p2p_status": (C.c_int, [vp, c_i32p]),

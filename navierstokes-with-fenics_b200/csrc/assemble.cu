@@ -522,7 +522,7 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
         const int newton = (flags & NSB_PICARD) ? 0 : 1;
         const double mc = cf.a0 / cf.k;
         NSB_TIMED(ctx, NSB_T_ASM_JAC, st);
-        const int rg = tuned ? nsb_launch_jacobian_rowgroups(ctx, ustar, mc, newton, A_out, st) : 1;
+        const int rg = tuned ? nsb_launch_jacobian_rowgroups(ctx, ustar, mc, newton, A_out, ctx->jac_block_scalar_out, st) : 1;
         if (rg < 0) return -1;
         if (rg == 0) return 0;
         NSB_DIM_DISPATCH(ctx,
@@ -533,6 +533,10 @@ extern "C" int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const dou
                                                      P.pair_slots, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mc,
                                                      cf, fm, newton, A_out)));
         NSB_LAUNCH_CHECK(ctx, "k_momentum_jacobian");
+        // the generic kernels do not carry the fused block-scalar output: same contract through the stand-alone kernel
+        if (ctx->jac_block_scalar_out &&
+            nsb_bsr_block_scalar_f32(ctx, ctx->jac_block_scalar_nnz, ctx->dim, A_out, ctx->jac_block_scalar_out, stream))
+            return -1;
     }
     return 0;
 }

@@ -75,7 +75,7 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
                      const int32_t* __restrict__ pair_cell, const uint8_t* __restrict__ pair_iloc,
                      const double* __restrict__ coords, const int32_t* __restrict__ cell_nodes,
                      const int32_t* __restrict__ cell_verts, const double* __restrict__ ustar, double mass_coef, double c_conv, double c_visc, int newton,
-                     double* __restrict__ vals) {
+                     double* __restrict__ vals, float* __restrict__ scal32) {
     using C = JacCfg<D>;
     using TB = CT<D>;
     constexpr int NL = C::NL, NV = C::NV, DD = C::DD, NS = C::NS, SSTR = C::SSTR;
@@ -253,6 +253,15 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
         // the group's rows: one contiguous range of the value array, written once, coalesced
         double* out = vals + (int64_t)e_lo * DD;
         for (int e = lane; e < nval; e += 32) out[e] = rowbuf[e];
+        // block-scalar copy for the single-precision preconditioner (nsb_matrix.diag32), while the blocks are still
+        // in shared memory: saves the 6.5 GB re-read of nsb_bsr_block_scalar_f32
+        if (scal32 != nullptr)
+            for (int e = lane; e < nval / DD; e += 32) {
+                double sd = 0.0;
+#pragma unroll
+                for (int i = 0; i < D; ++i) sd += rowbuf[e * DD + i * (D + 1)];
+                scal32[e_lo + e] = (float)(sd / D);
+            }
         __syncwarp();
     }
 }
@@ -261,7 +270,7 @@ k_jacobian_rowgroups(int32_t ngroups, const int32_t* __restrict__ group_row, con
 // caller keeps the generic one-thread-per-row kernel.
 template <int D>
 static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double* ustar, double mass_coef,
-                            int newton, double* A_out, cudaStream_t st) {
+                            int newton, double* A_out, float* S32_out, cudaStream_t st) {
     using C = JacCfg<D>;
     if (!P.group_row || !P.chunk_first || !P.round_ptr || !P.sched || !P.fold_ptr || P.ngroups <= 0 || P.group_max_entries > C::MAXB)
         return 1;
@@ -279,15 +288,15 @@ static int launch_rowgroups(nsb_ctx* ctx, const nsb_pattern_dev& P, const double
     if (blocks > need) blocks = need;
     k_jacobian_rowgroups<D><<<(int)blocks, C::WARPS * 32, C::SMEM, st>>>(
         P.ngroups, P.group_row, P.chunk_first, P.round_ptr, P.sched, P.fold_ptr, P.fold, P.rowptr, P.pair_ptr, P.pair_cell, P.pair_iloc,
-        ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out);
+        ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, mass_coef, ctx->coef.c_conv, ctx->coef.c_visc, newton, A_out, S32_out);
     NSB_LAUNCH_CHECK(ctx, "k_jacobian_rowgroups");
     return 0;
 }
 
 int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass_coef, int newton, double* A_out,
-                                  cudaStream_t st) {
+                                  float* S32_out, cudaStream_t st) {
     const nsb_pattern_dev& P = ctx->pat[NSB_PAT_P2P2];
-    if (ctx->dim == 2) return launch_rowgroups<2>(ctx, P, ustar, mass_coef, newton, A_out, st);
-    if (ctx->dim == 3) return launch_rowgroups<3>(ctx, P, ustar, mass_coef, newton, A_out, st);
+    if (ctx->dim == 2) return launch_rowgroups<2>(ctx, P, ustar, mass_coef, newton, A_out, S32_out, st);
+    if (ctx->dim == 3) return launch_rowgroups<3>(ctx, P, ustar, mass_coef, newton, A_out, S32_out, st);
     return 1;
 }

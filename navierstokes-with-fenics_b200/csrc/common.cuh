@@ -164,6 +164,8 @@ struct nsb_ctx {
     int32_t form_conv = 0, form_visc = 0;
     double coriolis[3] = {0.0, 0.0, 0.0};
     bool force_generic_assembly = false;
+    float* jac_block_scalar_out = nullptr;   // nsb_set_block_scalar_out: diag32 written alongside the momentum Jacobian
+    int64_t jac_block_scalar_nnz = 0;
     // reduction scratch (device) + pinned host mirror
     double* d_partials = nullptr;     // [NSB_MAX_PARTIALS * 8]
     double* d_scalars = nullptr;      // [64] device-resident Krylov scalars
@@ -197,7 +199,7 @@ int nsb_comm_destroy(nsb_ctx* ctx);
 // assemble_jac.cu: 0 = launched, 1 = not applicable (caller falls back), -1 = error
 int nsb_launch_residual_cells(nsb_ctx* ctx, const double* ustar, const double* un, const double* unm1,
                               const double* pn, double* b_out, cudaStream_t st);   // assemble_res.cu
-int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass_coef, int newton, double* A_out,
+int nsb_launch_jacobian_rowgroups(nsb_ctx* ctx, const double* ustar, double mass_coef, int newton, double* A_out, float* S32_out,
                                   cudaStream_t st);   // context.cu: fold finished event pairs into timers[].ms
 
 // RAII region: records a start/stop event pair on `st` around the launches of one kernel class

@@ -213,6 +213,42 @@ static int launch_spmv_kron32(nsb_ctx* ctx, const nsb_matrix* A, const float* x,
     return 0;
 }
 
+// out[k] = mean of the diagonal of block k, for the blocks of the listed block rows only (after nsb_bc_apply_matrix
+// changed those rows)
+__global__ void __launch_bounds__(256)
+k_block_scalar_rows(int32_t nlisted, const int32_t* __restrict__ rows, const int32_t* __restrict__ rowptr, int bs,
+                    const double* __restrict__ vals, float* __restrict__ out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = t >> 3;                              // 8 lanes per listed row
+    if (r >= nlisted) return;
+    const int32_t row = rows[r];
+    for (int32_t k = rowptr[row] + (int)(t & 7); k < rowptr[row + 1]; k += 8) {
+        const double* b = vals + (int64_t)k * bs * bs;
+        double sdiag = 0.0;
+        for (int i = 0; i < bs; ++i) sdiag += b[i * (bs + 1)];
+        out[k] = (float)(sdiag / bs);
+    }
+}
+extern "C" int nsb_bsr_block_scalar_rows_f32(nsb_ctx* ctx, int32_t nlisted, const int32_t* block_rows, const int32_t* rowptr,
+                                             int32_t bs, const double* vals, float* out, void* stream) {
+    NSB_REQUIRE(ctx, ctx && nlisted >= 0 && bs >= 1 && bs <= 3 && (nlisted == 0 || (block_rows && rowptr && vals && out)),
+                "bad arguments");
+    if (nlisted == 0) return 0;
+    nsb_timed_region region(ctx, NSB_T_VEC, (cudaStream_t)stream);
+    k_block_scalar_rows<<<nsb_blocks((int64_t)nlisted * 8, 256), 256, 0, (cudaStream_t)stream>>>(nlisted, block_rows, rowptr, bs, vals, out);
+    NSB_LAUNCH_CHECK(ctx, "k_block_scalar_rows");
+    NSB_COUNT(ctx, 1);
+    return 0;
+}
+
+extern "C" int nsb_set_block_scalar_out(nsb_ctx* ctx, float* out, int64_t nnz_blocks) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, out == nullptr || nnz_blocks > 0, "the block count of the P2 x P2 pattern is needed");
+    ctx->jac_block_scalar_out = out;
+    ctx->jac_block_scalar_nnz = out ? nnz_blocks : 0;
+    return 0;
+}
+
 // out[k] = mean of the diagonal of block k
 __global__ void __launch_bounds__(256)
 k_block_scalar(int64_t nnz, int bs, const double* __restrict__ vals, float* __restrict__ out) {

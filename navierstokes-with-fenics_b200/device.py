@@ -643,6 +643,17 @@ class Device:
             self._volume = self.sum(self._p1_weights)
         return self.dot(self._p1_weights, p[:n_own]), self._volume
 
+    def set_block_scalar_out(self, out):
+        """register (None: unregister) the float tensor the momentum-Jacobian assembly fills with the block-scalar copy"""
+        self._block_scalar_out = out
+        self.check(self.lib.nsb_set_block_scalar_out(self.ctx, _ptr(out), 0 if out is None else out.numel()))
+
+    def block_scalar_rows_f32(self, vals, bs, block_rows, out):
+        """refresh the block-scalar copy on the listed block rows (after bc_apply_matrix)"""
+        pat = self.patterns["P2P2"]
+        self.check(self.lib.nsb_bsr_block_scalar_rows_f32(self.ctx, block_rows.numel(), _ptr(block_rows), _ptr(pat.rowptr), bs,
+                                                          _ptr(vals), _ptr(out), self.stream))
+
     def block_scalar_f32(self, vals, bs, out):
         """out[k] = float(mean of the diagonal of the bs x bs block k of ``vals``)"""
         self.check(self.lib.nsb_bsr_block_scalar_f32(self.ctx, out.numel(), bs, _ptr(vals), _ptr(out), self.stream))

@@ -48,7 +48,7 @@ class IPCSSolver(SolverBase):
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard",
                  linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True, device=None,
-                 newton_forcing=0.003, pressure_rhs_projection=0):
+                 newton_forcing=0.001, pressure_rhs_projection=0):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -77,7 +77,7 @@ class IPCSSolver(SolverBase):
         self._linear_atol_factor = linear_atol_factor
         # Forcing term of the FIRST Newton update of a step (inexact Newton, Eisenstat-Walker): Newton contracts the
         # residual by rho = r1 / r0 per step (observed at the previous time step, 1e-4 .. 1e-6 here), so a linear
-        # residual of newton_forcing * rho * r0 perturbs r1 by at most newton_forcing (0.3 %; measured 0.1 %) -- the iteration counts and
+        # residual of newton_forcing * rho * r0 perturbs r1 by at most newton_forcing (0.1 %) -- the iteration counts and
         # the converged u* (whose accuracy is set by the LAST update, solved to linear_rtol * r0 as before) do not
         # change (tools/probe_newton.py, C5 and 16^3: identical counts over 14 steps, fields equal to 7e-13), the first
         # GMRES solve needs 4-5 iterations instead of 10.  Used only when the predicted r1 = rho * r0 is
@@ -178,6 +178,7 @@ class IPCSSolver(SolverBase):
         vd, vv, pd, pv = vd[self._vbc_keep], vv[self._vbc_keep], pd[self._pbc_keep], pv[self._pbc_keep]
         assert dev.partition is not None or len(vd) + len(pd) > 0
         self._vbc_dofs, self._vbc_vals = dev.upload(vd), dev.upload(vv)
+        self._vbc_nodes = dev.upload(np.unique(np.asarray(vd) // dev.dim).astype(np.int32))     # block rows with a Dirichlet dof
         self._pbc_dofs, self._pbc_vals = dev.upload(pd), dev.upload(pv)
         # Dirichlet or all-Neumann pressure problem: one decision for all ranks
         self._pressure_dirichlet = len(pd) > 0
@@ -360,13 +361,17 @@ class IPCSSolver(SolverBase):
         self.newton_residuals = [r0]           # residual norms of this step's Newton iteration (diagnostic)
         converged = newton_converged(r, r0, atol, rtol)
         while not converged and it < self._maxiter:
+            # the block-scalar f32 copy of the preconditioner is written by the assembly kernel itself (registered only
+            # for the duration of the call: the Device may be shared), then refreshed on the Dirichlet block rows
+            dev.set_block_scalar_out(self._S_mom32)
             dev.assemble_ipcs_momentum(L.MAT, ustar, A=self._A_mom)
+            dev.set_block_scalar_out(None)
             dev.bc_apply_matrix("P2P2", self._A_mom, L.BSR, d, self._vbc_dofs)
             dev.inv_diagonal(self._jac, self._dinvV)
             if self._A_mom32 is not None:
                 dev.to_f32(self._A_mom, self._A_mom32)
             if self._S_mom32 is not None:
-                dev.block_scalar_f32(self._A_mom, d, self._S_mom32)
+                dev.block_scalar_rows_f32(self._A_mom, d, self._vbc_nodes, self._S_mom32)
             if self._mom_pc == "chebyshev":
                 if it == 0:      # spectrum of D^-1 J changes little within a step: estimate once per step,
                     # and little from step to step: the power iteration continues from the previous

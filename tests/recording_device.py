@@ -123,6 +123,12 @@ class RecordingDevice(Device):
         self._rec("rhs_update", basis["l"], x)
         return basis["l"]
 
+    def set_block_scalar_out(self, out):
+        pass
+
+    def block_scalar_rows_f32(self, vals, bs, block_rows, out):
+        self._rec("block_scalar_f32", vals, bs, out)
+
     def block_scalar_f32(self, vals, bs, out):
         self._rec("block_scalar_f32", vals, bs, out)
 
