@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--impl", default="nsb200", choices=["nsb200", "reference"])
     ap.add_argument("--n", "--cells", dest="n", type=int, default=73, help="cells per edge of the unit cube (73 -> 9.93 M DOF)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--solver-option", action="append", default=[], metavar="KEY=VALUE",
+                    help="IPCSSolver keyword for experiments, e.g. newton_forcing=0 (numbers only)")
     ap.add_argument("--ref-n", type=int, default=CPU_SAMPLE_N,
                     help="cells per edge of the bounded sample the CPU arm runs (and of the same-size GPU leg)")
     return ap.parse_args()
@@ -302,7 +304,8 @@ def run_nsb200(args):
         dist.barrier()
     import nsb200
     n = args.n
-    solver, ts = make_cavity_solver(n, rank, world, local)
+    opts = {k: float(v) if "." in v or "e" in v else int(v) for k, v in (o.split("=", 1) for o in args.solver_option)}
+    solver, ts = make_cavity_solver(n, rank, world, local, **opts)
     dev = solver.dev
 
     def step(e2e=False):
@@ -419,7 +422,8 @@ def run_nsb200(args):
         "breakdown_note": "ms_per_step / shares from a second pass over the same %d steps with every kernel class "
                           "event-timed (%.1f ms/step); GB/s of the large kernels and the roofline from the headline pass"
                           % (K, ms_instrumented / K),
-        "newton_iterations": solver.newton_iterations[-K:], "krylov_iterations": solver.krylov_iterations[-1],
+        "newton_iterations": solver.newton_iterations[-K:], "newton_iterations_all_steps": solver.newton_iterations,
+        "krylov_iterations": solver.krylov_iterations[-1],
         "chebyshev_fallbacks": solver.chebyshev_fallbacks,
         "checksums": checksums,
         "assembly_gdof_per_s": {k: sizes["nV"] / (big[k][0] / big[k][1] * 1e-3) / 1e9

@@ -553,7 +553,10 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     // norm of iteration k is therefore copied to a pinned ring and examined LAG iterations later, while the
     // next ones are already queued; the loop ends with a blocking read of the newest norm, so the exit
     // criterion ||r|| <= tol is unchanged (at most LAG extra iterations are spent).
-    const int lag = (n < (int64_t)1500000 && maxit > 16) ? NSB_CG_LAG : 0;
+    // (pressure-sized systems only: past the tolerance the extra iterations still move the solution in its last digits,
+    // and the velocity mass solve -- 1.2 M rows per rank at C5 on 8 GPUs -- must stop at the same iteration for every
+    // number of ranks, or the fields of an 8-GPU run differ from the 1-GPU run in the 8th digit)
+    const int lag = (n < (int64_t)500000 && maxit > 16) ? NSB_CG_LAG : 0;
     if (lag && ensure_cg_ring(ctx)) return -1;
     while (rnorm > tol && it < maxit) {
         if (nsb_launch_spmv(ctx, A, p, q, p, ds + S_PQ, st)) return -1;

@@ -82,6 +82,12 @@ class HaloPlan:
             sends = int(self.send_ptr[i + 1] - self.send_ptr[i])
             if expects != sends:
                 raise ValueError("rank %d sends %d entries to rank %d, which expects %d" % (rank, sends, int(r), expects))
+            # the flow control of the peer-memory exchange (csrc/comm.cu: acknowledgements per block of the pair) leans on
+            # traffic in BOTH directions of every pair; a one-sided pair would let a pusher run ahead of a reader
+            mine = int(self.recv_ptr[i + 1] - self.recv_ptr[i])
+            if (sends == 0) != (mine == 0):
+                raise ValueError("ranks %d and %d exchange in one direction only (%d sent, %d received): not supported by "
+                                 "the peer-memory transport, use NSB_HALO=nccl" % (rank, int(r), sends, mine))
             nghost.append(theirs["n_ghost"])
             off.append(theirs["recv_ptr"][s])
             slot.append(s)
