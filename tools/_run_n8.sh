@@ -1,13 +1,11 @@
 set -u
-run() { # name, env...
-  name=$1; shift
-  env "$@" python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29518 bench.py --gpus 8 --steps 6 --warmup 5 --no-cpu-baseline > gpurun_out/n8x.out 2> gpurun_out/n8x_$name.err; echo "bench $name rc=$?"
-  grep '^{' gpurun_out/n8x.out | tail -1 > gpurun_out/n8x_$name.json
-  python - <<PY
+for N in 8 4 2; do
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/n${N}_bench.out 2> gpurun_out/n${N}_bench.err; echo "bench N=$N rc=$?"
+grep '^{' gpurun_out/n${N}_bench.out | tail -1 > gpurun_out/n${N}_bench.json
+python - <<PY
 import json
-d=json.load(open('gpurun_out/n8x_$name.json'))
-print('$name', d['value'], d['ms_per_step'], d['krylov_iterations'], d['checksums'], d['config']['parallelism'][:40])
+d=json.load(open('gpurun_out/n${N}_bench.json'))
+print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value'], d['krylov_iterations'], d['checksums'], d['gpu_launches'])
+print({k:round(v['ms_per_step'],2) for k,v in d['breakdown'].items()})
 PY
-}
-run nccl NSB_HALO=nccl
-run f32gather NSB_PC_GATHER=f32
+done
