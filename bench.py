@@ -153,7 +153,7 @@ def workload_config(n, gpus):
                               "in D^-1 J that runs in single precision on the block-scalar part of J (mean block diagonals as "
                               "FP32, float4-padded vectors; operator, Arnoldi basis, residual test and solution stay FP64) "
                               "(velocity); persistent single-kernel CG rtol 1e-12 with a degree-8 Chebyshev polynomial "
-                              "preconditioner (pressure) / Jacobi CG rtol 1e-13 (mass)"}
+                              "preconditioner (pressure) / Jacobi CG rtol 1e-15 from u* + the previous step's correction (mass)"}
 
 
 # ---------------------------------------------------------------------------------------------

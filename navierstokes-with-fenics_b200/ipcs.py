@@ -48,7 +48,7 @@ class IPCSSolver(SolverBase):
                  preconditioner_precision="f32-scalar", pressure_preconditioner="chebyshev", pressure_chebyshev_degree=8,
                  pressure_chebyshev_ratio=300.0, pressure_solve="auto", form_viscous_term="standard",
                  linear_atol_factor=1.0, correction_rtol=None, extrapolate_pressure_guess=True, device=None,
-                 newton_forcing=0.001, pressure_rhs_projection=0):
+                 newton_forcing=0.001, pressure_rhs_projection=0, extrapolate_correction_guess=1):
         """``partition`` (partition.Partition, halo plans finalized): this rank's share of a
         mesh-partitioned multi-GPU run; ``mesh`` / ``boundary_markers`` are then
         the partition's local mesh and its carried-over markers.  Field vectors hold
@@ -61,7 +61,7 @@ class IPCSSolver(SolverBase):
         self._time_stepping = time_stepping
         self._tol, self._maxiter = tol, max_iter
         # Krylov tolerances (relative residual) replacing the reference's LU: 1e-12 for the momentum and pressure solves,
-        # two digits more for the mass matrix of the correction step.  Measured on the 16^3 cavity against the oracle at
+        # three digits more for the mass matrix of the correction step.  Measured on the 16^3 cavity against the oracle at
         # 1e-14 (tools/probe_parity16.py, profiles/r2_parity16_tolerances.jsonl): with every solve at 1e-12 the fields
         # after two steps differ by 1.2e-8 / 2.2e-8 (velocity / pressure); tightening the pressure solve or the last
         # Newton update changes nothing (Newton residual 5e-15 either way); with the mass solve at 1e-13 they agree to
@@ -71,8 +71,9 @@ class IPCSSolver(SolverBase):
         # At C5 (h 4.5x smaller, 11 steps) the same experiment with the GPU path alone (profiles/r2_mass_tolerance_c5.jsonl):
         # ||u|| moves by 4e-8 relative between mass tolerances 1e-13 and 1e-14 and by 4.5e-9 between 1e-14 and 1e-15 --
         # one digit of the mass tolerance is one digit of the fields, with a factor ~4e5 between them.  Default:
-        # two digits below linear_rtol (1e-14: four more CG iterations than 1e-13).
-        self._correction_rtol = 0.01 * linear_rtol if correction_rtol is None else correction_rtol
+        # three digits below linear_rtol (1e-15: fields reproducible to ~5e-10 whatever the initial guess, the number of
+        # ranks or the summation order); the extrapolated correction guess (below) pays for the extra iterations.
+        self._correction_rtol = 1e-3 * linear_rtol if correction_rtol is None else correction_rtol
         # Newton updates are solved to ||r|| <= max(linear_rtol ||b||, linear_atol_factor * linear_rtol * r0), r0 = the
         # step's first Newton residual.  1.0 (default): every update to 1e-12 r0 -- the converged u* then differs from an
         # LU-exact Newton iterate by O(1e-12 r0), inside dolfin's own stopping tolerance (1e-10), but the pressure that
@@ -96,6 +97,7 @@ class IPCSSolver(SolverBase):
         # ten solutions are in the basis, but 70-79 again after the basis is thinned out -- on average no better than
         # the extrapolation (72), hence not the default.
         self._p_basis_size, self._p_basis = int(pressure_rhs_projection), None
+        self._extrapolate_corr, self._corr_prev, self._corr_k = bool(extrapolate_correction_guess), None, None
         self._cache = cache_constant_matrices
         assert momentum_preconditioner in ("jacobi", "chebyshev")
         assert pressure_preconditioner in ("jacobi", "chebyshev")
@@ -470,9 +472,19 @@ class IPCSSolver(SolverBase):
         dev.assemble_correction(L.VEC, ustar=ustar, pnew=self._pressure, pold=self._old_pressure, b=self._bV)
         dev.bc_apply_vector(L.BC_LINEAR, self._bV, self._vbc_dofs, self._vbc_vals)
         dev.copy(ustar, self._velocities[0])
+        # initial guess u* + omega (u^n - u*^n): the correction of the previous step, scaled by the step-size ratio
+        # (the correction is -(k / alpha0) times the projected gradient of the pressure increment, smooth in time)
+        if self._extrapolate_corr and self._corr_prev is not None and self._corr_k:
+            dev.axpy(self._next_step_size / self._corr_k, self._corr_prev, self._velocities[0])
         dev.bc_apply_vector(L.BC_LINEAR, self._velocities[0], self._vbc_dofs, self._vbc_vals)
         n_c, _ = dev.cg(self._mass, self._dinv_mass, self._bV, self._velocities[0], rtol=self._correction_rtol,
                         work=self._work)
+        if self._extrapolate_corr:
+            if self._corr_prev is None:
+                self._corr_prev = dev.empty(self._velocities[0].numel())
+            dev.copy(self._velocities[0], self._corr_prev)
+            dev.axpy(-1.0, ustar, self._corr_prev)
+            self._corr_k = self._next_step_size
         dev.halo_exchange(L.HALO_NODES, d, self._velocities[0])
         dev.halo_status()
         self.krylov_iterations.append(dict(momentum=self._kry_momentum, pressure=self._kry_pressure, correction=n_c))
