@@ -253,6 +253,19 @@ int nsb_set_forms(nsb_ctx* ctx, int32_t conv, int32_t visc, const double* coriol
 int nsb_assemble_ipcs_momentum(nsb_ctx* ctx, int32_t flags, const double* ustar, const double* un,
                                const double* unm1, const double* pn, double* b_out, double* A_out,
                                void* stream);
+/* Allocation-free variant of the residual F above.  It has NO counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, same output and same arithmetic as nsb_assemble_ipcs_momentum(NSB_VEC) with a
+ * registered scratch, but the element-vector scratch is a file-scope static device array of
+ * nsb_static_scratch_doubles() = 2 097 152 doubles (16 MiB, held by every GPU that loads the library until exit):
+ * meshes with more than 69 905 tetrahedra / 174 762 triangles (ncells * nloc * d doubles beyond that) are rejected with an
+ * error.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and registers nothing.
+ * Default weak form only (standard convective term, reduced viscous term, no Coriolis term).  All calls on one GPU
+ * share the array, which keeps the last call's element vectors (nothing in it needs to start at zero): calls that
+ * overlap on the GPU -- different streams, different contexts -- race; serialise them. */
+int64_t nsb_static_scratch_doubles(void);
+int nsb_assemble_ipcs_momentum_residual_noalloc(nsb_ctx* ctx, const double* ustar, const double* un, const double* unm1,
+                                                const double* pn, double* b_out, void* stream);
 /* IPCS pressure Poisson a / L   source/ns_ipcs_solver.py:149-171 (:160-164) */
 int nsb_assemble_poisson(nsb_ctx* ctx, int32_t flags, const double* pn, const double* ustar,
                          double* b_out, double* A_out, void* stream);

@@ -121,6 +121,8 @@ PROTOTYPES = {
     "nsb_comm_init": (C.c_int, [vp, C.c_int32, C.c_int32, vp]),
     "nsb_comm_finalize": (C.c_int, [vp]),
     "nsb_set_halo": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, vp, vp, vp, vp, vp, vp]),
+    "nsb_static_scratch_doubles": (C.c_int64, []),
+    "nsb_assemble_ipcs_momentum_residual_noalloc": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
     "nsb_bsr_block_scalar_f32": (C.c_int, [vp, C.c_int64, C.c_int32, vp, vp, vp]),
     "nsb_set_block_scalar_out": (C.c_int, [vp, vp, C.c_int64]),
     "nsb_bsr_block_scalar_rows_f32": (C.c_int, [vp, C.c_int32, vp, vp, C.c_int32, vp, vp, vp]),

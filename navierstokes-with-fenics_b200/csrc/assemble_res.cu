@@ -189,3 +189,72 @@ int nsb_launch_residual_cells(nsb_ctx* ctx, const double* ustar, const double* u
     NSB_COUNT(ctx, 1);
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the residual assembly (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA-graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  The element-vector scratch of the two-phase assembly lives in a file-scope device array of a fixed,
+// modest size instead of the caller-registered workspace of nsb_set_scratch; every GPU that loads the library holds
+// these 16 MiB until the process exits.  ALL calls (of all contexts) on one GPU share the array: calls that overlap
+// on the GPU (different streams) race.  Nothing in it has to start at zero -- phase 1 writes every entry phase 2
+// reads -- so it is never cleared; it keeps the last call's element vectors.
+// ---------------------------------------------------------------------------------------------
+#define NSB_STATIC_SCRATCH_DOUBLES (2 * 1024 * 1024)      /* 16 MiB: 69 905 tetrahedra or 174 762 triangles */
+static __device__ __align__(256) double g_static_scratch[NSB_STATIC_SCRATCH_DOUBLES];
+
+#define NSB_STATIC_MAX_DEVICES 64
+static double* g_static_scratch_addr[NSB_STATIC_MAX_DEVICES];   // device address of the array, per device (host code
+                                                                // must not pass the symbol itself to a kernel)
+
+extern "C" int64_t nsb_static_scratch_doubles(void) { return NSB_STATIC_SCRATCH_DOUBLES; }
+
+extern "C" int nsb_assemble_ipcs_momentum_residual_noalloc(nsb_ctx* ctx, const double* ustar, const double* un,
+                                                           const double* unm1, const double* pn, double* b_out,
+                                                           void* stream) {
+    NSB_REQUIRE(ctx, ctx != nullptr, "null context");
+    NSB_REQUIRE(ctx, ustar && un && unm1 && pn && b_out, "null vector argument");
+    const nsb_pattern_dev& P = ctx->pat[NSB_PAT_P2P2];
+    NSB_REQUIRE(ctx, P.nrows > 0 && P.pair_ptr && P.pair_cell && P.pair_iloc, "P2xP2 pattern not set");
+    NSB_REQUIRE(ctx, ctx->ncells > 0 && ctx->coords && ctx->cell_nodes && ctx->cell_verts, "mesh not set");
+    NSB_REQUIRE(ctx, ctx->dim == 2 || ctx->dim == 3, "dimension must be 2 or 3");
+    NSB_REQUIRE(ctx, ctx->form_conv == 0 && ctx->form_visc == 0 && ctx->coriolis[0] == 0.0 && ctx->coriolis[1] == 0.0 &&
+                ctx->coriolis[2] == 0.0,
+                "the allocation-free residual covers the default weak form only (standard convective term, reduced "
+                "viscous term, no Coriolis term): use nsb_assemble_ipcs_momentum");
+    const int D = ctx->dim, NL = D == 2 ? 6 : 10;
+    const int64_t need = (int64_t)ctx->ncells * NL * D;
+    if (need > (int64_t)NSB_STATIC_SCRATCH_DOUBLES) {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "mesh too large for the allocation-free residual: %d cells need %lld doubles of element "
+                 "vectors, the static scratch holds %lld (at most %lld cells in %dD); use nsb_assemble_ipcs_momentum with "
+                 "nsb_set_scratch", (int)ctx->ncells, (long long)need, (long long)NSB_STATIC_SCRATCH_DOUBLES,
+                 (long long)(NSB_STATIC_SCRATCH_DOUBLES / (NL * D)), D);
+        return nsb_fail(ctx, "%s%s", msg, "");
+    }
+    // set-up, once per device, with that device current: the device address of the static array
+    int dev = -1;
+    NSB_CUDA(ctx, cudaGetDevice(&dev));
+    NSB_REQUIRE(ctx, dev == ctx->device, "the context's device must be current");
+    NSB_REQUIRE(ctx, dev >= 0 && dev < NSB_STATIC_MAX_DEVICES, "device index out of range");
+    if (g_static_scratch_addr[dev] == nullptr) {
+        double* ptr = nullptr;
+        NSB_CUDA(ctx, cudaGetSymbolAddress((void**)&ptr, g_static_scratch));
+        NSB_REQUIRE(ctx, ptr != nullptr, "cudaGetSymbolAddress returned a null address");
+        g_static_scratch_addr[dev] = ptr;
+    }
+    double* scratch = g_static_scratch_addr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+    const int B1 = nsb_blocks(ctx->ncells, 128), B2 = nsb_blocks(P.nrows, 256);
+    if (D == 2) {
+        k_residual_cells<2><<<B1, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn,
+                                               ctx->coef, scratch);
+        k_gather_rows<2, 6><<<B2, 256, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, scratch, b_out);
+    } else {
+        k_residual_cells<3><<<B1, 128, 0, st>>>(ctx->ncells, ctx->coords, ctx->cell_nodes, ctx->cell_verts, ustar, un, unm1, pn,
+                                               ctx->coef, scratch);
+        k_gather_rows<3, 10><<<B2, 256, 0, st>>>(P.nrows, P.pair_ptr, P.pair_cell, P.pair_iloc, scratch, b_out);
+    }
+    NSB_LAUNCH_CHECK(ctx, "k_residual_cells (static scratch)");
+    NSB_COUNT(ctx, 1);
+    return 0;
+}
