@@ -88,7 +88,7 @@ class IPCSSolver(SolverBase):
         # GMRES solve needs 4-5 iterations instead of 10.  Used only when the predicted r1 = rho * r0 is
         # ten times above Newton's own tolerance, i.e. when a second, exact update is certain to follow.  0 switches it
         # off (every update to linear_rtol * r0); the first step of a run has no history and is solved exactly.
-        self._newton_forcing, self._newton_rho = float(newton_forcing), None
+        self._newton_forcing, self._newton_rho, self._newton_r1 = float(newton_forcing), None, None
         # Pressure projection: the same SPD operator every step -> initial guess = energy-norm best approximation of the
         # new solution in the span of the last `pressure_rhs_projection` solutions (Fischer 1998; nsb_rhs_guess /
         # nsb_rhs_update).  For the all-Neumann problem on one GPU and in the replicated solve; 0 = off (default: the
@@ -255,6 +255,9 @@ class IPCSSolver(SolverBase):
         self._old_pressure.copy_(state["old_pressure"])
         self._p_hist = None if state.get("p_hist") is None else state["p_hist"].clone()
         self._p_hist_steps, self._prev_k = state.get("p_hist_steps", 0), state.get("prev_k")
+        # predictors built from the steps before the restore say nothing about the restored state
+        self._newton_rho = self._newton_r1 = None
+        self._corr_prev = self._corr_k = None
         if self._p_replicated:
             self._p_g_stale = True
         self._time_stepping.__dict__.update(copy.deepcopy(state["time_stepping"]))
@@ -325,6 +328,8 @@ class IPCSSolver(SolverBase):
             self._old_pressure.copy_(p0)
         if self._p_replicated:
             self._p_g_stale = True
+        self._newton_rho = self._newton_r1 = None
+        self._corr_prev = self._corr_k = None
         del sp
 
     # ---- one time step -------------------------------------------------------------------------
@@ -397,10 +402,14 @@ class IPCSSolver(SolverBase):
             # every Newton update is solved to linear_rtol relative to the step's INITIAL residual r0
             # (the accuracy LU-exact Newton reaches anyway): later iterations need fewer Krylov steps
             eta = self._linear_rtol
-            if (it == 0 and self._newton_forcing > 0.0 and self._newton_rho is not None
-                    and self._newton_rho * r0 > 10.0 * max(atol, rtol * r0)):
+            if it == 0 and self._newton_forcing > 0.0 and self._newton_rho is not None:
+                # predicted residual after this update: the SMALLER of (previous contraction) x r0 and the previous
+                # step's r1 itself -- when r0 jumps (restart, a step change of the boundary data) the contraction of the
+                # last step says nothing, and dolfin's own exit rule (r2 < 1e-9 r0) leaves u* sensitive to r1 at that level
+                r1_pred = min(self._newton_rho * r0, self._newton_r1)
                 # only when a second (exact) update is certain to follow: the last update sets the accuracy of u*
-                eta = min(1e-3, max(eta, self._newton_forcing * self._newton_rho))
+                if r1_pred > 10.0 * max(atol, rtol * r0):
+                    eta = min(1e-3, max(eta, self._newton_forcing * r1_pred / r0))
             kw = dict(rtol=eta, atol=self._linear_atol_factor * eta * r0, restart=self._restart, work=self._work)
             if self._mom_pc == "chebyshev":
                 # the polynomial is only safe while the spectrum of D^-1 J stays near the real interval:
@@ -425,7 +434,8 @@ class IPCSSolver(SolverBase):
             if it == 1:
                 # contraction of the first update; an inexact first update that was followed by a poor contraction
                 # is not trusted as a predictor for the next step
-                self._newton_rho = r / r0 if (r0 > 0.0 and (eta == self._linear_rtol or r / r0 < 1e-2)) else None
+                ok = r0 > 0.0 and (eta == self._linear_rtol or r / r0 < 1e-2)
+                self._newton_rho, self._newton_r1 = (r / r0, r) if ok else (None, None)
             converged = newton_converged(r, r0, atol, rtol)
         self.newton_iterations.append(it)
         self.newton_residual = r
