@@ -112,6 +112,8 @@ struct nsb_cheb32_epi {
     // nullptr: gather from the float4 vector.
     const unsigned long long* x_h;
     unsigned long long* dnew_h;
+    // dofs flagged here are identity rows of the operator, (A x)_i = x_i (nsb_matrix.bc_mask of the cached operators)
+    const uint8_t* mask;
 };
 __device__ __forceinline__ unsigned long long nsb_pack_bf16x3(float a, float b, float c) {
     // round-to-nearest-even bf16 = upper 16 bits of the float

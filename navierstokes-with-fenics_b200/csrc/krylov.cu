@@ -225,8 +225,9 @@ bool nsb_spmv32_available(const nsb_matrix* A);
 int nsb_launch_spmv32(nsb_ctx* ctx, const nsb_matrix* A, const float* x, float* y, cudaStream_t st,
                       const nsb_cheb32_epi* epi = nullptr);
 
-// the single-precision Chebyshev polynomial is not exactly linear in v (FP32 rounding): only the flexible
-// GMRES may use it
+// the single-precision Chebyshev polynomial is not exactly linear in v (FP32 rounding): the flexible GMRES may use it,
+// and CG on an SPD operator (the polynomial is SPD for every interval end below lambda_max; its rounding perturbs the
+// search directions at the 1e-7 level, which costs CG nothing measurable: the residual recurrence stays FP64)
 static bool pc_single_precision(const nsb_matrix* A, const nsb_precond* M) {
     return M->kind == NSB_PC_CHEBYSHEV && M->lowp && nsb_spmv32_available(A);
 }
@@ -257,7 +258,7 @@ static int apply_cheb32(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M,
     for (int k = 1; k < M->degree; ++k) {
         const double rho = 1.0 / (2.0 * sigma1 - rho_old);
         if (fused) {                              // d and q alternate as old / new direction
-            nsb_cheb32_epi E;
+            nsb_cheb32_epi E{};
             E.dinv = M->inv_diag; E.r = r; E.dnew = q; E.z = z;
             E.zout = k == M->degree - 1 ? zout : nullptr;
             E.a = (float)(rho * rho_old); E.b = (float)(2.0 * rho / delta);
@@ -487,7 +488,7 @@ static int ensure_cg_ring(nsb_ctx* ctx) {
     return 0;
 }
 
-extern "C" int64_t nsb_cg_workspace_doubles(int64_t n) { return 7 * n; }
+extern "C" int64_t nsb_cg_workspace_doubles(int64_t n) { return 8 * n + 16; }   // r, z, p, q + 4 n of preconditioner scratch
 
 extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, const double* b, double* x,
                       double rtol, double atol, int32_t maxit, int32_t nullspace, double* work,
@@ -535,7 +536,7 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
     NSB_LAUNCH_CHECK(ctx, "k_cg_init");
     NSB_COUNT(ctx, 1);
     if (!jac) {
-        if (apply_pc(ctx, A, M, r, z, scratch, n, st)) return -1;
+        if (apply_pc(ctx, A, M, r, z, scratch, n, st, pc_single_precision(A, M))) return -1;
         NSB_TIMED(ctx, NSB_T_KRYLOV, st);
         k_reduce<true><<<G, 256, 0, st>>>(n, r, z, ctx->d_partials, ctx->d_counter, ds + cur);
         if (nsb_allreduce_sum(ctx, ds + cur, 1, st)) return -1;
@@ -573,7 +574,7 @@ extern "C" int nsb_cg(nsb_ctx* ctx, const nsb_matrix* A, const nsb_precond* M, c
         NSB_LAUNCH_CHECK(ctx, "k_cg_update1");
         NSB_COUNT(ctx, 1);
         if (!jac) {
-            if (apply_pc(ctx, A, M, r, z, scratch, n, st)) return -1;
+            if (apply_pc(ctx, A, M, r, z, scratch, n, st, pc_single_precision(A, M))) return -1;
             NSB_TIMED(ctx, NSB_T_KRYLOV, st);
             k_reduce<true><<<G, 256, 0, st>>>(n, r, z, ctx->d_partials, ctx->d_counter, ds + nxt);
             NSB_LAUNCH_CHECK(ctx, "k_reduce(rz)");

@@ -76,7 +76,11 @@ int nsb_launch_spmv(nsb_ctx* ctx, const nsb_matrix* A, const double* x, double* 
 // NSB_PAD32(bs) floats per node.  On a partitioned mesh the padded node is moved as 8-byte words by the
 // ordinary halo exchange (a float4 = 2 doubles, a float2 = 1).
 bool nsb_spmv32_available(const nsb_matrix* A) {
-    if (A->kind != NSB_BSR || (A->bs != 3 && A->bs != 2)) return false;
+    if (A->bs != 3 && A->bs != 2) return false;
+    // a Kronecker CSR matrix (scalar values applied to bs interleaved components) IS block-scalar: its float copy in
+    // diag32 serves the same kernel (the velocity mass matrix of the correction step)
+    if (A->kind == NSB_CSR) return A->diag32 != nullptr;
+    if (A->kind != NSB_BSR) return false;
     if (A->diag32) return true;
     return A->vals32 && A->tiles && A->ntiles > 0 &&
            ((((uintptr_t)A->vals32) | ((uintptr_t)A->col) | ((uintptr_t)A->tiles)) & 15) == 0;
@@ -158,6 +162,11 @@ k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* 
                              c2 = reinterpret_cast<const float2*>(E.z)[row];
                 ri[0] = a2.x; ri[1] = a2.y; dold[0] = b2.x; dold[1] = b2.y; zi[0] = c2.x; zi[1] = c2.y;
             }
+            if (E.mask != nullptr) {
+#pragma unroll
+                for (int c = 0; c < BS; ++c)
+                    if (E.mask[row * BS + c]) acc[c] = dold[c];
+            }
 #pragma unroll
             for (int c = 0; c < BS; ++c) {
                 ri[c] -= (float)E.dinv[row * BS + c] * acc[c];
@@ -178,6 +187,11 @@ k_spmv_kron32(int32_t nrows, const int32_t* __restrict__ rowptr, const int32_t* 
                 reinterpret_cast<float2*>(E.z)[row] = make_float2(zi[0], zi[1]);
             }
         } else {
+            if (E.mask != nullptr) {
+#pragma unroll
+                for (int c = 0; c < BS; ++c)
+                    if (E.mask[row * BS + c]) acc[c] = x[row * PB + c];
+            }
             if constexpr (BS == 3) reinterpret_cast<float4*>(y)[row] = make_float4(acc[0], acc[1], acc[2], 0.0f);
             else reinterpret_cast<float2*>(y)[row] = make_float2(acc[0], acc[1]);
         }
@@ -192,7 +206,8 @@ static int launch_spmv_kron32(nsb_ctx* ctx, const nsb_matrix* A, const float* x,
     // 8 x 4 38.7, 2 x 4 39.1, 4 x 8 39.5, 8 x 8 56.5, 16 x 2 66.8, 32 x 2 121
     const int lanes = per_row <= 40.0 ? 4 : 8;
     const int blocks = nsb_blocks((int64_t)A->nrows * lanes, 256);
-    const nsb_cheb32_epi E = epi ? *epi : nsb_cheb32_epi{};
+    nsb_cheb32_epi E = epi ? *epi : nsb_cheb32_epi{};
+    E.mask = A->bc_mask;
 #define NSB_KRON(LANES, U)                                                                                                  \
     do {                                                                                                                    \
         if (epi) k_spmv_kron32<BS, LANES, U, true><<<blocks, 256, 0, st>>>(A->nrows, A->rowptr, A->col, A->diag32, x, nown, xg, y, E);  \

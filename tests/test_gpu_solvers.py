@@ -296,6 +296,48 @@ def test_lambda_max_on_the_block_scalar_copy(case):
     assert abs(lam64 - lam32) < 0.2 * lam64          # S (x) I is the dominant part of J
 
 
+def test_cg_mass_matrix_with_f32_chebyshev_polynomial(case):
+    """velocity mass system of the correction step (Kronecker CSR, Dirichlet rows through the mask): Jacobi-CG and CG
+    preconditioned by the single-precision Chebyshev polynomial on the float copy (block-scalar kernel, masked identity
+    rows, bf16 gathers) reach the sparse-LU solution; the polynomial needs fewer iterations"""
+    import torch
+    import oracle
+    import nsb200._lib as L
+    dev, d = case["dev"], case["d"]
+    pat = dev.patterns["P2P2"]
+    n = pat.nrows * d
+    A = dev.empty(pat.nnz)
+    dev.assemble_correction(L.MAT, A=A)
+    dofs, vals = dev.spaces.dirichlet_table([(1, None, (0.3,) * d), (3, None, (0.0,) * d)], "V")
+    mask = np.zeros(n, dtype=np.uint8)
+    mask[dofs] = 1
+    A32 = dev.empty(pat.nnz, dtype=torch.float32)
+    dev.to_f32(A, A32)
+    mat = dev.matrix("P2P2", A, L.CSR, d, up(dev, mask), diag32=A32)
+    dinv = dev.empty(n)
+    dev.inv_diagonal(mat, dinv)
+    rng = np.random.default_rng(31)
+    b = rng.uniform(-1, 1, n) * 1e-3
+    b[dofs] = vals
+    Mh = sp.kron(sp.csr_matrix((A.cpu().numpy(), pat.col_host, pat.rowptr_host), shape=(pat.nrows, pat.nrows)), sp.identity(d)).tocsr()
+    ref = spla.spsolve(oracle.bc.apply_ident(Mh, dofs).tocsc(), b)
+    x0 = np.zeros(n)
+    x0[dofs] = vals
+    xj = up(dev, x0)
+    it_j, _ = dev.cg(mat, dinv, up(dev, b), xj, rtol=1e-14)
+    assert rel_max_err(xj.cpu().numpy(), ref) < 1e-10
+    lmax = 1.1 * dev.lambda_max(mat, dinv, iters=40, lowp=True)
+    lam_ref = float(np.abs(spla.eigs(sp.diags(dinv.cpu().numpy()) @ oracle.bc.apply_ident(Mh, dofs), k=1, which="LM",
+                                     return_eigenvectors=False, tol=1e-8)[0]))
+    assert 0.95 * lam_ref < lmax / 1.1 < 1.02 * lam_ref, (lmax / 1.1, lam_ref)
+    for degree in (2, 3, 5):
+        pc = dev.precond(dinv, L.PC_CHEBYSHEV, degree, lmax / 20.0, lmax, lowp=True)
+        xc = up(dev, x0)
+        it_c, _ = dev.cg(mat, pc, up(dev, b), xc, rtol=1e-14)
+        assert rel_max_err(xc.cpu().numpy(), ref) < 1e-10, degree
+        assert it_c < it_j, (degree, it_c, it_j)
+
+
 def _channel_bcs(d):
     import nsb200
     V, P = nsb200.VelocityBCType, nsb200.PressureBCType
