@@ -77,9 +77,10 @@ class IPCSSolver(SolverBase):
         self._correction_rtol = 1e-3 * linear_rtol if correction_rtol is None else correction_rtol
         # Newton updates are solved to ||r|| <= max(linear_rtol ||b||, linear_atol_factor * linear_rtol * r0), r0 = the
         # step's first Newton residual.  1.0 (default): every update to 1e-12 r0 -- the converged u* then differs from an
-        # LU-exact Newton iterate by O(1e-12 r0), inside dolfin's own stopping tolerance (1e-10), but the pressure that
-        # follows sees that difference amplified by alpha0 / k and 1 / h (measured at 16^3, dt = 1e-2: velocity 2e-9,
-        # pressure 1.9e-8 relative); 0.01 solves the last update two digits further (about two more GMRES iterations)
+        # LU-exact Newton iterate by O(1e-12 r0), inside dolfin's own stopping tolerance (1e-10).  Measured at 16^3,
+        # dt = 1e-2 against the oracle at 1e-15 (profiles/r2_forcing_parity_16cubed.jsonl): 1.1e-10 / 1.4e-10 (velocity /
+        # pressure) with 1.0, and the same with 0.1 and 0.01 (one or two more GMRES iterations): the factor is a knob for
+        # harder problems, not needed here.  (The 1.9e-8 once attributed to it was the mass-solve tolerance, above.)
         self._linear_atol_factor = linear_atol_factor
         # Forcing term of the FIRST Newton update of a step (inexact Newton, Eisenstat-Walker): Newton contracts the
         # residual by rho = r1 / r0 per step (observed at the previous time step, 1e-4 .. 1e-6 here), so a linear
@@ -270,17 +271,40 @@ class IPCSSolver(SolverBase):
             self._p_g_stale = True
         self._time_stepping.__dict__.update(copy.deepcopy(state["time_stepping"]))
 
-    def fetch_solution(self, out=None):
+    def fetch_solution(self, out=None, wait=True):
         """Device -> pinned host copy of the mixed solution vector (what the reference hands to
-        its XDMF writer, source/ns_problem.py:733-735).  Returns (host tensor, bytes)."""
+        its XDMF writer, source/ns_problem.py:733-735).  Returns (host tensor, bytes).
+        ``wait=False``: the copy runs on a side stream behind the kernels issued so far and overlaps the next time
+        step; ``wait_solution()`` (or the next ``fetch_solution`` / ``solution``) waits for it -- the host tensor
+        must not be read before."""
+        self.wait_solution()                      # the previous copy still owns the host buffer and self._w
         w = self.solution
         if out is None:
             if not hasattr(self, "_w_host"):
                 self._w_host = self.dev.host_buffer(w.numel())
             out = self._w_host
-        out.copy_(w, non_blocking=True)
-        torch.cuda.current_stream(self.dev.torch_device).synchronize()
+        cur = torch.cuda.current_stream(self.dev.torch_device)
+        if wait or self.dev.torch_device.type != "cuda":
+            out.copy_(w, non_blocking=True)
+            cur.synchronize()
+            return out, w.numel() * 8
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(self.dev.torch_device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        self._copy_stream.wait_event(ready)
+        with torch.cuda.stream(self._copy_stream):
+            out.copy_(w, non_blocking=True)
+        self._copy_done = torch.cuda.Event()
+        self._copy_done.record(self._copy_stream)
         return out, w.numel() * 8
+
+    def wait_solution(self):
+        """block until the copy started by ``fetch_solution(wait=False)`` has arrived"""
+        ev = getattr(self, "_copy_done", None)
+        if ev is not None:
+            ev.synchronize()
+            self._copy_done = None
 
     # ---- constant operators (pressure stiffness, velocity mass), quirk Q8 ----------------------
     def _assemble_constant(self):
@@ -613,6 +637,7 @@ class IPCSSolver(SolverBase):
         """mixed-space vector (source/ns_ipcs_solver.py:240-247), with the mean-pressure shift
         of source/ns_solver_base.py:1190-1203 applied to the copy when requested."""
         dev, sp = self.dev, self.dev.spaces
+        self.wait_solution()                      # an overlapped copy of the previous solution still reads self._w
         if not hasattr(self, "_w"):
             self._w = dev.zeros(sp.ndofs_W)
             self._v2w, self._q2w = dev.upload(sp.V_to_W()), dev.upload(sp.Q_to_W())
