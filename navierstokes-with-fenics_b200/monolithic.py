@@ -26,6 +26,8 @@ class MixedSolverBase(SolverBase):
         # degree and the ratio lambda_max / lambda_min of its interval
         self.saddle_options = dict(inner_rtol=1e-2, vel_degree=8, vel_ratio=8.0, lp_degree=8, lp_ratio=300.0)
         self.krylov_iterations, self.inner_iterations = [], 0
+        # inexact first Newton update of a time step (instationary solver, hand-written K16 only); 0 = every update exact
+        self.newton_forcing, self._newton_rho, self._newton_r1 = 0.0, None, None
         # ``device``: an existing Device of this mesh (the dolfin-named compat layer shares one per mesh)
         self.dev = dev = Device(mesh, device_index, mixed=True) if device is None else device
         self._nW = dev.spaces.ndofs_W
@@ -96,13 +98,25 @@ class MixedSolverBase(SolverBase):
         while not converged and it < maxit:
             jacobian()
             if self._use_gmres():
-                self._gmres_update(r0)
+                # forcing term for the FIRST update of a time step (same rule as ipcs.py: only when the predicted r1 --
+                # the smaller of previous contraction x r0 and the previous step's r1 -- is ten times above the Newton
+                # tolerance, so that a second, exact update is certain to follow and sets the accuracy)
+                eta = None
+                if it == 0 and self.newton_forcing > 0.0 and self._newton_rho is not None:
+                    r1_pred = min(self._newton_rho * r0, self._newton_r1)
+                    if r1_pred > 10.0 * max(atol, rtol * r0):
+                        eta = min(1e-3, max(self._linear_rtol, self.newton_forcing * r1_pred / r0))
+                self._gmres_update(r0, eta)
             else:
+                eta = None
                 dev.direct_solve("WW", self._A, self._b, self._dx, self._reorder)
             dev.axpy(-1.0, self._dx, x)
             r = residual()
             hist.append(r)
             it += 1
+            if it == 1 and self.newton_forcing > 0.0:
+                ok = r0 > 0.0 and (eta is None or r / r0 < 1e-2)
+                self._newton_rho, self._newton_r1 = (r / r0, r) if ok else (None, None)
             converged = (r / r0 < rtol) or (r < atol)
         self.newton_history = hist
         if not converged and error_on_nonconvergence:
@@ -171,7 +185,7 @@ class MixedSolverBase(SolverBase):
         self._vel_lmax = None
         del C
 
-    def _gmres_update(self, r0):
+    def _gmres_update(self, r0, eta=None):
         """dx = J^-1 b by flexible GMRES, right-preconditioned by the block-triangular Cahouet-Chabard operator;
         solved to ``linear_rtol`` relative to the step's initial Newton residual, like the IPCS momentum solve"""
         import ctypes as C
@@ -190,7 +204,8 @@ class MixedSolverBase(SolverBase):
         # ||r|| <= max(rtol ||b||, 0.01 rtol r0): the first update to rtol, the later (small) ones two digits below the
         # step's initial residual -- the residual norm weighs velocity rows ~ h^2 alpha0/k against pressure rows ~ h,
         # and the pressure only reaches the 1e-8 parity bar with the last update solved that far
-        n_it, _ = dev.gmres(self._Amat, pc, self._b, self._dx, rtol=self._linear_rtol, atol=0.01 * self._linear_rtol * r0,
+        rtol_ = self._linear_rtol if eta is None else eta
+        n_it, _ = dev.gmres(self._Amat, pc, self._b, self._dx, rtol=rtol_, atol=(0.01 if eta is None else 1.0) * rtol_ * r0,
                             maxit=20 * self._gmres_restart, restart=self._gmres_restart, work=self._gmres_work, x0_is_zero=True)
         self.krylov_iterations.append(n_it)
         self.inner_iterations += S.inner_iterations - t0
