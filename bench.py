@@ -149,11 +149,11 @@ def workload_config(n, gpus):
             "linear_solvers": "FP64 flexible GMRES(40), every Newton update to 1e-12 of the step's first residual except the "
                               "first update of a step (forcing term 0.001 x the Newton contraction observed at the previous "
                               "step, only when a second update is certain to follow: same Newton counts, same fields), "
-                              "right-preconditioned by a degree-10 Chebyshev polynomial "
+                              "started from the previous step's update, right-preconditioned by a degree-10 Chebyshev polynomial "
                               "in D^-1 J that runs in single precision on the block-scalar part of J (mean block diagonals as "
                               "FP32, float4-padded vectors; operator, Arnoldi basis, residual test and solution stay FP64) "
                               "(velocity); persistent single-kernel CG rtol 1e-12 with a degree-8 Chebyshev polynomial "
-                              "preconditioner (pressure) / Jacobi CG rtol 1e-15 from u* + the previous step's correction (mass)"}
+                              "preconditioner (pressure) / CG rtol 1e-15 from u* + the previous step's correction, degree-2 single-precision Chebyshev polynomial preconditioner (mass)"}
 
 
 # ---------------------------------------------------------------------------------------------
