@@ -67,3 +67,48 @@ def test_bc_tuple_translation_matches_reference_format():
     assert nsb200.solver_base.newton_converged(1e-11, 1.0, 1e-10, 1e-9)
     assert nsb200.solver_base.newton_converged(1e-3, 1e7, 1e-10, 1e-9)
     assert not nsb200.solver_base.newton_converged(1e-3, 1.0, 1e-10, 1e-9)
+
+
+def test_ipcs_newton_forcing_and_update_guess_host_logic(built_library):
+    """Host logic of the inexact first Newton update and of the extrapolated update guess (ipcs.py), on the recording device
+    with scripted residual norms r0 = 1, r1 = 1e-4, r2 = 1e-13 per step: step 1 solves both updates to linear_rtol from a
+    zero guess; from step 2 on the first update is solved to 0.001 x min(rho r0, r1 of the previous step) / r0 = 1e-7 from the
+    previous step's update, the second exactly; a state restore drops both predictors."""
+    import nsb200
+    from recording_device import RecordingDevice
+    m, mk = nsb200.hyper_cube(2, 3)
+    ts = nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=0.01)
+    dev = RecordingDevice(m, norm_script=(1.0, 1e-4, 1e-13))
+    s = nsb200.IPCSSolver(m, mk, "standard", ts, device=dev)
+    s.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=0.1))
+    V = nsb200.VelocityBCType
+    s.set_boundary_conditions([(V.no_slip, w, None) for w in (1, 2, 3)] + [(V.constant, 4, (1.0, 0.0))])
+
+    def step():
+        dev.log.clear()
+        ts.update_coefficients()
+        s.solve()
+        ts.advance_time()
+        s.advance_time()
+        return [(e[8], e[9], e[11]) for e in dev.log if e[0] == "gmres"]          # (rtol, atol, x0_is_zero)
+    first = step()
+    assert first == [(1e-12, 1e-12, True), (1e-12, 1e-12, True)]
+    second = step()
+    assert second[0][2] is False and second[1][2] is True                          # guess only for the first update
+    assert abs(second[0][0] - 1e-7) < 1e-20 and abs(second[0][1] - 1e-7) < 1e-20 and second[1][:2] == (1e-12, 1e-12)
+    assert s.newton_iterations == [2, 2]
+    state = s.get_state()
+    s.set_state(state)
+    assert step() == first                                                         # predictors dropped by the restore
+    # forcing off: every update exact, the guess stays
+    s2 = nsb200.IPCSSolver(m, mk, "standard", nsb200.BDFTimeStepping(0.0, 1.0, order=2, desired_start_time_step=0.01),
+                           device=RecordingDevice(m, norm_script=(1.0, 1e-4, 1e-13)), newton_forcing=0.0,
+                           extrapolate_newton_update=0)
+    s2.set_equation_coefficients(dict(convective_term=1.0, pressure_term=1.0, viscous_term=0.1))
+    s2.set_boundary_conditions([(V.no_slip, w, None) for w in (1, 2, 3)] + [(V.constant, 4, (1.0, 0.0))])
+    for _ in range(2):
+        s2._time_stepping.update_coefficients()
+        s2.solve()
+        s2._time_stepping.advance_time()
+        s2.advance_time()
+    assert all(e[8] == 1e-12 and e[11] is True for e in s2.dev.log if e[0] == "gmres")
