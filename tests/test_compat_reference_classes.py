@@ -248,3 +248,28 @@ def test_forms_outside_the_vocabulary_are_refused(compat):
         D.NonlinearVariationalSolver(D.NonlinearVariationalProblem(F, u, [], D.derivative(F, u)))
     with pytest.raises(NotImplementedError):
         D.FunctionSpace(mesh, D.FiniteElement("DG", cell, 1))
+
+
+@pytest.mark.parametrize("dim,n", [(2, 4), (3, 3)])
+def test_reference_grid_generator_marks_what_the_mirror_marks(compat, dim, n):
+    """source/grid_generator.py hyper_cube / hyper_rectangle, imported unchanged and run on the compat layer (its
+    CompiledSubDomain strings decide which exterior facet gets which id), against nsb200.grid: same vertices, same cells in
+    the same order, same boundary id on every exterior facet -- the marker conventions of the mirror are the reference's own"""
+    D, _ = compat
+    import nsb200
+    import grid_generator
+    mesh, markers = grid_generator.hyper_cube(dim, n)
+    m2, _ = nsb200.hyper_cube(dim, n)
+    assert np.array_equal(mesh._m.coords, m2.coords) and np.array_equal(mesh._m.cells, m2.cells)
+    assert np.array_equal(mesh._m.bfacets, m2.bfacets)
+    ref_ids = np.array([markers[f] for f in D.facets(mesh) if f.exterior()])
+    assert np.array_equal(ref_ids, m2.bfacet_marker)
+    Mk = grid_generator.HyperCubeBoundaryMarkers
+    assert set(int(i) for i in np.unique(ref_ids)) == {Mk.left.value, Mk.right.value, Mk.bottom.value, Mk.top.value} | \
+        ({Mk.back.value, Mk.front.value} if dim == 3 else set())
+    p1 = (2.0, 1.0) if dim == 2 else (2.0, 1.0, 0.5)
+    nn = (2 * n, n) if dim == 2 else (2 * n, n, 2)
+    mesh, markers = grid_generator.hyper_rectangle((0.0,) * dim, p1, nn)
+    m2, _ = nsb200.hyper_rectangle((0.0,) * dim, p1, nn)
+    assert np.array_equal(mesh._m.cells, m2.cells)
+    assert np.array_equal(np.array([markers[f] for f in D.facets(mesh) if f.exterior()]), m2.bfacet_marker)
